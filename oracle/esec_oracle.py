@@ -422,7 +422,8 @@ class E2SecOracle:
 
     def __init__(self, ground_label, hand_label, support_hand, thresh, translation, roll, ground_pts,
                  total_unique_labels, replace=False, old=(), new=(), relations=3,
-                 filter_mode="closure", seed=0, ref_filter=None, keep_details=False):
+                 filter_mode="closure", seed=0, ref_filter=None, keep_details=False,
+                 radius_override=None):
         self.ground_label, self.hand_label, self.support_hand = ground_label, hand_label, support_hand
         self.thresh = float(thresh)
         self.T = np.asarray(translation, np.float64)
@@ -436,6 +437,8 @@ class E2SecOracle:
         self.relations = relations
         self.filter_mode, self.seed, self.ref_filter = filter_mode, seed, ref_filter
         self.keep_details = keep_details
+        # test speed-up only: {(frame, label_index): median_distance} replaces the O(n^2) pdist call
+        self.radius_override = radius_override or {}
         # globals :32-59
         self.o = {"1": None, "2": None, "3": None}
         self.count = {"1": 0, "2": 0, "3": 0}
@@ -482,7 +485,9 @@ class E2SecOracle:
             obj = transform_points(transform_points(cloud[idx], self.T), self.R)
             if i != self.ground_idx and i != 0 and len(obj) > 3:             # :1520
                 center = np.median(obj, axis=0)                              # :1523
-                radius = pairwise_median(obj)                                # :1524
+                radius = self.radius_override.get((frame, i))
+                if radius is None:
+                    radius = pairwise_median(obj)                            # :1524
                 d.update(radius=radius, seed=find_seed(obj, center), filtered=True, median=center)
                 if self.filter_mode == "closure":
                     out = closure_filter(obj, center, radius)

@@ -235,5 +235,44 @@ def run_reference_capture(mode, pcl, lab, savename, work, tr):
     return out, fixture, ref
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and "--frames" not in sys.argv:
     main()
+
+
+def write_frames_fixture(path=None):
+    """tests/golden/pushing06_frames.npz -- the 75 processed Pushing_06 frames (file index i % 3 == 0)
+    reduced to the points the path can use: valid (non-NaN) points whose upscaled + replaced label is a
+    tracked non-ground entity (4, 5, 6, 11).  Ground-label and border points are never read after frame 0
+    (manipulation_analyser.py:1514-1546 skips them, the relations use the frame-0 `ground`), so dropping
+    them changes no output.  Stored sparse: raster index (delta coded), float32 xyz, uint8 label."""
+    path = path or os.path.join(GOLD, "pushing06_frames.npz")
+    pcl = os.path.join(REF, "example", "Pushing_06")
+    lab = os.path.join(REF, "example", "Pushing_06_labels")
+    files = sorted(os.listdir(pcl))
+    fid, hand_raw, offs, idx, xs, labs = [], [], [0], [], [], []
+    for i, f in enumerate(files):
+        if i % 3:
+            continue
+        stem = f[:-7]
+        xyz, _ = pcd_io.read_pcd_xyz(os.path.join(pcl, stem + "_pc.pcd"))
+        raw = pcd_io.read_labels(os.path.join(lab, stem + "_left-labels.dat"))
+        full = esec_oracle.replace_labels(esec_oracle.resize_nearest(raw, 640, 480),
+                                          ARGS["old"], ARGS["new"]).flatten()
+        keep = np.isin(full, [4, 5, 6, 11]) & ~np.isnan(xyz).any(1)
+        k = np.nonzero(keep)[0]
+        fid.append(i)
+        hand_raw.append(bool((raw == ARGS["hand_label"]).any()))
+        offs.append(offs[-1] + len(k))
+        idx.append(np.diff(k, prepend=0).astype(np.uint32))
+        xs.append(xyz[k])
+        labs.append(full[k].astype(np.uint8))
+    xyz = np.concatenate(xs)
+    np.savez_compressed(path, frame_ids=np.asarray(fid, np.int32), hand_in_raw=np.asarray(hand_raw),
+                        offsets=np.asarray(offs, np.int64), idx_delta=np.concatenate(idx),
+                        x=xyz[:, 0].copy(), y=xyz[:, 1].copy(), z=xyz[:, 2].copy(),
+                        label=np.concatenate(labs), n_points=np.int64(307200))
+    return path
+
+
+if __name__ == "__main__" and "--frames" in sys.argv:
+    print(write_frames_fixture())
