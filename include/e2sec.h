@@ -1,0 +1,167 @@
+/* e2sec.h -- C ABI of the B200-native e2SEC extraction hot path.
+ *
+ * Drop-in boundary for ONE path of tobi-code/ManipulationLibrary: the per-frame pass of
+ * manipulation_analyser.py (_process :1355-2182) and the native operator it calls
+ * (cython_filter_new/filter_cython_new.pyx:6-93).  Every entry point below names the reference
+ * interface it replaces.  Plain pointers and sizes only; no C++ exceptions cross this boundary.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative E2SEC_ERR_* otherwise; e2sec_last_error(ctx)
+ *     gives the message (e2sec_last_error(NULL) for failures of e2sec_create itself);
+ *   - the caller allocates every output buffer; pointer arguments are HOST pointers unless the
+ *     argument name ends in _dev or the function says otherwise;
+ *   - one context = one CUDA device + one stream; not thread-safe (the reference keeps its state in
+ *     module globals, manipulation_analyser.py:32-59, and is not re-entrant either);
+ *   - there is NO CPU fallback: without a CUDA device e2sec_create fails with E2SEC_ERR_CUDA.
+ */
+#ifndef E2SEC_H
+#define E2SEC_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define E2SEC_ABI_VERSION 1
+#define E2SEC_MAX_ENTITIES 64      /* len(total_unique_labels) upper bound                           */
+#define E2SEC_LABEL_LUT 4096       /* raw labels must be integers in [0, E2SEC_LABEL_LUT)            */
+
+#define E2SEC_OK 0
+#define E2SEC_ERR_ARG (-1)
+#define E2SEC_ERR_CUDA (-2)
+#define E2SEC_ERR_CAPACITY (-3)
+#define E2SEC_ERR_IO (-4)
+#define E2SEC_ERR_STATE (-5)
+
+/* Filter modes.  CLOSURE = deterministic fixed point of the reference's flood fill
+ * (connected component of the seed in the radius graph).  REFERENCE_SEEDED replays pyx:61-83 pass by
+ * pass with CPython's MT19937 (random.seed(s); random.choice(list)) for the per-call seed
+ * filter_seed(base, frame, label_index) = (base + 1000003*frame + 7919*label_index) mod 2^32.        */
+#define E2SEC_FILTER_CLOSURE 0
+#define E2SEC_FILTER_REFERENCE_SEEDED 1
+
+typedef struct e2sec_ctx e2sec_ctx;
+
+/* Sequence parameters = the arguments of analyse_maniac_manipulation (:2184-2185) that the per-frame
+ * pass reads, plus the frame-0 products (:1397-1426) which are INPUTS here.           */
+typedef struct e2sec_params {
+    int32_t n_entities;                          /* len(total_unique_labels) (:1406-1426)              */
+    int32_t entity_label[E2SEC_MAX_ENTITIES];    /* total_unique_labels, ascending as np.unique gives  */
+    int32_t hand_label, ground_label;
+    int32_t support_hand;                        /* label, or -1 for None                              */
+    int32_t n_replace;                           /* replace=True: old[i] -> new[i], sequential (:176)  */
+    int32_t replace_old[16], replace_new[16];
+    double thresh;                               /* touching threshold                                 */
+    double translation[16], roll[16];            /* row-major 4x4 (:1484-1485)                         */
+    int32_t n_ground;                            /* the frame-0 ground cloud, already transformed      */
+    const double *ground_xyz;                    /* n_ground x 3, row-major, host                      */
+    int32_t filter_mode;                         /* E2SEC_FILTER_*                                     */
+    uint32_t filter_seed;                        /* base seed for REFERENCE_SEEDED                     */
+} e2sec_params;
+
+/* ---- records: phase-1 output, one per frame, all doubles (integers are exact in a double) --------
+ * record[0] frame id   record[1] flags (bit0: hand label occurs in the frame's labels (:1429),
+ *                                       bit1: filtered hand non-empty (:1475/:1551))
+ * record[2] n_entities K   record[3] frame id of the previous KEPT frame (bit0 and bit1 set) whose clouds the
+ *                                       cross table below was computed against, -1 if there is none
+ * entity e at record[4 + 16*e ..]:
+ *    +0 n_raw (valid points of the label)   +1 n_out (points of the filtered cloud, seed counted twice)
+ *    +2 seed raster index (-1: not filtered) +3 radius = np.median(pdist()) (:1524), NaN if unfiltered
+ *    +4..6 per-axis median (:1523)   +7..9 AABB min   +10..12 AABB max   +13..15 mean of the cloud
+ * pair table at record[4 + 16*K ..], (K+1) x (K+1) row-major, index K = the ground cloud:
+ *    exact minimum point-to-point distance when it is < thresh; otherwise some value >= thresh
+ *    (+inf when either cloud is empty).  Entities 0 (border) and ground_label's own index hold +inf.
+ * cross table after it, K x K row-major: [a][b] = the same distance between entity a's filtered cloud in the
+ *    previous kept frame and entity b's filtered cloud in this frame.  _process keeps o1/o2/o3 as the clouds
+ *    of the previous frame that passed :1551 until :1669-1675 re-assigns them, so the o2 / o3 search of
+ *    :1562-1658 measures exactly these cross-frame distances.                                          */
+#define E2SEC_REC_HEADER 4
+#define E2SEC_REC_ENTITY 16
+#define E2SEC_FLAG_HAND_LABEL 1
+#define E2SEC_FLAG_HAND_POINTS 2
+size_t e2sec_record_doubles(int32_t n_entities);
+
+/* ---- context ----------------------------------------------------------------------------------- */
+int e2sec_abi_version(void);
+int e2sec_create(int device, e2sec_ctx **out);
+void e2sec_destroy(e2sec_ctx *ctx);
+const char *e2sec_last_error(const e2sec_ctx *ctx);
+/* cudaStream_t the context launches on (for callers that time with CUDA events) */
+void *e2sec_stream(e2sec_ctx *ctx);
+
+/* Sets the sequence parameters and (re)allocates device buffers for batches of up to max_frames
+ * frames of n_points points.  Replaces the global reset of analyse_maniac_manipulation :2224-2250
+ * and the frame-0 branch of _process :1397-1426 (whose products arrive in `p`).                     */
+int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t max_frames, int32_t n_points);
+/* Forgets the previous kept frame (the halo the cross-frame distances are measured against): call it before
+ * the first batch of a new sequence or shard.  Frames of one sequence must then arrive in order; a shard
+ * that starts mid-sequence feeds its halo frame(s) first and drops their records.                     */
+int e2sec_reset_sequence(e2sec_ctx *ctx);
+
+/* Phase 1 of _process (:1433-1546 + the geometry behind :363-1353) for a batch of frames: label
+ * upscale/replace, NaN mask, segmentation, transform, per-entity filter, AABB / mean, all-pairs
+ * touching distances.  Stream-ordered; returns after the records are on the host unless
+ * records is NULL (then read them with e2sec_records_dev / your own copy after e2sec_sync).
+ *   xyz        n_frames x n_points x 3 float32 (PCD order, NaN = invalid), host or device
+ *   labels     n_frames x (label_w*label_h) int32, host or device; if label_w*label_h != n_points the
+ *              image is upscaled nearest-neighbour to (width x height) like cv2.resize (:1433)
+ *   frame_ids  n_frames int32 host (file index i of :2271; seeds REFERENCE_SEEDED)
+ *   on_device  non-zero: xyz and labels are device pointers                                         */
+int e2sec_process_batch(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
+                        int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                        const int32_t *frame_ids, int on_device, double *records);
+const double *e2sec_records_dev(e2sec_ctx *ctx);
+int e2sec_sync(e2sec_ctx *ctx);
+/* number of kernels launched by this context so far (bench.py's gpu_launches) */
+int64_t e2sec_launch_count(const e2sec_ctx *ctx);
+/* per-stage device time of the last batch in ms: segment, medians, radius, filter, stats, pairs     */
+int e2sec_stage_ms(e2sec_ctx *ctx, float out[8]);
+
+/* ---- operators at the reference's own seams ------------------------------------------------------ */
+/* filter_cython_new.region_filter_cython (pyx:9).  pcd: n x 3 float64 C-contiguous.  `center` is the
+ * seed target (the reference passes hand_center == obj_center, :1525).  out must hold (n+1) x 3.     */
+int e2sec_region_filter(e2sec_ctx *ctx, const double *pcd, int32_t n, const double center[3],
+                        double median_distance, int32_t mode, uint32_t seed, double *out,
+                        int32_t *n_out);
+/* filter_cython_new.distance_cython (pyx:6) -- host arithmetic, kept for API completeness.           */
+double e2sec_distance(const double p1[3], const double p2[3]);
+/* np.median(scipy.spatial.distance.pdist(pts)) (:1524), exact.                                       */
+int e2sec_pairwise_median(e2sec_ctx *ctx, const double *pts, int32_t n, double *median);
+/* np.median(pts, axis=0) (:1523), exact.                                                            */
+int e2sec_axis_median(e2sec_ctx *ctx, const double *pts, int32_t n, double median[3]);
+/* np.min(a.compute_point_cloud_distance(b)) (:397-484): exact when < limit, else a value >= limit.
+ * limit <= 0 means "always exact".                                                                   */
+int e2sec_min_distance(e2sec_ctx *ctx, const double *a, int32_t na, const double *b, int32_t nb,
+                       double limit, double *dist);
+
+/* ---- phase 2: the sequential part of _process (:1558-1675 selection, :363-1353 relation rows,
+ * :1795-1829 / :2000-2007 column emit) over records in frame order.  Host code. -------------------- */
+typedef struct e2sec_resolver e2sec_resolver;
+int e2sec_resolver_create(const e2sec_params *p, e2sec_resolver **out);
+void e2sec_resolver_destroy(e2sec_resolver *r);
+/* Feeds n_frames records (frame order).  Emitted 30-row columns accumulate inside the resolver.      */
+int e2sec_resolver_feed(e2sec_resolver *r, const double *records, int32_t n_frames);
+/* Number of eSEC columns so far (0 before the first column; the reference's '-' column is implicit). */
+int32_t e2sec_resolver_columns(const e2sec_resolver *r);
+const char *e2sec_resolver_error(const e2sec_resolver *r);
+/* Copies the raw eSEC table: codes as 30 x n_cols x 6 bytes (NUL-terminated, lower/mixed case as the
+ * reference writes them) and final_columns (n_cols).                                                 */
+int e2sec_resolver_table(const e2sec_resolver *r, char *codes, int32_t *final_columns);
+/* o1/o2/o3 entity indices (-1 while unassigned) and sticky absent flags (:389-427).                  */
+int e2sec_resolver_state(const e2sec_resolver *r, int32_t labels[3], int32_t absent[3]);
+/* esec_to_e2sec (:62-111) on a rows x n_cols table of 6-byte codes: upper-cases, drops column 0 and
+ * the H,G / 3,G rows, removes repeated columns; returns the new column count, thins final_columns.   */
+int32_t e2sec_esec_to_e2sec(const char *codes, int32_t rows, int32_t n_cols, int32_t relations,
+                            char *out_codes, int32_t *final_columns, int32_t *n_final);
+
+/* ---- input decode (host): o3d.io.read_point_cloud :1441 and pd.read_csv :1391 -------------------- */
+int e2sec_read_pcd_xyz(const char *path, float *xyz, int64_t capacity_points, int32_t *width,
+                       int32_t *height);
+int e2sec_read_labels(const char *path, int32_t *labels, int64_t capacity, int32_t *rows, int32_t *cols);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* E2SEC_H */

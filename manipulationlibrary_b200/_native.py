@@ -1,0 +1,118 @@
+"""ctypes binding of libe2sec.so (include/e2sec.h). There is no fallback: if the library is missing or
+cannot be loaded, importing this module raises."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libe2sec.so")
+
+MAX_ENTITIES = 64
+REC_HEADER = 4
+REC_ENTITY = 16
+FLAG_HAND_LABEL = 1
+FLAG_HAND_POINTS = 2
+FILTER_CLOSURE = 0
+FILTER_REFERENCE_SEEDED = 1
+FILTER_MODES = {"closure": FILTER_CLOSURE, "reference_seeded": FILTER_REFERENCE_SEEDED}
+
+
+class Params(C.Structure):
+    _fields_ = [("n_entities", C.c_int32), ("entity_label", C.c_int32 * MAX_ENTITIES),
+                ("hand_label", C.c_int32), ("ground_label", C.c_int32), ("support_hand", C.c_int32),
+                ("n_replace", C.c_int32), ("replace_old", C.c_int32 * 16), ("replace_new", C.c_int32 * 16),
+                ("thresh", C.c_double), ("translation", C.c_double * 16), ("roll", C.c_double * 16),
+                ("n_ground", C.c_int32), ("ground_xyz", C.POINTER(C.c_double)),
+                ("filter_mode", C.c_int32), ("filter_seed", C.c_uint32)]
+
+
+class E2SecError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("%s not found: build it with `python -m manipulationlibrary_b200.build` "
+                          "(this path has no CPU fallback)" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+    sig = {
+        "e2sec_abi_version": (C.c_int, []),
+        "e2sec_record_doubles": (C.c_size_t, [i32]),
+        "e2sec_create": (C.c_int, [C.c_int, C.POINTER(vp)]),
+        "e2sec_destroy": (None, [vp]),
+        "e2sec_last_error": (C.c_char_p, [vp]),
+        "e2sec_stream": (vp, [vp]),
+        "e2sec_configure": (C.c_int, [vp, C.POINTER(Params), i32, i32]),
+        "e2sec_reset_sequence": (C.c_int, [vp]),
+        "e2sec_process_batch": (C.c_int, [vp, vp, vp, i32, i32, i32, i32, i32, vp, C.c_int, vp]),
+        "e2sec_records_dev": (vp, [vp]),
+        "e2sec_sync": (C.c_int, [vp]),
+        "e2sec_launch_count": (i64, [vp]),
+        "e2sec_stage_ms": (C.c_int, [vp, vp]),
+        "e2sec_region_filter": (C.c_int, [vp, vp, i32, vp, dbl, i32, C.c_uint32, vp, vp]),
+        "e2sec_distance": (dbl, [vp, vp]),
+        "e2sec_pairwise_median": (C.c_int, [vp, vp, i32, vp]),
+        "e2sec_axis_median": (C.c_int, [vp, vp, i32, vp]),
+        "e2sec_min_distance": (C.c_int, [vp, vp, i32, vp, i32, dbl, vp]),
+        "e2sec_resolver_create": (C.c_int, [C.POINTER(Params), C.POINTER(vp)]),
+        "e2sec_resolver_destroy": (None, [vp]),
+        "e2sec_resolver_feed": (C.c_int, [vp, vp, i32]),
+        "e2sec_resolver_columns": (i32, [vp]),
+        "e2sec_resolver_error": (C.c_char_p, [vp]),
+        "e2sec_resolver_table": (C.c_int, [vp, vp, vp]),
+        "e2sec_resolver_state": (C.c_int, [vp, vp, vp]),
+        "e2sec_esec_to_e2sec": (i32, [vp, i32, i32, i32, vp, vp, vp]),
+        "e2sec_read_pcd_xyz": (C.c_int, [C.c_char_p, vp, i64, vp, vp]),
+        "e2sec_read_labels": (C.c_int, [C.c_char_p, vp, i64, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)        # AttributeError here = the library does not export what the header declares
+        fn.restype = res
+        fn.argtypes = args
+    return lib, sorted(sig)
+
+
+lib, EXPORTS = _load()
+
+
+def ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def make_params(total_unique_labels, hand_label, ground_label, support_hand, thresh, translation, roll, ground,
+                replace=False, old=(), new=(), filter_mode="closure", filter_seed=0):
+    """-> (Params, keepalive). Labels must be integer valued, as the MANIAC label images are."""
+    tul = np.asarray(total_unique_labels, np.float64)
+    if len(tul) > MAX_ENTITIES:
+        raise ValueError("more than %d entities" % MAX_ENTITIES)
+    if not np.all(tul == np.round(tul)):
+        raise ValueError("labels must be integer valued")
+    p = Params()
+    p.n_entities = len(tul)
+    for i, v in enumerate(tul):
+        p.entity_label[i] = int(v)
+    p.hand_label, p.ground_label = int(hand_label), int(ground_label)
+    p.support_hand = -1 if support_hand is None else int(support_hand)
+    old, new = list(old) if replace else [], list(new) if replace else []
+    if len(old) != len(new) or len(old) > 16:
+        raise ValueError("old/new must have equal length <= 16")
+    p.n_replace = len(old)
+    for i, (o, n) in enumerate(zip(old, new)):
+        p.replace_old[i], p.replace_new[i] = int(o), int(n)
+    p.thresh = float(thresh)
+    T = np.ascontiguousarray(translation, np.float64).reshape(16)
+    R = np.ascontiguousarray(roll, np.float64).reshape(16)
+    for i in range(16):
+        p.translation[i], p.roll[i] = T[i], R[i]
+    g = np.ascontiguousarray(ground, np.float64).reshape(-1, 3)
+    p.n_ground = len(g)
+    p.ground_xyz = g.ctypes.data_as(C.POINTER(C.c_double))
+    p.filter_mode = FILTER_MODES[filter_mode] if isinstance(filter_mode, str) else int(filter_mode)
+    p.filter_seed = int(filter_seed) & 0xFFFFFFFF
+    return p, g
+
+
+def record_doubles(K):
+    return int(lib.e2sec_record_doubles(int(K)))

@@ -1,0 +1,131 @@
+// common.cuh -- shared device structures and helpers of the e2SEC hot path (sm_100a).
+//
+// Compiled with --fmad=false: every float64 expression below is evaluated with separate IEEE
+// multiplies and adds in source order, which is what numpy / scipy / Cython do on the reference side
+// (manipulation_analyser.py and cython_filter_new/filter_cython_new.pyx). Fused operations are
+// requested explicitly (fma / fmaf) where a kernel wants them.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/e2sec.h"
+
+#define E2_SEG 1024          // points per warp segment in the segmentation kernels
+#define E2_SEG_WARPS 8       // warps per CTA there
+#define E2_TILE 256          // points per tile in the pair-distance kernels
+#define E2_NBINS 256         // bins per refinement pass of the radius selection
+#define E2_CAND_CAP 32768    // candidate keys kept for the final exact selection
+
+typedef unsigned long long u64;
+
+// Per-(frame, entity) state of the radius selection (np.median(pdist()), manipulation_analyser.py:1524).
+struct RadiusState {
+    u64 klo;        // interval [klo, klo + width) in key space (key = bit pattern of the float64 d^2)
+    u64 width;
+    u64 below;      // exact number of pairs with key < klo
+    u64 k1, k2;     // 0-based ranks of the two middle pair distances (equal when the pair count is odd)
+    int shift;      // bin = (key - klo) >> shift
+    int phase;      // 0 = refine (histogram pass), 1 = collect, 2 = done, 3 = inactive (not filtered)
+    int n;          // points of the entity
+    int pad;
+};
+
+// Device view of one context. Entity-level arrays are indexed fe = frame * K + e.
+struct Dev {
+    int F, N, K, cap;                 // frames in this batch, points per frame, entities, stored-point capacity
+    int maxF;                         // frame slot maxF of every per-frame buffer is the HALO: a copy of the last kept
+                                      // frame of the previous batches (its clouds feed the cross-frame distances)
+    int S;                            // segments per frame = ceil(N / E2_SEG)
+    int hand_idx, ground_idx;
+    int hand_label;
+    int n_ground;
+    int filter_mode;
+    unsigned filter_seed;
+    double thresh;
+    double T[16], R[16];
+    // inputs
+    const float *xyz;                 // F x N x 3
+    const int *labels;                // F x label_size
+    int label_size;                   // label_w * label_h
+    const int *rowmap, *colmap;       // nearest-neighbour source row / column per destination row / column (or null)
+    int width, label_w;
+    const int *lut;                   // raw label -> entity index, -1 untracked
+    const int *frame_ids;             // F
+    // segmentation
+    unsigned *seg_cnt;                // F x S x K   valid points of entity e in segment s (becomes offsets)
+    int *ent_raw;                     // F x K       valid points per entity
+    int *ent_off;                     // F x K       offset of the entity's points in the frame's storage (-1: not stored)
+    int *flags;                       // F           E2SEC_FLAG_*
+    int *frame_used;                  // F+1         stored points of the frame
+    int *prev_slot;                   // F           frame slot of the previous kept frame (maxF = halo, -1 = none)
+    int *prev_id;                     // F           its frame id (-1 = none)
+    int *halo_info;                   // [0] valid, [1] frame id, [2] slot of the last kept frame of this batch (-1 none)
+    double *px, *py, *pz;             // F x cap     transformed points, grouped by entity, raster order inside
+    unsigned *pidx;                   // F x cap     raster index of each stored point
+    // filter inputs
+    double *med;                      // F x K x 3   per-axis median
+    double *radius;                   // F x K       median pairwise distance
+    RadiusState *rs;                  // F x K
+    u64 *hist;                        // F x K x E2_NBINS
+    u64 *cand;                        // F x K x E2_CAND_CAP
+    unsigned *cand_n;                 // F x K
+    // filter outputs
+    int *seed_pos;                    // F x K       position of the seed inside the entity (-1: unfiltered)
+    unsigned char *member;            // F x cap     closure membership
+    unsigned *front_a, *front_b;      // F x cap     frontier lists (positions inside the entity)
+    unsigned *flist;                  // F x cap     filtered cloud as positions, output order (seed duplicate excluded)
+    int *n_list;                      // F x K       entries of flist
+    // stats + pairs
+    double *aabb;                     // F x K x 6
+    double *mean;                     // F x K x 3
+    const double *gx, *gy, *gz;       // ground cloud
+    double gaabb[6];
+    u64 *pair_key;                    // F x (K+1) x (K+1)   min d^2 key per in-frame pair
+    u64 *cross_key;                   // F x K x K           min d^2 key, entity a of the previous kept frame vs b of this one
+    double *records;                  // F x rec_doubles
+    int rec_doubles;
+    int *error;                       // device error flag
+};
+
+__device__ __forceinline__ u64 d2key(double v) { return (u64)__double_as_longlong(v); }
+__device__ __forceinline__ double key2d(u64 k) { return __longlong_as_double((long long)k); }
+
+// sqrt((dx*dx + dy*dy) + dz*dz) squared part, in the operation order of scipy's pdist / distance_cython
+__device__ __forceinline__ double dist2(double ax, double ay, double az, double bx, double by, double bz)
+{
+    double dx = ax - bx, dy = ay - by, dz = az - bz;
+    return (dx * dx + dy * dy) + dz * dz;
+}
+
+// total order key of a float64 for radix selection
+__device__ __forceinline__ u64 f64_sortkey(double v)
+{
+    u64 b = (u64)__double_as_longlong(v);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double f64_from_sortkey(u64 k)
+{
+    u64 b = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+    return __longlong_as_double((long long)b);
+}
+
+__device__ __forceinline__ double warp_min_d(double v)
+{
+    for (int o = 16; o; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_max_d(double v)
+{
+    for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ u64 warp_sum_u64(u64 v)
+{
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ u64 warp_min_u64(u64 v)
+{
+    for (int o = 16; o; o >>= 1) { u64 w = __shfl_xor_sync(0xffffffffu, v, o); v = w < v ? w : v; }
+    return v;
+}

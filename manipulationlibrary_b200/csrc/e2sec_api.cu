@@ -1,0 +1,659 @@
+// e2sec_api.cu -- context, buffers and the C ABI of include/e2sec.h (device side).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -lineinfo (see build.py).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "seg.cuh"
+#include "select.cuh"
+#include "radius.cuh"
+#include "filter.cuh"
+#include "pairs.cuh"
+
+#define E2_MAX_REFINE 6        // histogram rounds launched per batch (each narrows the key interval 256x)
+
+static std::string g_create_error;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+};
+
+struct e2sec_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    e2sec_params params;
+    std::vector<double> ground;
+    bool configured = false;
+    int maxF = 0, N = 0, K = 0;
+    size_t cap_total = 0;          // stored-point capacity over the whole batch (maxF * N)
+    Dev d;
+    std::vector<DevBuf *> bufs;
+    DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
+        pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
+        gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
+        frame_used, prev_slot, prev_id, halo_info;
+    int map_cfg[4] = {0, 0, 0, 0};
+    int64_t launches = 0;
+    cudaEvent_t ev[8];
+    bool ev_valid = false;
+    int sm_count = 148;
+};
+
+#define CU(call)                                                                         \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);               \
+            return E2SEC_ERR_CUDA;                                                       \
+        }                                                                                \
+    } while (0)
+
+static int fail(e2sec_ctx *ctx, int code, const std::string &msg)
+{
+    if (ctx) ctx->err = msg; else g_create_error = msg;
+    return code;
+}
+
+static int ensure(e2sec_ctx *ctx, DevBuf &b, size_t bytes)
+{
+    if (b.bytes >= bytes && b.p) return 0;
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.bytes = 0;
+    CU(cudaMalloc(&b.p, bytes ? bytes : 16));
+    b.bytes = bytes ? bytes : 16;
+    return 0;
+}
+
+extern "C" int e2sec_abi_version(void) { return E2SEC_ABI_VERSION; }
+
+extern "C" size_t e2sec_record_doubles(int32_t K)
+{
+    return (size_t)E2SEC_REC_HEADER + (size_t)E2SEC_REC_ENTITY * K + (size_t)(K + 1) * (K + 1) + (size_t)K * K;
+}
+
+extern "C" const char *e2sec_last_error(const e2sec_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+extern "C" int e2sec_create(int device, e2sec_ctx **out)
+{
+    if (!out) return fail(nullptr, E2SEC_ERR_ARG, "e2sec_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, E2SEC_ERR_CUDA, std::string("e2sec_create: no CUDA device (") + cudaGetErrorString(e) +
+                                                 "); this path has no CPU fallback");
+    if (device < 0 || device >= count) return fail(nullptr, E2SEC_ERR_ARG, "e2sec_create: bad device index");
+    e2sec_ctx *ctx = new e2sec_ctx();
+    ctx->device = device;
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        return fail(nullptr, E2SEC_ERR_CUDA, "e2sec_create: cannot create a stream");
+    }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    ctx->ev_valid = true;
+    cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)(sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double)));
+    memset(&ctx->d, 0, sizeof(Dev));
+    ctx->bufs = {&ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
+                 &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
+                 &ctx->radius, &ctx->rs, &ctx->hist, &ctx->cand, &ctx->cand_n, &ctx->seed_pos, &ctx->member,
+                 &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
+                 &ctx->gz, &ctx->pair_key, &ctx->records, &ctx->error, &ctx->plan_off, &ctx->plan_total,
+                 &ctx->below_acc, &ctx->min_above, &ctx->single_count, &ctx->cross_key, &ctx->frame_used, &ctx->prev_slot,
+                 &ctx->prev_id, &ctx->halo_info};
+    *out = ctx;
+    return E2SEC_OK;
+}
+
+extern "C" void e2sec_destroy(e2sec_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (DevBuf *b : ctx->bufs)
+        if (b->p) cudaFree(b->p);
+    if (ctx->ev_valid)
+        for (auto &ev : ctx->ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" void *e2sec_stream(e2sec_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+extern "C" int64_t e2sec_launch_count(const e2sec_ctx *ctx) { return ctx ? ctx->launches : 0; }
+extern "C" const double *e2sec_records_dev(e2sec_ctx *ctx) { return ctx ? (const double *)ctx->records.p : nullptr; }
+
+extern "C" int e2sec_sync(e2sec_ctx *ctx)
+{
+    if (!ctx) return E2SEC_ERR_ARG;
+    CU(cudaStreamSynchronize(ctx->stream));
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_reset_sequence(e2sec_ctx *ctx)
+{
+    if (!ctx) return E2SEC_ERR_ARG;
+    if (!ctx->halo_info.p) return E2SEC_OK;
+    CU(cudaMemsetAsync(ctx->halo_info.p, 0, 4 * sizeof(int), ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return E2SEC_OK;
+}
+
+// Allocates every work buffer for F frames x N points x K entities and points ctx->d at them.
+static int allocate(e2sec_ctx *ctx, int F, int N, int K)
+{
+    const size_t cap = (size_t)(F + 1) * N;      // + the halo slot
+    const int S = (N + E2_SEG - 1) / E2_SEG;
+    const size_t FK = (size_t)(F + 1) * K;
+    int rc = 0;
+    rc |= ensure(ctx, ctx->xyz_stage, (size_t)F * N * 3 * sizeof(float));
+    rc |= ensure(ctx, ctx->lab_stage, (size_t)F * N * sizeof(int));
+    rc |= ensure(ctx, ctx->cross_key, (size_t)F * K * K * sizeof(u64));
+    rc |= ensure(ctx, ctx->frame_used, (size_t)(F + 1) * sizeof(int));
+    rc |= ensure(ctx, ctx->prev_slot, (size_t)F * sizeof(int));
+    rc |= ensure(ctx, ctx->prev_id, (size_t)F * sizeof(int));
+    rc |= ensure(ctx, ctx->halo_info, 4 * sizeof(int));
+    rc |= ensure(ctx, ctx->lut, E2SEC_LABEL_LUT * sizeof(int));
+    rc |= ensure(ctx, ctx->frame_ids, F * sizeof(int));
+    rc |= ensure(ctx, ctx->seg_cnt, (size_t)F * S * K * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->ent_raw, FK * sizeof(int));
+    rc |= ensure(ctx, ctx->ent_off, FK * sizeof(int));
+    rc |= ensure(ctx, ctx->flags, F * sizeof(int));
+    rc |= ensure(ctx, ctx->px, cap * sizeof(double));
+    rc |= ensure(ctx, ctx->py, cap * sizeof(double));
+    rc |= ensure(ctx, ctx->pz, cap * sizeof(double));
+    rc |= ensure(ctx, ctx->pidx, cap * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->med, FK * 3 * sizeof(double));
+    rc |= ensure(ctx, ctx->radius, FK * sizeof(double));
+    rc |= ensure(ctx, ctx->rs, FK * sizeof(RadiusState));
+    rc |= ensure(ctx, ctx->hist, FK * E2_NBINS * sizeof(u64));
+    rc |= ensure(ctx, ctx->cand, FK * E2_CAND_CAP * sizeof(u64));
+    rc |= ensure(ctx, ctx->cand_n, FK * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->seed_pos, FK * sizeof(int));
+    rc |= ensure(ctx, ctx->member, cap);
+    rc |= ensure(ctx, ctx->front_a, cap * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->front_b, cap * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->flist, cap * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->n_list, FK * sizeof(int));
+    rc |= ensure(ctx, ctx->aabb, FK * 6 * sizeof(double));
+    rc |= ensure(ctx, ctx->mean, FK * 3 * sizeof(double));
+    rc |= ensure(ctx, ctx->pair_key, (size_t)F * (K + 1) * (K + 1) * sizeof(u64));
+    rc |= ensure(ctx, ctx->records, (size_t)F * e2sec_record_doubles(K) * sizeof(double));
+    rc |= ensure(ctx, ctx->error, sizeof(int));
+    rc |= ensure(ctx, ctx->plan_off, (FK + 1) * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->plan_total, sizeof(unsigned));
+    rc |= ensure(ctx, ctx->below_acc, FK * sizeof(u64));
+    rc |= ensure(ctx, ctx->min_above, FK * sizeof(u64));
+    rc |= ensure(ctx, ctx->single_count, FK * sizeof(u64));
+    if (rc) return E2SEC_ERR_CUDA;
+    ctx->maxF = F;
+    ctx->N = N;
+    ctx->K = K;
+    ctx->cap_total = ctx->px.bytes / sizeof(double);
+    Dev &d = ctx->d;
+    d.maxF = F;
+    d.cross_key = (u64 *)ctx->cross_key.p;
+    d.frame_used = (int *)ctx->frame_used.p;
+    d.prev_slot = (int *)ctx->prev_slot.p;
+    d.prev_id = (int *)ctx->prev_id.p;
+    d.halo_info = (int *)ctx->halo_info.p;
+    d.lut = (const int *)ctx->lut.p;
+    d.frame_ids = (const int *)ctx->frame_ids.p;
+    d.seg_cnt = (unsigned *)ctx->seg_cnt.p;
+    d.ent_raw = (int *)ctx->ent_raw.p;
+    d.ent_off = (int *)ctx->ent_off.p;
+    d.flags = (int *)ctx->flags.p;
+    d.px = (double *)ctx->px.p;
+    d.py = (double *)ctx->py.p;
+    d.pz = (double *)ctx->pz.p;
+    d.pidx = (unsigned *)ctx->pidx.p;
+    d.med = (double *)ctx->med.p;
+    d.radius = (double *)ctx->radius.p;
+    d.rs = (RadiusState *)ctx->rs.p;
+    d.hist = (u64 *)ctx->hist.p;
+    d.cand = (u64 *)ctx->cand.p;
+    d.cand_n = (unsigned *)ctx->cand_n.p;
+    d.seed_pos = (int *)ctx->seed_pos.p;
+    d.member = (unsigned char *)ctx->member.p;
+    d.front_a = (unsigned *)ctx->front_a.p;
+    d.front_b = (unsigned *)ctx->front_b.p;
+    d.flist = (unsigned *)ctx->flist.p;
+    d.n_list = (int *)ctx->n_list.p;
+    d.aabb = (double *)ctx->aabb.p;
+    d.mean = (double *)ctx->mean.p;
+    d.pair_key = (u64 *)ctx->pair_key.p;
+    d.records = (double *)ctx->records.p;
+    d.error = (int *)ctx->error.p;
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t max_frames, int32_t n_points)
+{
+    if (!ctx || !p) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    if (p->n_entities < 2 || p->n_entities > E2SEC_MAX_ENTITIES) return fail(ctx, E2SEC_ERR_ARG, "n_entities out of range");
+    if (max_frames < 1 || n_points < 1) return fail(ctx, E2SEC_ERR_ARG, "max_frames / n_points must be positive");
+    if (p->n_replace < 0 || p->n_replace > 16) return fail(ctx, E2SEC_ERR_ARG, "n_replace out of range");
+    int hand_idx = -1, ground_idx = -1;
+    for (int e = 0; e < p->n_entities; ++e) {
+        if (p->entity_label[e] == p->hand_label) hand_idx = e;
+        if (p->entity_label[e] == p->ground_label) ground_idx = e;
+    }
+    // the reference raises IndexError at :1520 / :1406-1426 when either label is missing
+    if (hand_idx < 0) return fail(ctx, E2SEC_ERR_ARG, "hand_label is not in total_unique_labels");
+    if (ground_idx < 0) return fail(ctx, E2SEC_ERR_ARG, "ground_label is not in total_unique_labels");
+    if (p->n_ground < 0 || (p->n_ground > 0 && !p->ground_xyz)) return fail(ctx, E2SEC_ERR_ARG, "ground cloud missing");
+    int rc = allocate(ctx, max_frames, n_points, p->n_entities);
+    if (rc) return rc;
+    ctx->params = *p;
+    ctx->ground.assign(p->ground_xyz, p->ground_xyz + (size_t)3 * p->n_ground);
+    ctx->params.ground_xyz = ctx->ground.data();
+    // label LUT: sequential replacement (:176-198) composed with the lookup in total_unique_labels (:1456-1472)
+    std::vector<int> lut(E2SEC_LABEL_LUT);
+    for (int raw = 0; raw < E2SEC_LABEL_LUT; ++raw) {
+        int v = raw;
+        for (int i = 0; i < p->n_replace; ++i)
+            if (v == p->replace_old[i]) v = p->replace_new[i];
+        int idx = -1;
+        for (int e = 0; e < p->n_entities; ++e)
+            if (p->entity_label[e] == v) { idx = e; break; }
+        lut[raw] = idx;
+    }
+    CU(cudaMemcpyAsync(ctx->lut.p, lut.data(), lut.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    // ground cloud as SoA + its AABB
+    const int G = p->n_ground;
+    std::vector<double> soa((size_t)3 * (G ? G : 1));
+    double box[6] = {0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < G; ++i)
+        for (int a = 0; a < 3; ++a) {
+            double v = p->ground_xyz[3 * (size_t)i + a];
+            soa[(size_t)a * G + i] = v;
+            if (i == 0 || v < box[a]) box[a] = v;
+            if (i == 0 || v > box[3 + a]) box[3 + a] = v;
+        }
+    if (ensure(ctx, ctx->gx, sizeof(double) * (G ? G : 1)) || ensure(ctx, ctx->gy, sizeof(double) * (G ? G : 1)) ||
+        ensure(ctx, ctx->gz, sizeof(double) * (G ? G : 1)))
+        return E2SEC_ERR_CUDA;
+    if (G) {
+        CU(cudaMemcpyAsync(ctx->gx.p, soa.data(), sizeof(double) * G, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->gy.p, soa.data() + G, sizeof(double) * G, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->gz.p, soa.data() + 2 * (size_t)G, sizeof(double) * G, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    CU(cudaStreamSynchronize(ctx->stream));
+    Dev &d = ctx->d;
+    d.K = p->n_entities;
+    d.N = n_points;
+    d.hand_idx = hand_idx;
+    d.ground_idx = ground_idx;
+    d.hand_label = p->hand_label;
+    d.n_ground = G;
+    d.filter_mode = p->filter_mode;
+    d.filter_seed = p->filter_seed;
+    d.thresh = p->thresh;
+    memcpy(d.T, p->translation, sizeof(d.T));
+    memcpy(d.R, p->roll, sizeof(d.R));
+    d.gx = (const double *)ctx->gx.p;
+    d.gy = (const double *)ctx->gy.p;
+    d.gz = (const double *)ctx->gz.p;
+    memcpy(d.gaabb, box, sizeof(box));
+    d.rec_doubles = (int)e2sec_record_doubles(d.K);
+    ctx->configured = true;
+    return e2sec_reset_sequence(ctx);
+}
+
+// cv2.resize(..., INTER_NEAREST) source index tables (:1433)
+static int upload_maps(e2sec_ctx *ctx, int lw, int lh, int width, int height)
+{
+    if (ctx->map_cfg[0] == lw && ctx->map_cfg[1] == lh && ctx->map_cfg[2] == width && ctx->map_cfg[3] == height) return 0;
+    std::vector<int> rows(height), cols(width);
+    const double ifx = 1.0 / ((double)width / (double)lw), ify = 1.0 / ((double)height / (double)lh);
+    for (int x = 0; x < width; ++x) { int s = (int)std::floor(x * ifx); cols[x] = s < lw - 1 ? s : lw - 1; }
+    for (int y = 0; y < height; ++y) { int s = (int)std::floor(y * ify); rows[y] = s < lh - 1 ? s : lh - 1; }
+    if (ensure(ctx, ctx->rowmap, height * sizeof(int)) || ensure(ctx, ctx->colmap, width * sizeof(int))) return E2SEC_ERR_CUDA;
+    CU(cudaMemcpyAsync(ctx->rowmap.p, rows.data(), height * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->colmap.p, cols.data(), width * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->map_cfg[0] = lw; ctx->map_cfg[1] = lh; ctx->map_cfg[2] = width; ctx->map_cfg[3] = height;
+    return 0;
+}
+
+#define LAUNCHED() do { ++ctx->launches; } while (0)
+
+// Everything after segmentation: medians, radius, filter, stats, pairs, records. `d` already describes the batch.
+static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, bool need_radius, bool do_pairs, bool do_records)
+{
+    cudaStream_t st = ctx->stream;
+    const int FK = d.F * d.K;
+    PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p};
+    u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
+    if (need_median) { axis_median_kernel<<<dim3(3, FK), E2_SEL_THREADS, 0, st>>>(d); LAUNCHED(); }
+    cudaEventRecord(ctx->ev[2], st);
+    if (need_radius) {
+        CU(cudaMemsetAsync(below_acc, 0, sizeof(u64) * FK, st));
+        CU(cudaMemsetAsync(single, 0, sizeof(u64) * FK, st));
+        radius_init_kernel<<<FK, 256, 0, st>>>(d, min_above); LAUNCHED();
+        const int grid = ctx->sm_count * 3;
+        const size_t smem = sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double);
+        for (int round = 0; round < E2_MAX_REFINE; ++round) {
+            radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 0); LAUNCHED();
+            pair_pass_kernel<false><<<grid, E2_PAIR_THREADS, smem, st>>>(d, plan, below_acc, min_above); LAUNCHED();
+            radius_select_kernel<<<(FK + 127) / 128, 128, 0, st>>>(d, below_acc, single); LAUNCHED();
+        }
+        radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 1); LAUNCHED();
+        pair_pass_kernel<true><<<ctx->sm_count * 8, E2_PAIR_THREADS, 3 * E2_TILE * sizeof(double), st>>>(d, plan, below_acc, min_above); LAUNCHED();
+        radius_final_kernel<<<FK, E2_SEL_THREADS, 0, st>>>(d, min_above, single); LAUNCHED();
+    }
+    cudaEventRecord(ctx->ev[3], st);
+    region_filter_kernel<<<FK, E2_FILTER_THREADS, 0, st>>>(d); LAUNCHED();
+    cudaEventRecord(ctx->ev[4], st);
+    entity_stats_kernel<<<FK, E2_STATS_THREADS, 0, st>>>(d); LAUNCHED();
+    cudaEventRecord(ctx->ev[5], st);
+    if (do_pairs) {
+        prev_kept_kernel<<<1, 32, 0, st>>>(d); LAUNCHED();
+        pair_distance_kernel<<<dim3(d.K * (d.K - 1) / 2 + d.K + d.K * d.K, d.F), E2_PD_THREADS, 0, st>>>(d); LAUNCHED();
+        halo_save_kernel<<<64, 256, 0, st>>>(d); LAUNCHED();
+        halo_commit_kernel<<<1, 1, 0, st>>>(d); LAUNCHED();
+    }
+    cudaEventRecord(ctx->ev[6], st);
+    if (do_records) { assemble_kernel<<<d.F, 128, 0, st>>>(d); LAUNCHED(); }
+    cudaEventRecord(ctx->ev[7], st);
+    CU(cudaGetLastError());
+    return E2SEC_OK;
+}
+
+static int check_device_error(e2sec_ctx *ctx)
+{
+    int err = 0;
+    CU(cudaMemcpyAsync(&err, ctx->error.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (err == E2SEC_ERR_CAPACITY) return fail(ctx, err, "stored points exceed the frame capacity");
+    if (err == E2SEC_ERR_STATE) return fail(ctx, err, "radius selection lost its rank (internal error)");
+    if (err) return fail(ctx, err, "device-side error");
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_process_batch(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
+                                   int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                                   const int32_t *frame_ids, int on_device, double *records)
+{
+    if (!ctx) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    if (!ctx->configured) return fail(ctx, E2SEC_ERR_STATE, "e2sec_configure has not been called");
+    if (!xyz || !labels || !frame_ids) return fail(ctx, E2SEC_ERR_ARG, "null input");
+    if (n_frames < 0 || n_frames > ctx->maxF) return fail(ctx, E2SEC_ERR_CAPACITY, "n_frames exceeds max_frames");
+    if (n_frames == 0) return E2SEC_OK;
+    const int N = ctx->N;
+    const long long lsz = (long long)label_w * label_h;
+    const bool upscale = (lsz != N);
+    if (lsz <= 0 || lsz > N) return fail(ctx, E2SEC_ERR_ARG, "label image must be non-empty and not larger than the cloud");
+    if (upscale) {
+        if ((long long)width * height != N || label_w > width || label_h > height)
+            return fail(ctx, E2SEC_ERR_ARG, "label upscaling needs width*height == n_points and label dims <= cloud dims");
+        if (upload_maps(ctx, label_w, label_h, width, height)) return E2SEC_ERR_CUDA;
+    }
+    cudaStream_t st = ctx->stream;
+    Dev d = ctx->d;
+    d.F = n_frames;
+    d.cap = N;
+    d.S = (N + E2_SEG - 1) / E2_SEG;
+    d.label_size = (int)lsz;
+    d.rowmap = upscale ? (const int *)ctx->rowmap.p : nullptr;
+    d.colmap = upscale ? (const int *)ctx->colmap.p : nullptr;
+    d.width = upscale ? width : N;
+    d.label_w = label_w;
+    cudaEventRecord(ctx->ev[0], st);
+    if (on_device) {
+        d.xyz = xyz;
+        d.labels = labels;
+    } else {
+        CU(cudaMemcpyAsync(ctx->xyz_stage.p, xyz, (size_t)n_frames * N * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->lab_stage.p, labels, (size_t)n_frames * lsz * sizeof(int), cudaMemcpyHostToDevice, st));
+        d.xyz = (const float *)ctx->xyz_stage.p;
+        d.labels = (const int *)ctx->lab_stage.p;
+    }
+    CU(cudaMemcpyAsync(ctx->frame_ids.p, frame_ids, n_frames * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(ctx->flags.p, 0, n_frames * sizeof(int), st));
+    CU(cudaMemsetAsync(ctx->error.p, 0, sizeof(int), st));
+    const dim3 sgrid((d.S + E2_SEG_WARPS - 1) / E2_SEG_WARPS, n_frames);
+    seg_count_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
+    seg_scan_kernel<<<n_frames, E2SEC_MAX_ENTITIES, 0, st>>>(d); LAUNCHED();
+    seg_scatter_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
+    cudaEventRecord(ctx->ev[1], st);
+    int rc = run_entity_stages(ctx, d, true, true, true, true);
+    if (rc) return rc;
+    if (records)
+        CU(cudaMemcpyAsync(records, ctx->records.p, (size_t)n_frames * d.rec_doubles * sizeof(double), cudaMemcpyDeviceToHost, st));
+    return check_device_error(ctx);
+}
+
+extern "C" int e2sec_stage_ms(e2sec_ctx *ctx, float out[8])
+{
+    if (!ctx || !out) return E2SEC_ERR_ARG;
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < 8; ++i) out[i] = 0.f;
+    for (int i = 0; i < 7; ++i)
+        if (cudaEventElapsedTime(&out[i], ctx->ev[i], ctx->ev[i + 1]) != cudaSuccess) out[i] = -1.f;
+    cudaGetLastError();
+    return E2SEC_OK;
+}
+
+// ---- operators -----------------------------------------------------------------------------------
+// A scratch "batch" of one frame holding `ne` clouds as entities 1..ne (entity 0 stays empty).
+static int load_clouds(e2sec_ctx *ctx, Dev &d, int ne, const double *const *pts, const int *ns)
+{
+    size_t total = 0;
+    for (int i = 0; i < ne; ++i) total += (size_t)ns[i];
+    const int K = ne + 1;
+    if (total > 0x3fffffff) return fail(ctx, E2SEC_ERR_CAPACITY, "cloud too large");
+    if (!ctx->cap_total || total > ctx->cap_total || K > ctx->K) {
+        // grow the scratch without disturbing a configured sequence's shape
+        const int keepF = ctx->maxF, keepN = ctx->N, keepK = ctx->K;
+        size_t want = total > 65536 ? total : 65536;
+        int rc = allocate(ctx, 1, (int)want, K > keepK ? K : keepK);
+        if (rc) return rc;
+        if (ctx->configured) {
+            rc = allocate(ctx, keepF, keepN, K > keepK ? K : keepK);
+            if (rc) return rc;
+            ctx->K = keepK;
+        }
+    }
+    if (ctx->halo_info.p) CU(cudaMemsetAsync(ctx->halo_info.p, 0, 4 * sizeof(int), ctx->stream));   // the scratch overwrites the halo
+    d = ctx->d;
+    d.F = 1;
+    d.K = K;
+    d.cap = (int)ctx->cap_total;
+    d.N = d.cap;
+    d.S = 0;
+    d.hand_idx = 1;
+    d.ground_idx = -1;
+    d.n_ground = 0;
+    d.rec_doubles = (int)e2sec_record_doubles(K);
+    std::vector<int> raw(K, 0), off(K, -1);
+    std::vector<double> soa;
+    size_t o = 0;
+    for (int i = 0; i < ne; ++i) {
+        const int n = ns[i];
+        raw[i + 1] = n;
+        off[i + 1] = (int)o;
+        soa.resize((size_t)3 * n);
+        for (int j = 0; j < n; ++j)
+            for (int a = 0; a < 3; ++a) soa[(size_t)a * n + j] = pts[i][3 * (size_t)j + a];
+        if (n) {
+            CU(cudaMemcpyAsync(d.px + o, soa.data(), sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+            CU(cudaMemcpyAsync(d.py + o, soa.data() + n, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+            CU(cudaMemcpyAsync(d.pz + o, soa.data() + 2 * (size_t)n, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+        }
+        o += n;
+    }
+    int zero = 0;
+    CU(cudaMemcpyAsync(d.ent_raw, raw.data(), K * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d.ent_off, off.data(), K * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync((void *)d.frame_ids, &zero, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemsetAsync(d.error, 0, sizeof(int), ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return E2SEC_OK;
+}
+
+extern "C" double e2sec_distance(const double p1[3], const double p2[3])
+{
+    const double dx = p1[0] - p2[0], dy = p1[1] - p2[1], dz = p1[2] - p2[2];
+    return std::sqrt((dx * dx + dy * dy) + dz * dz);
+}
+
+extern "C" int e2sec_axis_median(e2sec_ctx *ctx, const double *pts, int32_t n, double median[3])
+{
+    if (!ctx || !pts || !median || n < 1) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    Dev d;
+    const double *pp[1] = {pts};
+    int nn[1] = {n};
+    // the kernel skips clouds of <= 3 points (the reference never filters them): pad the call by repetition
+    std::vector<double> rep;
+    if (n <= 3) {
+        // np.median of 1..3 values on the host (trivial, not a data path)
+        for (int a = 0; a < 3; ++a) {
+            double v[3];
+            for (int i = 0; i < n; ++i) v[i] = pts[3 * i + a];
+            for (int i = 0; i < n; ++i)
+                for (int j = i + 1; j < n; ++j)
+                    if (v[j] < v[i]) { double t = v[i]; v[i] = v[j]; v[j] = t; }
+            median[a] = (n & 1) ? v[n / 2] : (v[n / 2 - 1] + v[n / 2]) / 2.0;
+        }
+        return E2SEC_OK;
+    }
+    int rc = load_clouds(ctx, d, 1, pp, nn);
+    if (rc) return rc;
+    axis_median_kernel<<<dim3(3, d.K), E2_SEL_THREADS, 0, ctx->stream>>>(d); LAUNCHED();
+    CU(cudaMemcpyAsync(median, d.med + 3, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return E2SEC_OK;
+}
+
+static int run_radius_only(e2sec_ctx *ctx, const Dev &d)
+{
+    cudaStream_t st = ctx->stream;
+    const int FK = d.F * d.K;
+    PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p};
+    u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
+    CU(cudaMemsetAsync(below_acc, 0, sizeof(u64) * FK, st));
+    CU(cudaMemsetAsync(single, 0, sizeof(u64) * FK, st));
+    radius_init_kernel<<<FK, 256, 0, st>>>(d, min_above); LAUNCHED();
+    const size_t smem = sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double);
+    for (int round = 0; round < 12; ++round) {     // an operator call may take as many rounds as it needs
+        radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 0); LAUNCHED();
+        unsigned total = 0;
+        CU(cudaMemcpyAsync(&total, plan.total, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (!total) break;
+        pair_pass_kernel<false><<<ctx->sm_count * 3, E2_PAIR_THREADS, smem, st>>>(d, plan, below_acc, min_above); LAUNCHED();
+        radius_select_kernel<<<(FK + 127) / 128, 128, 0, st>>>(d, below_acc, single); LAUNCHED();
+    }
+    radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 1); LAUNCHED();
+    pair_pass_kernel<true><<<ctx->sm_count * 8, E2_PAIR_THREADS, 3 * E2_TILE * sizeof(double), st>>>(d, plan, below_acc, min_above); LAUNCHED();
+    radius_final_kernel<<<FK, E2_SEL_THREADS, 0, st>>>(d, min_above, single); LAUNCHED();
+    CU(cudaGetLastError());
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_pairwise_median(e2sec_ctx *ctx, const double *pts, int32_t n, double *median)
+{
+    if (!ctx || !pts || !median || n < 2) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    if (n <= 3) {       // 1 or 3 pairs: host arithmetic in pdist's expression order
+        double v[3];
+        int m = 0;
+        for (int i = 0; i < n; ++i)
+            for (int j = i + 1; j < n; ++j) v[m++] = e2sec_distance(pts + 3 * i, pts + 3 * j);
+        for (int i = 0; i < m; ++i)
+            for (int j = i + 1; j < m; ++j)
+                if (v[j] < v[i]) { double t = v[i]; v[i] = v[j]; v[j] = t; }
+        *median = (m & 1) ? v[m / 2] : (v[m / 2 - 1] + v[m / 2]) / 2.0;
+        return E2SEC_OK;
+    }
+    Dev d;
+    const double *pp[1] = {pts};
+    int nn[1] = {n};
+    int rc = load_clouds(ctx, d, 1, pp, nn);
+    if (rc) return rc;
+    rc = run_radius_only(ctx, d);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(median, d.radius + 1, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    return check_device_error(ctx);
+}
+
+extern "C" int e2sec_region_filter(e2sec_ctx *ctx, const double *pcd, int32_t n, const double center[3],
+                                   double median_distance, int32_t mode, uint32_t seed, double *out, int32_t *n_out)
+{
+    if (!ctx || !pcd || !center || !out || !n_out || n < 1) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    if (n == 2) {       // pyx:35-42: a two-point cloud returns np.zeros((1, 3))
+        out[0] = out[1] = out[2] = 0.0;
+        *n_out = 1;
+        return E2SEC_OK;
+    }
+    Dev d;
+    const double *pp[1] = {pcd};
+    // the kernel's n <= 3 shortcut belongs to _process (:1520), not to the operator: pad tiny clouds by running them
+    // through the same code with the guard satisfied is impossible, so clouds of 1 or 3 points go through as 4+ only
+    if (n <= 3) return fail(ctx, E2SEC_ERR_ARG, "region_filter operator needs at least 4 points (the reference path never calls it with fewer, :1520)");
+    int nn[1] = {n};
+    int rc = load_clouds(ctx, d, 1, pp, nn);
+    if (rc) return rc;
+    d.filter_mode = mode;
+    d.filter_seed = seed;       // frame id 0, entity 1 -> seed + 7919; undo so that `seed` is the seed used
+    d.filter_seed = seed - 7919u;
+    CU(cudaMemcpyAsync(d.med + 3, center, 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d.radius + 1, &median_distance, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    region_filter_kernel<<<d.K, E2_FILTER_THREADS, 0, ctx->stream>>>(d); LAUNCHED();
+    int m = 0, sp = -1;
+    CU(cudaMemcpyAsync(&m, d.n_list + 1, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(&sp, d.seed_pos + 1, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    std::vector<unsigned> fl(m > 0 ? m : 1);
+    if (m) CU(cudaMemcpyAsync(fl.data(), d.flist, sizeof(unsigned) * m, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int a = 0; a < 3; ++a) out[a] = pcd[3 * (size_t)sp + a];      // dicti[0] = first_point
+    for (int i = 0; i < m; ++i)
+        for (int a = 0; a < 3; ++a) out[3 * (size_t)(i + 1) + a] = pcd[3 * (size_t)fl[i] + a];
+    *n_out = m + 1;
+    return check_device_error(ctx);
+}
+
+extern "C" int e2sec_min_distance(e2sec_ctx *ctx, const double *a, int32_t na, const double *b, int32_t nb,
+                                  double limit, double *dist)
+{
+    if (!ctx || !a || !b || !dist || na < 0 || nb < 0) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    if (na == 0 || nb == 0) { *dist = INFINITY; return E2SEC_OK; }
+    Dev d;
+    const double *pp[2] = {a, b};
+    int nn[2] = {na, nb};
+    int rc = load_clouds(ctx, d, 2, pp, nn);
+    if (rc) return rc;
+    d.thresh = (limit > 0.0) ? limit : 1e150;
+    d.filter_mode = E2SEC_FILTER_CLOSURE;
+    // both clouds pass unfiltered: flist = identity
+    std::vector<unsigned> id((size_t)(na > nb ? na : nb));
+    for (size_t i = 0; i < id.size(); ++i) id[i] = (unsigned)i;
+    int nl[3] = {0, na, nb}, sp[3] = {-1, -1, -1};
+    CU(cudaMemcpyAsync(d.flist, id.data(), sizeof(unsigned) * na, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d.flist + na, id.data(), sizeof(unsigned) * nb, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d.n_list, nl, sizeof(nl), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d.seed_pos, sp, sizeof(sp), cudaMemcpyHostToDevice, ctx->stream));
+    entity_stats_kernel<<<d.K, E2_STATS_THREADS, 0, ctx->stream>>>(d); LAUNCHED();
+    pair_distance_kernel<<<dim3(d.K * (d.K - 1) / 2 + d.K, 1), E2_PD_THREADS, 0, ctx->stream>>>(d); LAUNCHED();   // in-frame slots only
+    u64 key = 0;
+    CU(cudaMemcpyAsync(&key, d.pair_key + (size_t)1 * (d.K + 1) + 2, sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    double d2;
+    memcpy(&d2, &key, sizeof(double));
+    *dist = std::sqrt(d2);
+    return check_device_error(ctx);
+}

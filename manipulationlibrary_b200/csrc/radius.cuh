@@ -1,0 +1,330 @@
+// radius.cuh -- exact np.median(scipy.spatial.distance.pdist(objects[i])) (manipulation_analyser.py:1524)
+// without materialising the n(n-1)/2 distances.
+//
+// Selection runs on the float64 SQUARED distance d2 = (dx*dx + dy*dy) + dz*dz (pdist's own expression
+// before its sqrt; sqrt is monotone, so the k-th smallest distance is the sqrt of the k-th smallest d2).
+// Keys are the bit patterns of d2 (non-negative doubles order like unsigned integers).
+//
+//   radius_init_kernel     per entity: pair count, the two middle ranks, an upper bound of d2 from the
+//                          AABB, first key interval [key(D2max * 2^-16), key(D2max)]
+//   radius_plan_kernel     work list: one item = one 256 x 256 tile pair (ti <= tj) of an active entity
+//   pair_hist_kernel       every pair of the item -> bin = (key - klo) >> shift, counted in thread-private
+//                          uint16 shared-memory counters [bin][thread] (no atomics in the pair loop)
+//   radius_select_kernel   picks the bin holding the lower middle rank, shrinks the interval 256x; when the
+//                          interval holds <= E2_CAND_CAP pairs switches the entity to "collect"
+//   pair_collect_kernel    appends the keys inside the interval, tracks the smallest key above it
+//   radius_final_kernel    block_select2 over the candidates -> (sqrt(a) + sqrt(b)) / 2
+#pragma once
+#include "common.cuh"
+#include "select.cuh"
+
+#define E2_PAIR_THREADS 128     // 2 i-points per thread
+#define E2_FLUSH_ITEMS 100      // uint16 counters: <= 512 increments per thread per item
+
+struct PairPlan {
+    unsigned *off;      // F*K + 1 exclusive prefix of items
+    unsigned *total;    // = off[F*K]
+};
+
+__device__ __forceinline__ int shift_for_width(u64 width)
+{
+    int s = 0;
+    while (s < 63 && ((width - 1) >> s) >= (u64)E2_NBINS) ++s;
+    return s;
+}
+
+// grid F*K CTAs of 256 threads
+__global__ void __launch_bounds__(256) radius_init_kernel(Dev d, u64 *min_above)
+{
+    __shared__ double red[6][8];
+    const int fe = blockIdx.x, f = fe / d.K;
+    const int off = d.ent_off[fe], n = d.ent_raw[fe];
+    RadiusState &rs = d.rs[fe];
+    if (threadIdx.x == 0) {
+        d.radius[fe] = __longlong_as_double(0x7ff8000000000000ll);
+        d.cand_n[fe] = 0;
+        min_above[fe] = ~0ull;
+    }
+    for (int b = threadIdx.x; b < E2_NBINS; b += blockDim.x) d.hist[(size_t)fe * E2_NBINS + b] = 0;
+    if (off < 0 || n <= 3) {
+        if (threadIdx.x == 0) { rs.phase = 3; rs.n = n; }
+        return;
+    }
+    const double *x = d.px + (size_t)f * d.cap + off, *y = d.py + (size_t)f * d.cap + off, *z = d.pz + (size_t)f * d.cap + off;
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        lo[0] = fmin(lo[0], x[i]); hi[0] = fmax(hi[0], x[i]);
+        lo[1] = fmin(lo[1], y[i]); hi[1] = fmax(hi[1], y[i]);
+        lo[2] = fmin(lo[2], z[i]); hi[2] = fmax(hi[2], z[i]);
+    }
+    for (int a = 0; a < 3; ++a) {
+        lo[a] = warp_min_d(lo[a]);
+        hi[a] = warp_max_d(hi[a]);
+        if ((threadIdx.x & 31) == 0) { red[a][threadIdx.x >> 5] = lo[a]; red[3 + a][threadIdx.x >> 5] = hi[a]; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double ext2 = 0.0;
+        for (int a = 0; a < 3; ++a) {
+            double l = red[a][0], h = red[3 + a][0];
+            for (int w = 1; w < 8; ++w) { l = fmin(l, red[a][w]); h = fmax(h, red[3 + a][w]); }
+            ext2 += (h - l) * (h - l);
+        }
+        u64 P = (u64)n * (u64)(n - 1) / 2;
+        rs.k2 = P / 2;
+        rs.k1 = (P & 1) ? rs.k2 : rs.k2 - 1;
+        rs.n = n;
+        rs.below = 0;
+        if (!(ext2 > 0.0)) {           // every point identical: all distances are 0
+            d.radius[fe] = 0.0;
+            rs.phase = 2;
+            return;
+        }
+        double top = ext2 * 1.000001;  // d2 of any pair <= squared AABB diagonal (+ rounding slack)
+        u64 khi = d2key(top) + 1;
+        u64 klo = d2key(top * (1.0 / 65536.0));
+        rs.klo = klo;
+        rs.width = khi - klo;
+        rs.shift = shift_for_width(rs.width);
+        rs.phase = 0;
+    }
+}
+
+// single CTA: items per entity for the wanted phase, exclusive scan
+__global__ void __launch_bounds__(1024) radius_plan_kernel(Dev d, PairPlan plan, int want_phase)
+{
+    __shared__ unsigned warp_tot[32];
+    __shared__ unsigned carry;
+    const int n_fe = d.F * d.K;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n_fe; base += 1024) {
+        int fe = base + threadIdx.x;
+        unsigned items = 0;
+        if (fe < n_fe && d.rs[fe].phase == want_phase) {
+            unsigned T = (unsigned)((d.rs[fe].n + E2_TILE - 1) / E2_TILE);
+            items = T * (T + 1) / 2;
+        }
+        unsigned v = items;
+        for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, v, o); if ((threadIdx.x & 31) >= o) v += t; }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            unsigned w = warp_tot[threadIdx.x];
+            for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, w, o); if (threadIdx.x >= o) w += t; }
+            warp_tot[threadIdx.x] = w;
+        }
+        __syncthreads();
+        unsigned excl = carry + v - items + ((threadIdx.x >> 5) ? warp_tot[(threadIdx.x >> 5) - 1] : 0);
+        if (fe < n_fe) plan.off[fe] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + items;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { plan.off[n_fe] = carry; *plan.total = carry; }
+}
+
+struct PairItem { int fe, ti, tj; };
+
+// item index -> (entity, tile pair). Row ti of the upper triangle holds tiles tj = ti .. T-1.
+__device__ __forceinline__ PairItem decode_item(const Dev &d, const PairPlan &plan, unsigned item)
+{
+    int lo = 0, hi = d.F * d.K;     // last fe with off[fe] <= item
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (plan.off[mid] <= item) lo = mid; else hi = mid;
+    }
+    PairItem it;
+    it.fe = lo;
+    unsigned local = item - plan.off[lo];
+    int T = (d.rs[lo].n + E2_TILE - 1) / E2_TILE;
+    int ti = 0;
+    unsigned row = (unsigned)T;
+    while (local >= row) { local -= row; --row; ++ti; }
+    it.ti = ti;
+    it.tj = ti + (int)local;
+    return it;
+}
+
+extern __shared__ __align__(16) unsigned char pair_smem[];
+
+// Shared layout: uint16 cnt[E2_NBINS][E2_PAIR_THREADS] | double sx[256], sy[256], sz[256]
+template <bool COLLECT>
+__global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *min_above)
+{
+    unsigned short *cnt = reinterpret_cast<unsigned short *>(pair_smem);
+    double *sx = reinterpret_cast<double *>(pair_smem + (COLLECT ? 0 : sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS));
+    double *sy = sx + E2_TILE, *sz = sy + E2_TILE;
+    __shared__ PairItem cur;
+    __shared__ u64 red[E2_PAIR_THREADS / 32];
+    const int tid = threadIdx.x;
+    // counter slot of this thread inside a bin row: lanes of one warp hit 32 distinct 4-byte words (banks);
+    // threads tid and tid + 64 share a word but own different halves of it
+    const int slot = ((tid & 63) << 1) | (tid >> 6);
+    const unsigned total = *plan.total;
+    if (total == 0) return;
+    const unsigned per = (total + gridDim.x - 1) / gridDim.x;
+    const unsigned first = blockIdx.x * per;
+    const unsigned last = min(total, first + per);
+    if (first >= last) return;
+    if (!COLLECT)
+        for (int i = tid; i < E2_NBINS * E2_PAIR_THREADS / 2; i += E2_PAIR_THREADS) reinterpret_cast<unsigned *>(cnt)[i] = 0;
+    int cur_fe = -1, since_flush = 0;
+    u64 below = 0, above_min = ~0ull;
+    u64 klo = 0, width = 0;
+    int shift = 0;
+
+    auto flush = [&](int fe) {
+        __syncthreads();
+        if (!COLLECT) {
+            for (int b = tid; b < E2_NBINS; b += E2_PAIR_THREADS) {
+                const unsigned *row = reinterpret_cast<const unsigned *>(cnt + b * E2_PAIR_THREADS);
+                unsigned s = 0;
+                for (int w = 0; w < E2_PAIR_THREADS / 2; ++w) {
+                    unsigned v = row[(w + tid) & (E2_PAIR_THREADS / 2 - 1)];
+                    s += (v & 0xffffu) + (v >> 16);
+                }
+                if (s) atomicAdd(d.hist + (size_t)fe * E2_NBINS + b, (u64)s);
+            }
+            __syncthreads();
+            for (int i = tid; i < E2_NBINS * E2_PAIR_THREADS / 2; i += E2_PAIR_THREADS) reinterpret_cast<unsigned *>(cnt)[i] = 0;
+            u64 b = warp_sum_u64(below);
+            if ((tid & 31) == 0 && b) atomicAdd(below_acc + fe, b);
+            below = 0;
+        } else {
+            u64 m = warp_min_u64(above_min);
+            if ((tid & 31) == 0 && m != ~0ull) atomicMin(min_above + fe, m);
+            above_min = ~0ull;
+        }
+        __syncthreads();
+        since_flush = 0;
+    };
+    (void)red;
+
+    for (unsigned item = first; item < last; ++item) {
+        if (tid == 0) cur = decode_item(d, plan, item);
+        __syncthreads();
+        const PairItem it = cur;
+        if (it.fe != cur_fe || since_flush >= E2_FLUSH_ITEMS) {
+            if (cur_fe >= 0) flush(cur_fe);
+            cur_fe = it.fe;
+            const RadiusState &rs = d.rs[it.fe];
+            klo = rs.klo; width = rs.width; shift = rs.shift;
+        }
+        ++since_flush;
+        const int f = it.fe / d.K;
+        const int n = d.rs[it.fe].n;
+        const size_t pb = (size_t)f * d.cap + d.ent_off[it.fe];
+        const double *X = d.px + pb, *Y = d.py + pb, *Z = d.pz + pb;
+        const int jb = it.tj * E2_TILE, ib = it.ti * E2_TILE;
+        const int jn = min(E2_TILE, n - jb);
+        __syncthreads();      // previous item's readers of sx/sy/sz are done
+        for (int j = tid; j < jn; j += E2_PAIR_THREADS) { sx[j] = X[jb + j]; sy[j] = Y[jb + j]; sz[j] = Z[jb + j]; }
+        const int gi0 = ib + tid, gi1 = ib + tid + E2_PAIR_THREADS;
+        double x0 = 0, y0 = 0, z0 = 0, x1 = 0, y1 = 0, z1 = 0;
+        if (gi0 < n) { x0 = X[gi0]; y0 = Y[gi0]; z0 = Z[gi0]; }
+        if (gi1 < n) { x1 = X[gi1]; y1 = Y[gi1]; z1 = Z[gi1]; }
+        __syncthreads();
+        // pair (i, j) is taken when i < j; i beyond n is switched off by giving it the largest index
+        const int lim0 = (gi0 < n) ? gi0 : 0x7fffffff, lim1 = (gi1 < n) ? gi1 : 0x7fffffff;
+        for (int j = 0; j < jn; ++j) {
+            const double xj = sx[j], yj = sy[j], zj = sz[j];
+            const int gj = jb + j;
+            const u64 ka = d2key(dist2(x0, y0, z0, xj, yj, zj));
+            const u64 kb = d2key(dist2(x1, y1, z1, xj, yj, zj));
+            const u64 ta = ka - klo, tb = kb - klo;
+            if (gj > lim0) {
+                if (ta < width) {
+                    if (!COLLECT) cnt[(unsigned)(ta >> shift) * E2_PAIR_THREADS + slot] += 1;
+                    else { unsigned pos = atomicAdd(d.cand_n + it.fe, 1u); if (pos < E2_CAND_CAP) d.cand[(size_t)it.fe * E2_CAND_CAP + pos] = ka; }
+                } else if (ka < klo) { if (!COLLECT) ++below; }
+                else if (COLLECT && ka < above_min) above_min = ka;
+            }
+            if (gj > lim1) {
+                if (tb < width) {
+                    if (!COLLECT) cnt[(unsigned)(tb >> shift) * E2_PAIR_THREADS + slot] += 1;
+                    else { unsigned pos = atomicAdd(d.cand_n + it.fe, 1u); if (pos < E2_CAND_CAP) d.cand[(size_t)it.fe * E2_CAND_CAP + pos] = kb; }
+                } else if (kb < klo) { if (!COLLECT) ++below; }
+                else if (COLLECT && kb < above_min) above_min = kb;
+            }
+        }
+    }
+    if (cur_fe >= 0) flush(cur_fe);
+}
+
+// one thread per entity
+__global__ void radius_select_kernel(Dev d, u64 *below_acc, u64 *single_count)
+{
+    const int fe = blockIdx.x * blockDim.x + threadIdx.x;
+    if (fe >= d.F * d.K) return;
+    RadiusState &rs = d.rs[fe];
+    if (rs.phase != 0) return;
+    u64 *h = d.hist + (size_t)fe * E2_NBINS;
+    const u64 below = below_acc[fe];
+    below_acc[fe] = 0;
+    u64 total = 0;
+    for (int b = 0; b < E2_NBINS; ++b) total += h[b];
+    const u64 r1 = rs.k1;
+    if (r1 < below) {                         // the rank lies under the interval: reopen downwards
+        rs.width += rs.klo;
+        rs.klo = 0;
+        rs.shift = shift_for_width(rs.width);
+    } else if (r1 >= below + total) {         // cannot happen while the interval reaches the d2 upper bound
+        atomicExch(d.error, E2SEC_ERR_STATE);
+        rs.phase = 2;
+    } else {
+        u64 acc = below;
+        int b1 = 0;
+        for (; b1 < E2_NBINS - 1; ++b1) {
+            if (r1 < acc + h[b1]) break;
+            acc += h[b1];
+        }
+        const u64 in_bin = h[b1];
+        u64 nklo = rs.klo + ((u64)b1 << rs.shift);
+        u64 nend = rs.klo + ((u64)(b1 + 1) << rs.shift);
+        if (nend > rs.klo + rs.width || nend < nklo) nend = rs.klo + rs.width;
+        rs.klo = nklo;
+        rs.width = nend - nklo;
+        rs.below = acc;
+        if (rs.width == 1) {                  // a single key: every pair of the bin has exactly this d2
+            single_count[fe] = in_bin;
+            rs.phase = 1;
+        } else if (in_bin <= (u64)E2_CAND_CAP) {
+            single_count[fe] = 0;
+            rs.phase = 1;
+        } else {
+            rs.shift = shift_for_width(rs.width);
+        }
+    }
+    for (int b = 0; b < E2_NBINS; ++b) h[b] = 0;
+}
+
+// grid F*K CTAs of E2_SEL_THREADS
+__global__ void __launch_bounds__(E2_SEL_THREADS) radius_final_kernel(Dev d, const u64 *min_above, const u64 *single_count)
+{
+    __shared__ SelectSmem sm;
+    const int fe = blockIdx.x;
+    RadiusState &rs = d.rs[fe];
+    if (rs.phase != 1) return;
+    const u64 r1 = rs.k1 - rs.below, r2 = rs.k2 - rs.below;
+    u64 v1, v2;
+    const u64 single = single_count[fe];
+    if (single) {
+        v1 = rs.klo;
+        v2 = (r2 < single) ? rs.klo : min_above[fe];
+    } else {
+        const unsigned m = min(d.cand_n[fe], (unsigned)E2_CAND_CAP);
+        const u64 *c = d.cand + (size_t)fe * E2_CAND_CAP;
+        if (r2 < m) {
+            block_select2([&](int i) { return c[i]; }, (int)m, r1, r2, v1, v2, sm);
+        } else {
+            block_select2([&](int i) { return c[i]; }, (int)m, r1, r1, v1, v2, sm);
+            v2 = min_above[fe];
+        }
+    }
+    if (threadIdx.x == 0) {
+        double a = sqrt(key2d(v1)), b = sqrt(key2d(v2));
+        d.radius[fe] = (rs.k1 == rs.k2) ? a : (a + b) / 2.0;
+        rs.phase = 2;
+    }
+}

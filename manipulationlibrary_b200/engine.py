@@ -1,0 +1,213 @@
+"""Thin Python object model over the C ABI: Engine (device phase 1 + operators), Resolver (host phase 2),
+and record accessors. Mirrors nothing in the reference by itself -- manipulation_analyser.py in this
+package is the drop-in surface; this is what it calls."""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as nat
+from ._native import E2SecError, lib, ptr
+
+
+class Engine:
+    """One CUDA device + stream. Raises E2SecError when no device is present (no CPU fallback)."""
+
+    def __init__(self, device=0):
+        h = C.c_void_p()
+        rc = lib.e2sec_create(int(device), C.byref(h))
+        if rc != 0:
+            raise E2SecError("e2sec_create failed (%d): %s" % (rc, lib.e2sec_last_error(None).decode()))
+        self._h = h
+        self.K = None
+        self.n_points = None
+        self.max_frames = None
+        self._keep = None
+
+    def close(self):
+        if self._h:
+            lib.e2sec_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise E2SecError("%s failed (%d): %s" % (what, rc, lib.e2sec_last_error(self._h).decode()))
+
+    # ---- sequence -------------------------------------------------------------------------------
+    def configure(self, params, max_frames, n_points, keepalive=None):
+        self._check(lib.e2sec_configure(self._h, C.byref(params), int(max_frames), int(n_points)), "e2sec_configure")
+        self.K, self.n_points, self.max_frames = int(params.n_entities), int(n_points), int(max_frames)
+        self._keep = (params, keepalive)
+
+    def reset_sequence(self):
+        self._check(lib.e2sec_reset_sequence(self._h), "e2sec_reset_sequence")
+
+    def process_batch(self, xyz, labels, frame_ids, label_shape=None, image_shape=None):
+        """xyz (F, N, 3) float32, labels (F, N) or (F, h, w) int32 (host numpy). -> records (F, rec) float64."""
+        xyz = np.ascontiguousarray(xyz, np.float32)
+        F = xyz.shape[0]
+        labels = np.ascontiguousarray(labels, np.int32).reshape(F, -1)
+        fid = np.ascontiguousarray(frame_ids, np.int32)
+        lw, lh, w, h = self._shapes(labels.shape[1], label_shape, image_shape)
+        rec = np.empty((F, nat.record_doubles(self.K)), np.float64)
+        self._check(lib.e2sec_process_batch(self._h, ptr(xyz), ptr(labels), F, lw, lh, w, h, ptr(fid), 0, ptr(rec)),
+                    "e2sec_process_batch")
+        return rec
+
+    def process_batch_device(self, xyz_ptr, labels_ptr, n_frames, frame_ids, label_size, records=None,
+                             label_shape=None, image_shape=None):
+        """Device-resident inputs (raw pointers, e.g. torch tensors' data_ptr())."""
+        fid = np.ascontiguousarray(frame_ids, np.int32)
+        lw, lh, w, h = self._shapes(label_size, label_shape, image_shape)
+        self._check(lib.e2sec_process_batch(self._h, C.c_void_p(xyz_ptr), C.c_void_p(labels_ptr), int(n_frames), lw, lh,
+                                            w, h, ptr(fid), 1, ptr(records) if records is not None else None),
+                    "e2sec_process_batch")
+        return records
+
+    def _shapes(self, label_size, label_shape, image_shape):
+        if label_size == self.n_points:
+            return label_size, 1, self.n_points, 1
+        if label_shape is None or image_shape is None:
+            raise ValueError("label image smaller than the cloud: pass label_shape=(rows, cols) and image_shape=(rows, cols)")
+        return int(label_shape[1]), int(label_shape[0]), int(image_shape[1]), int(image_shape[0])
+
+    def sync(self):
+        self._check(lib.e2sec_sync(self._h), "e2sec_sync")
+
+    @property
+    def stream(self):
+        return lib.e2sec_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return int(lib.e2sec_launch_count(self._h))
+
+    def stage_ms(self):
+        out = np.zeros(8, np.float32)
+        self._check(lib.e2sec_stage_ms(self._h, ptr(out)), "e2sec_stage_ms")
+        return dict(zip(["segment", "medians", "radius", "filter", "stats", "pairs", "assemble"], out[:7].tolist()))
+
+    # ---- operators ------------------------------------------------------------------------------
+    def region_filter(self, pcd, center, median_distance, mode="closure", seed=0):
+        pcd = np.ascontiguousarray(pcd, np.float64)
+        if pcd.ndim != 2 or pcd.shape[1] != 3:
+            raise ValueError("pcd must be (n, 3)")
+        center = np.ascontiguousarray(center, np.float64)
+        out = np.empty((len(pcd) + 1, 3), np.float64)
+        n_out = C.c_int32()
+        self._check(lib.e2sec_region_filter(self._h, ptr(pcd), len(pcd), ptr(center), float(median_distance),
+                                            nat.FILTER_MODES[mode], int(seed) & 0xFFFFFFFF, ptr(out), C.byref(n_out)),
+                    "e2sec_region_filter")
+        return out[:n_out.value].copy()
+
+    def pairwise_median(self, pts):
+        pts = np.ascontiguousarray(pts, np.float64)
+        out = C.c_double()
+        self._check(lib.e2sec_pairwise_median(self._h, ptr(pts), len(pts), C.byref(out)), "e2sec_pairwise_median")
+        return out.value
+
+    def axis_median(self, pts):
+        pts = np.ascontiguousarray(pts, np.float64)
+        out = np.empty(3, np.float64)
+        self._check(lib.e2sec_axis_median(self._h, ptr(pts), len(pts), ptr(out)), "e2sec_axis_median")
+        return out
+
+    def min_distance(self, a, b, limit=0.0):
+        a = np.ascontiguousarray(a, np.float64)
+        b = np.ascontiguousarray(b, np.float64)
+        out = C.c_double()
+        self._check(lib.e2sec_min_distance(self._h, ptr(a), len(a), ptr(b), len(b), float(limit), C.byref(out)),
+                    "e2sec_min_distance")
+        return out.value
+
+
+class Resolver:
+    """Host phase 2 (sequential): records in frame order -> eSEC table."""
+
+    def __init__(self, params, keepalive=None):
+        h = C.c_void_p()
+        rc = lib.e2sec_resolver_create(C.byref(params), C.byref(h))
+        if rc != 0:
+            raise E2SecError("e2sec_resolver_create failed (%d)" % rc)
+        self._h = h
+        self.K = int(params.n_entities)
+
+    def close(self):
+        if self._h:
+            lib.e2sec_resolver_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def feed(self, records):
+        records = np.ascontiguousarray(records, np.float64).reshape(-1, nat.record_doubles(self.K))
+        rc = lib.e2sec_resolver_feed(self._h, ptr(records), len(records))
+        if rc != 0:
+            raise E2SecError("e2sec_resolver_feed failed (%d): %s" % (rc, lib.e2sec_resolver_error(self._h).decode()))
+
+    @property
+    def n_columns(self):
+        return int(lib.e2sec_resolver_columns(self._h))
+
+    def table(self):
+        """-> (codes (30, n) 'S5' array as the reference's chararray, final_columns list)."""
+        n = self.n_columns
+        codes = np.zeros((30, max(n, 1), 6), np.uint8)
+        fc = np.zeros(max(n, 1), np.int32)
+        if n:
+            lib.e2sec_resolver_table(self._h, ptr(codes), ptr(fc))
+        arr = codes[:, :n].reshape(30, n, 6).view("S6").reshape(30, n).astype("S5")
+        return arr, fc[:n].tolist()
+
+    def state(self):
+        lab = np.zeros(3, np.int32)
+        ab = np.zeros(3, np.int32)
+        lib.e2sec_resolver_state(self._h, ptr(lab), ptr(ab))
+        return lab.tolist(), ab.astype(bool).tolist()
+
+
+def esec_to_e2sec_native(table, relations, final_columns):
+    """esec_to_e2sec (manipulation_analyser.py:62-111) through the C ABI. table: (rows, n) bytes/str array."""
+    t = np.asarray(table)
+    rows, n = t.shape
+    codes = np.zeros((rows, n, 6), np.uint8)
+    as_bytes = np.char.encode(t, "ascii") if t.dtype.kind == "U" else t
+    flat = as_bytes.astype("S6").reshape(rows, n)
+    codes[:] = np.frombuffer(flat.tobytes(), np.uint8).reshape(rows, n, 6)
+    out = np.zeros((rows, max(n, 1), 6), np.uint8)
+    fc = np.ascontiguousarray(final_columns, np.int32).copy()
+    nf = C.c_int32(len(fc))
+    fcbuf = np.zeros(max(len(fc), 1), np.int32)
+    fcbuf[:len(fc)] = fc
+    c2 = lib.e2sec_esec_to_e2sec(ptr(codes), rows, n, int(relations), ptr(out), ptr(fcbuf), C.byref(nf))
+    if c2 < 0:
+        raise E2SecError("e2sec_esec_to_e2sec failed (%d)" % c2)
+    r2 = rows - {3: 6, 2: 4, 1: 2}[int(relations)]
+    e2 = out.reshape(-1)[: r2 * c2 * 6].reshape(r2, c2, 6).view("S6").reshape(r2, c2).astype("S5")
+    return e2, fcbuf[: nf.value].tolist()
+
+
+# ---- record accessors ------------------------------------------------------------------------------
+def rec_entity(rec, e):
+    r = rec[nat.REC_HEADER + nat.REC_ENTITY * e: nat.REC_HEADER + nat.REC_ENTITY * (e + 1)]
+    return dict(n_raw=int(r[0]), n_out=int(r[1]), seed=int(r[2]), radius=r[3], median=r[4:7], lo=r[7:10], hi=r[10:13],
+                mean=r[13:16])
+
+
+def rec_pairs(rec, K):
+    o = nat.REC_HEADER + nat.REC_ENTITY * K
+    return rec[o: o + (K + 1) * (K + 1)].reshape(K + 1, K + 1)
+
+
+def rec_cross(rec, K):
+    o = nat.REC_HEADER + nat.REC_ENTITY * K + (K + 1) * (K + 1)
+    return rec[o: o + K * K].reshape(K, K)

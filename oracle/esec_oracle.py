@@ -488,7 +488,8 @@ class E2SecOracle:
                 radius = self.radius_override.get((frame, i))
                 if radius is None:
                     radius = pairwise_median(obj)                            # :1524
-                d.update(radius=radius, seed=find_seed(obj, center), filtered=True, median=center)
+                sd = find_seed(obj, center)
+                d.update(radius=radius, seed=sd, seed_raster=int(idx[sd]), filtered=True, median=center)
                 if self.filter_mode == "closure":
                     out = closure_filter(obj, center, radius)
                 else:

@@ -1,0 +1,97 @@
+"""Host phase 2 (csrc/resolver.cpp through the C ABI) against the reference-run goldens, no GPU needed:
+records come from the CPU oracle (oracle/records.py), the sequential logic under test is the C++ resolver."""
+import numpy as np
+import pytest
+
+from oracle import esec_oracle as eo
+from oracle.records import RecordOracle
+from tests.helpers import PUSHING06_ARGS, Pushing06Frames, load_golden
+
+
+def _oracle(mode, gold, fx):
+    ov = {(int(r[0]), int(r[1])): float(r[4]) for r in gold["filter_calls"]}
+    ref_filter = None
+    if mode == "reference_seeded":
+        from oracle import build_ref
+        try:
+            ref_filter = build_ref.load()
+        except ImportError:
+            pass
+    return eo.E2SecOracle(PUSHING06_ARGS["ground_label"], PUSHING06_ARGS["hand_label"], None, PUSHING06_ARGS["thresh"],
+                          fx["translation"], fx["roll"], fx["ground"], fx["total_unique_labels"], replace=False,
+                          filter_mode=mode, seed=20261104, ref_filter=ref_filter, radius_override=ov)
+
+
+@pytest.fixture(scope="module")
+def oracle_records():
+    out = {}
+    fx = load_golden("pushing06_fixture")
+    frames = Pushing06Frames()
+    for mode in ("closure",):
+        gold = load_golden("pushing06_" + mode)
+        ro = RecordOracle(_oracle(mode, gold, fx))
+        recs = []
+        for k in range(len(frames)):
+            xyz, lab = frames.dense(k)
+            recs.append(ro.frame_record(int(frames.frame_ids[k]), xyz, lab, bool(frames.hand_in_raw[k])))
+        out[mode] = np.array(recs)
+    return out
+
+
+def _params(fx, mode="closure"):
+    from manipulationlibrary_b200 import _native as nat
+    return nat.make_params(fx["total_unique_labels"], 11, 2, None, 0.07, fx["translation"], fx["roll"], fx["ground"],
+                           filter_mode=mode, filter_seed=20261104)
+
+
+def test_resolver_reproduces_reference_matrix(oracle_records):
+    from manipulationlibrary_b200.engine import Resolver, esec_to_e2sec_native
+    fx = load_golden("pushing06_fixture")
+    gold = load_golden("pushing06_closure")
+    p, keep = _params(fx)
+    r = Resolver(p, keep)
+    recs = oracle_records["closure"]
+    r.feed(recs[:30])            # fed in two calls: state carries over
+    r.feed(recs[30:])
+    table, fc = r.table()
+    assert table.shape == (30, len(fc))
+    e2, fc2 = esec_to_e2sec_native(table, 3, fc)
+    assert e2.shape == gold["e2sec"].shape
+    assert (e2.astype("U5") == gold["e2sec"]).all()
+    assert fc2 == list(gold["final_columns"])
+    # every emitted raw column equals the reference's column for that frame
+    gcols = {int(c[0]): row for c, row in zip(gold["columns"], gold["raw_columns"])}
+    for j, f in enumerate(fc):
+        assert (np.char.upper(table[:, j].astype("U5")) == np.char.upper(gcols[f])).all(), f
+    labels, absent = r.state()
+    last = gold["columns"][-1]
+    assert labels == [int(last[1]), int(last[2]), int(last[3])]
+
+
+def test_resolver_rejects_out_of_order_feed(oracle_records):
+    from manipulationlibrary_b200.engine import Resolver
+    from manipulationlibrary_b200._native import E2SecError
+    fx = load_golden("pushing06_fixture")
+    p, keep = _params(fx)
+    r = Resolver(p, keep)
+    recs = oracle_records["closure"]
+    kept = [i for i, x in enumerate(recs) if int(x[1]) == 3]
+    r.feed(recs[: kept[3] + 1])
+    with pytest.raises(E2SecError):
+        r.feed(recs[kept[5]: kept[5] + 1])      # skips a kept frame: the cross table no longer matches
+
+
+def test_esec_to_e2sec_native_matches_oracle():
+    from manipulationlibrary_b200.engine import esec_to_e2sec_native
+    rng = np.random.default_rng(3)
+    for trial in range(20):
+        n = int(rng.integers(1, 12))
+        t = rng.choice(["n", "t", "HAr", "VArT", "u", "a"], size=(30, n)).astype("U5")
+        for j in range(1, n):
+            if rng.random() < 0.4:
+                t[:, j] = t[:, j - 1]
+        fc = list(range(0, 3 * n, 3))
+        want, _, wfc = eo.esec_to_e2sec(t, 3, fc)
+        got, gfc = esec_to_e2sec_native(t, 3, fc)
+        assert got.shape == want.shape and (got.astype("U5") == want).all()
+        assert gfc == list(wfc)
