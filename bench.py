@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""e2SEC extraction throughput (BASELINE.json metric) on synthetic 640x480 / 10-object streams.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step = one pass of the hot path (phase 1 on the GPU for a batch of `--batch` frames of the stream; the sequential
+phase-2 resolver runs over all records at the end of the timed region, after the one all-gather when N > 1).
+`value` = frames/s with the frames already resident in HBM; `e2e` = the same through the C ABI with pinned HOST
+buffers (H2D of every frame and D2H of the records inside the timed region).  `roofline` is for the dominant
+stage of the step; `cpu_baseline` is the CPU oracle (a port of the reference's per-frame pass) on the host cores.
+--impl reference times that CPU path alone, frame-parallel over all host cores.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "e2sec_frames_per_sec"
+UNIT = "frames/s"
+WIDTH, HEIGHT, N_OBJECTS, STREAM_CONFIG = 640, 480, 10, 2
+BYTES_PER_POINT = 16                     # 12 B xyz float32 + 4 B int32 label, read once
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=100, help="frames per step and per GPU")
+    ap.add_argument("--pool", type=int, default=300, help="distinct frames resident per GPU (cycled)")
+    ap.add_argument("--filter-mode", default="closure", choices=["closure", "reference_seeded"])
+    ap.add_argument("--cpu-frames", type=int, default=4, help="frames of the cpu_baseline sample (0 = skip)")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name():
+    return "synthetic %dx%d organised cloud stream, %d labelled objects" % (WIDTH, HEIGHT, N_OBJECTS)
+
+
+# ---- CPU oracle legs (the only places bench.py touches oracle/) ------------------------------------------------------
+def _oracle_for(stream, mode):
+    from oracle import esec_oracle as eo
+    return eo.E2SecOracle(stream.ground_label, stream.hand_label, None, stream.thresh, stream.translation, stream.roll,
+                          stream.ground, stream.total_unique_labels, filter_mode=mode, seed=20261104)
+
+
+def cpu_baseline_single(stream, first, n_frames, mode):
+    """The oracle's sequential per-frame pass on one core: frames/s over n_frames consecutive frames."""
+    orc = _oracle_for(stream, mode)
+    frames = [stream.frame(first + i) for i in range(n_frames)]
+    t0 = time.perf_counter()
+    for i, (xyz, lab) in enumerate(frames):
+        orc.process_frame(first + i, xyz, lab.reshape(stream.H, stream.W))
+    dt = time.perf_counter() - t0
+    return n_frames / dt, dt
+
+
+def _ref_worker(conn, wid, first, mode):
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    stream = SyntheticStream(WIDTH, HEIGHT, N_OBJECTS, config=STREAM_CONFIG)
+    orc = _oracle_for(stream, mode)
+    nxt = None
+    while True:
+        msg = conn.recv()
+        if msg[0] == "prep":
+            nxt = (msg[1], stream.frame(msg[1]))
+            conn.send("ok")
+        elif msg[0] == "run":
+            f, (xyz, lab) = nxt
+            orc.process_frame(f, xyz, lab.reshape(stream.H, stream.W))
+            conn.send("ok")
+        else:
+            return
+
+
+def run_reference(args):
+    """The reference's CPU implementation of the path (oracle port), one frame per host core per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        cores = os.cpu_count() or 1
+    try:                                          # one worker holds ~0.5 GB of pdist output at a time
+        import psutil
+        cores = max(1, min(cores, int(psutil.virtual_memory().available / 2 ** 30 / 1.5)))
+    except Exception:
+        pass
+    cores = min(cores, 64)
+    ctx = mp.get_context("fork")
+    span = args.steps + args.warmup + 1
+    workers = []
+    for w in range(cores):
+        a, b = ctx.Pipe()
+        p = ctx.Process(target=_ref_worker, args=(b, w, 30 + w * span, args.filter_mode), daemon=True)
+        p.start()
+        workers.append((p, a, 30 + w * span))
+
+    def step(i, timed):
+        for _, c, first in workers:
+            c.send(("prep", first + i))
+        for _, c, _ in workers:
+            c.recv()
+        t0 = time.perf_counter()
+        for _, c, _ in workers:
+            c.send(("run",))
+        for _, c, _ in workers:
+            c.recv()
+        return time.perf_counter() - t0
+
+    for i in range(args.warmup):
+        step(i, False)
+    total = 0.0
+    for i in range(args.steps):
+        total += step(args.warmup + i, True)
+    for p, c, _ in workers:
+        c.send(("stop",))
+        p.join(timeout=5)
+    frames = cores * args.steps
+    value = frames / total
+    sample = "%d frames per step (one per host core), %d timed steps" % (cores, args.steps)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(), "filter_mode": args.filter_mode, "frames_per_step": cores},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }), flush=True)
+
+
+# ---- clocks ----------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, uuid):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", uuid, "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            if t < t0 or t > t1 + 0.1:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---- the B200 arm ----------------------------------------------------------------------------------------------------
+def generate_pool(stream, first, count):
+    from concurrent.futures import ThreadPoolExecutor
+    xyz = np.empty((count, stream.N, 3), np.float32)
+    lab = np.empty((count, stream.N), np.int32)
+
+    def one(i):
+        xyz[i], lab[i] = stream.frame(first + i)
+
+    with ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1)) as ex:
+        list(ex.map(one, range(count)))
+    return xyz, lab
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from manipulationlibrary_b200 import _native as nat
+    from manipulationlibrary_b200.engine import Engine, Resolver
+    from manipulationlibrary_b200.sharding import gather_records
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU arm)")
+    stream = SyntheticStream(WIDTH, HEIGHT, N_OBJECTS, config=STREAM_CONFIG)
+    B, K, W = args.batch, args.steps, args.warmup
+    N = stream.N
+    pool = max(B, min(args.pool, (K + W) * B))
+    pool = (pool // B) * B
+    rank_first = rank * (K + W) * B               # every rank owns its block of the stream (weak scaling)
+
+    # cpu_baseline before the CUDA context exists on this rank (rank 0, N = 1 only)
+    cpu = None
+    if rank == 0 and world == 1 and args.cpu_frames > 0:
+        v, dt = cpu_baseline_single(stream, 30, args.cpu_frames, args.filter_mode)
+        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": "%d consecutive frames of the same stream, oracle.esec_oracle.E2SecOracle.process_frame, %.1f s" % (args.cpu_frames, dt)}
+
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    hx, hl = generate_pool(stream, rank_first, pool)
+    hx_t = torch.from_numpy(hx).pin_memory()
+    hl_t = torch.from_numpy(hl).pin_memory()
+    dx = hx_t.to(dev, non_blocking=True)
+    dl = hl_t.to(dev, non_blocking=True)
+    torch.cuda.synchronize()
+
+    p, keep = nat.make_params(**stream.params(filter_mode=args.filter_mode, filter_seed=20261104))
+    eng = Engine(local)
+    eng.configure(p, B, N, keep)
+    est = torch.cuda.ExternalStream(eng.stream, device=dev)
+    rec_w = nat.record_doubles(int(p.n_entities))
+    total_frames = (K + W) * B
+    rec_host = torch.empty((total_frames, rec_w), dtype=torch.float64).pin_memory()
+    rec_np = rec_host.numpy()
+    ids_all = np.arange(rank_first, rank_first + total_frames, dtype=np.int32)
+
+    def step(i, on_device):
+        s = (i * B) % pool
+        ids = ids_all[i * B: (i + 1) * B]
+        out = rec_np[i * B: (i + 1) * B]
+        if on_device:
+            eng.process_batch_device(dx[s].data_ptr(), dl[s].data_ptr(), B, ids, N, records=out)
+        else:
+            rc = nat.lib.e2sec_process_batch(eng._h, hx_t[s].data_ptr(), hl_t[s].data_ptr(), B, N, 1, N, 1, nat.ptr(ids), 0,
+                                             nat.ptr(out))
+            eng._check(rc, "e2sec_process_batch")
+
+    def finish(n_steps, first_step):
+        """one gather of the records (N > 1) + the sequential phase 2 on rank 0"""
+        local_rec = rec_np[first_step * B: (first_step + n_steps) * B]
+        if world > 1:
+            full = gather_records(local_rec, n_steps * B * world, world, device=dev)
+        else:
+            full = local_rec
+        cols = 0
+        if rank == 0:
+            per = n_steps * B
+            for r in range(world):                     # every shard is its own sequence in this benchmark
+                res = Resolver(p, keep)
+                res.feed(full[r * per: (r + 1) * per])
+                cols += res.n_columns
+                res.close()
+        return cols
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(on_device, first_step, n_steps):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        l0 = eng.launch_count
+        t0 = time.perf_counter()
+        with torch.cuda.stream(est):
+            ev0.record()
+        for i in range(n_steps):
+            step(first_step + i, on_device)
+        cols = finish(n_steps, first_step)
+        with torch.cuda.stream(est):
+            ev1.record()
+        barrier()
+        t1 = time.perf_counter()
+        ms = max(ev0.elapsed_time(ev1), 0.0)
+        wall = (t1 - t0) * 1e3
+        t = torch.tensor([ms, wall], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), float(t[1]), eng.launch_count - l0, cols, (t0, t1)
+
+    eng.reset_sequence()
+    for i in range(W):
+        step(i, True)
+    uuid = str(torch.cuda.get_device_properties(dev).uuid)
+    sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if rank == 0 else None
+    time.sleep(0.3 if sampler else 0.0)
+    ms, wall_ms, launches, cols, (t0, t1) = timed(True, W, K)
+    stages = eng.stage_ms()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    # the event pair brackets device work AND the host resolver between launches; wall is reported beside it
+    frames = K * B * world
+    value = frames / (ms * 1e-3)
+
+    e2e = None
+    if not args.no_e2e:
+        eng.reset_sequence()
+        step(0, False)
+        ems, ewall, _, _, _ = timed(False, W, K)
+        e2e = {"value": frames / (ewall * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * N * BYTES_PER_POINT,
+               "d2h_bytes_per_step": B * rec_w * 8, "timing": "wall clock around the C-ABI calls, pinned host buffers"}
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        which = "measured" if "hbm_gbs" in peaks else "fallback"
+        dom = max(stages, key=lambda k: stages[k])
+        dom_ms = stages[dom]
+        alg = B * N * BYTES_PER_POINT
+        achieved = alg / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None
+        step_gbs = frames / world * N * BYTES_PER_POINT / (ms * 1e-3) / 1e9
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": workload_name(), "frames_per_step_per_gpu": B, "frames_timed": frames,
+                       "pool_frames_per_gpu": pool, "filter_mode": args.filter_mode,
+                       "l2": "inputs larger than L2 (one step reads %d MB)" % (alg // 2 ** 20),
+                       "parallelism": "frame-sharded x%d, one record all-gather" % world},
+            "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": wall_ms / K, "esec_columns": cols,
+            "stages_ms_last_step": stages,
+            "roofline": {"bound": "hbm", "kernel": dom + " stage of one step", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "peak_source": which, "whole_step_gbs_per_gpu": step_gbs, "whole_step_frac": step_gbs / peak},
+        }
+        if e2e:
+            out["e2e"] = e2e
+        if cpu:
+            out["cpu_baseline"] = cpu
+        print(json.dumps(out), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

