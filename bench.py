@@ -286,6 +286,7 @@ def run_b200(args):
 
     def timed(on_device, first_step, n_steps):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        eng.reset_sequence()                # the timed block is its own sequence (the resolver starts at its first frame)
         barrier()
         l0 = eng.launch_count
         t0 = time.perf_counter()

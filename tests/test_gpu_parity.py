@@ -234,7 +234,10 @@ def test_empty_and_ragged_frames(engine):
     rec = engine.process_batch(xyz, lab, [0, 3, 6])
     assert rec[0, 1] == 0 and rec[1, 1] == 0 and rec[2, 1] == 3
     ent = lambda f, e: rec[f, REC_HEADER + REC_ENTITY * e: REC_HEADER + REC_ENTITY * (e + 1)]
-    assert ent(0, 5)[0] == 0 and ent(1, 2)[0] == 100 and ent(1, 2)[1] == 101
+    obj4 = eo.transform_points(eo.transform_points(xyz[1, :100].astype(np.float64), fx["translation"]), fx["roll"])
+    want4 = eo.closure_filter(obj4, np.median(obj4, axis=0), eo.pairwise_median(obj4))
+    assert ent(0, 5)[0] == 0 and ent(1, 2)[0] == 100 and ent(1, 2)[1] == len(want4)
+    np.testing.assert_array_equal(ent(1, 2)[7:10], want4.min(0))
     assert ent(2, 3)[0] == 3 and ent(2, 3)[1] == 3 and ent(2, 3)[2] == -1 and np.isnan(ent(2, 3)[3])
     obj = eo.transform_points(eo.transform_points(xyz[2, 60:63].astype(np.float64), fx["translation"]), fx["roll"])
     np.testing.assert_array_equal(ent(2, 3)[7:10], obj.min(0))
