@@ -1,0 +1,212 @@
+"""Drop-in surface of the reference's manipulation_analyser.py for the e2SEC extraction path.
+
+Same entry points, arguments and outputs as /root/reference/manipulation_analyser.py:
+    analyse_maniac_manipulation(...)   :2184-2291   writes e2sec_<savename>.npy in the CWD, returns None
+    _process(...)                      :1355-2182   one frame -> (translation, roll, ESEC_table)
+    esec_to_e2sec(esec_array, relations) :62-111    -> (e2sec_array, esec_array), thins the module's final_columns
+Everything that touches points runs in libe2sec.so (sm_100a CUDA through the C ABI of include/e2sec.h); the
+sequential o1/o2/o3 + relation logic is the library's host resolver.  There is no Open3D, no Cython and no CPU
+fallback: without a CUDA device the first call raises.
+
+Scope notes:
+  * frame-0 setup (_getGroundiNewNew :278-361, _getTranslation :212-276) is random in the reference and outside
+    this path; its products are INPUTS here: call set_frame0(translation, roll, ground) before the first frame.
+  * icp=True (:1677-1738) and relations 1 / 2 are not implemented: they raise NotImplementedError.
+  * debug=True writes the data behind the reference's debug PNGs (:1830-1998) as
+    debug_images/<savename>/<frame>.json (AABBs, centres, relation codes) and prunes them to final_columns like
+    _clean_debug_images (:160-173); matplotlib rendering is unavailable on this box.
+State lives in module globals like the reference's (:32-59): one sequence at a time per process.
+"""
+import json
+import os
+import shutil
+
+import numpy as np
+
+from . import _native as nat
+from .engine import Engine, Resolver, esec_to_e2sec_native, rec_entity
+
+IMAGE_SHAPE = (480, 640)            # :1390, :1433
+BATCH_FRAMES = 25
+
+final_columns = []
+total_unique_labels = 0
+hand_label_inarray = -1
+_frame0 = None
+_state = None                       # per-sequence: engine, resolver, params
+
+
+def set_frame0(translation, roll, ground):
+    """The frame-0 products the reference computes at :1397-1404 (4x4, 4x4, (G,3) ground cloud already transformed)."""
+    global _frame0
+    _frame0 = (np.asarray(translation, np.float64).reshape(4, 4), np.asarray(roll, np.float64).reshape(4, 4),
+               np.ascontiguousarray(ground, np.float64).reshape(-1, 3))
+
+
+def _total_unique_labels(label0, hand_label, replace, old, ignored_labels, cut_labels):
+    """:1406-1426"""
+    tul = np.unique(label0)
+    if replace:
+        for v in old:
+            tul = np.delete(tul, np.where(tul == v))
+    for v in ignored_labels:
+        if v in tul:
+            tul = np.delete(tul, np.where(tul == v))
+    if hand_label not in tul:
+        if len(cut_labels) > 0:
+            tul = np.append(tul, cut_labels)
+        tul = np.append(tul, hand_label)
+    elif len(cut_labels) > 0:
+        tul = np.append(tul, cut_labels)
+    return tul
+
+
+def read_frame(pcd_file, label_file):
+    """o3d.io.read_point_cloud (:1441) + pd.read_csv (:1391) through the library's host readers."""
+    xyz = np.empty((IMAGE_SHAPE[0] * IMAGE_SHAPE[1], 3), np.float32)
+    w, h = nat.C.c_int32(), nat.C.c_int32()
+    rc = nat.lib.e2sec_read_pcd_xyz(os.fsencode(pcd_file), nat.ptr(xyz), xyz.shape[0], nat.C.byref(w), nat.C.byref(h))
+    if rc != 0:
+        raise IOError("cannot read %s (e2sec_read_pcd_xyz -> %d)" % (pcd_file, rc))
+    lab = np.empty(IMAGE_SHAPE[0] * IMAGE_SHAPE[1], np.int32)
+    rows, cols = nat.C.c_int32(), nat.C.c_int32()
+    rc = nat.lib.e2sec_read_labels(os.fsencode(label_file), nat.ptr(lab), lab.shape[0], nat.C.byref(rows), nat.C.byref(cols))
+    if rc != 0:
+        raise IOError("cannot read %s (e2sec_read_labels -> %d)" % (label_file, rc))
+    return xyz[: w.value * h.value], lab[: rows.value * cols.value].reshape(rows.value, cols.value)
+
+
+def _check_args(relations, icp, cython):
+    if relations != 3:
+        raise NotImplementedError("relations=%r: this path implements relations=3 (T/N + SSR + DSR)" % (relations,))
+    if icp:
+        raise NotImplementedError("icp=True (rigid-model tracking, manipulation_analyser.py:1677-1738) is outside this "
+                                  "path; call with icp=False")
+    if not cython:
+        raise NotImplementedError("cython=False selects Open3D's statistical outlier branch (:1534-1541), not built")
+
+
+def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
+                    thresh, max_frames, filter_mode, filter_seed):
+    global _state, total_unique_labels, hand_label_inarray, final_columns
+    if _frame0 is None:
+        raise NotImplementedError("frame-0 setup (_getGroundiNewNew / _getTranslation) is outside this path: call "
+                                  "manipulation_analyser.set_frame0(translation, roll, ground) first")
+    tul = _total_unique_labels(label0, hand_label, replace, old, ignored_labels, cut_labels)
+    total_unique_labels = tul
+    hand_label_inarray = int(np.where(tul == hand_label)[0][0])      # IndexError like :1520 when absent
+    int(np.where(tul == ground_label)[0][0])
+    T, R, ground = _frame0
+    p, keep = nat.make_params(tul, hand_label, ground_label, support_hand, thresh, T, R, ground, replace=replace,
+                              old=old, new=new, filter_mode=filter_mode, filter_seed=filter_seed)
+    if _state is not None:
+        _state["engine"].close()
+        _state["resolver"].close()
+    eng = Engine(0)
+    eng.configure(p, max_frames, IMAGE_SHAPE[0] * IMAGE_SHAPE[1], keep)
+    _state = dict(engine=eng, resolver=Resolver(p, keep), params=p, keep=keep, K=len(tul), records={})
+    final_columns = []
+
+
+def _table_from_resolver(relations):
+    global final_columns
+    table, fc = _state["resolver"].table()
+    final_columns = list(fc)
+    if table.shape[1] == 0:
+        t = np.chararray((10 * relations, 1), itemsize=5)
+        t[:] = "-"
+        return t
+    return table.view(np.chararray)
+
+
+def _run_batch(frames, xyz, labels, label_shape):
+    eng = _state["engine"]
+    kw = {}
+    if labels.shape[1] != xyz.shape[1]:
+        kw = dict(label_shape=label_shape, image_shape=IMAGE_SHAPE)
+    rec = eng.process_batch(xyz, labels, frames, **kw)
+    _state["resolver"].feed(rec)
+    for f, r in zip(frames, rec):
+        _state["records"][int(f)] = r
+
+
+def _process(pcd_file, label_file, ground_label, hand_label, support_hand, translation, roll, frame, ESEC_table,
+             relations, replace=False, old=[], new=[], ignored_labels=[], cut_labels=[], thresh=0.1, debug=False,
+             cython=True, icp=True, savename="", filter_mode="closure", filter_seed=0):
+    """One frame of the sequence (the reference's per-frame entry point, :1355-1357)."""
+    _check_args(relations, icp, cython)
+    xyz, label = read_frame(pcd_file, label_file)
+    if frame == 0 or _state is None:
+        _start_sequence(label, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
+                        thresh, 1, filter_mode, filter_seed)
+    _run_batch(np.array([frame], np.int32), xyz[None], label.reshape(1, -1).astype(np.int32), label.shape)
+    T, R, _ = _frame0
+    return T, R, _table_from_resolver(relations)
+
+
+def esec_to_e2sec(esec_array, relations):
+    """:62-111 -> (e2sec_array, esec_array upper-cased); thins the module-level final_columns like the reference."""
+    global final_columns
+    e2, fc = esec_to_e2sec_native(np.asarray(esec_array), relations, final_columns)
+    final_columns = fc
+    up = np.char.upper(np.asarray(esec_array)).view(np.chararray)
+    return e2.view(np.chararray), up
+
+
+def _debug_artefact(frame, rec, column, K):
+    ents = {}
+    for e in range(K):
+        d = rec_entity(rec, e)
+        ents[str(int(total_unique_labels[e]))] = dict(points=d["n_out"], aabb_min=list(d["lo"]), aabb_max=list(d["hi"]),
+                                                      mean=list(d["mean"]))
+    return dict(frame=int(frame), relations=[c.decode() if isinstance(c, bytes) else str(c) for c in column], entities=ents)
+
+
+def _clean_debug_images(final_columns, savename):
+    """:160-173"""
+    path = "debug_images/" + savename + "/"
+    for item in sorted(os.listdir(path)):
+        if int(item.split(".")[0]) not in final_columns:
+            os.remove(path + item)
+
+
+def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, support_hand, relations, replace, old,
+                                new, ignored_labels, thresh, cut_labels=[], debug=False, cython=True, icp=True,
+                                savename="", filter_mode="closure", filter_seed=0):
+    """:2184-2291.  Extra keyword arguments (additions): filter_mode 'closure' | 'reference_seeded', filter_seed."""
+    global final_columns
+    _check_args(relations, icp, cython)
+    if debug:
+        for d in ("debug_images/", "event_images/"):
+            if os.path.exists(d + savename + "/"):
+                shutil.rmtree(d + savename + "/")
+            os.makedirs(d + savename + "/")
+    fps = 10
+    step = int(30 / fps)                                                 # :2266-2268
+    files = sorted(os.listdir(pcl_path))
+    todo = [(i, f) for i, f in enumerate(files) if i % step == 0]
+    started = False
+    for s in range(0, len(todo), BATCH_FRAMES):
+        chunk = todo[s: s + BATCH_FRAMES]
+        xs, ls, ids = [], [], []
+        for i, f in chunk:
+            xyz, label = read_frame(pcl_path + f[0:-7] + "_pc.pcd", label_path + f[0:-7] + "_left-labels.dat")
+            if not started:
+                _start_sequence(label, ground_label, hand_label, support_hand, replace, old, new, ignored_labels,
+                                cut_labels, thresh, BATCH_FRAMES, filter_mode, filter_seed)
+                started = True
+            xs.append(xyz)
+            ls.append(label.reshape(-1).astype(np.int32))
+            ids.append(i)
+            lshape = label.shape
+        _run_batch(np.array(ids, np.int32), np.stack(xs), np.stack(ls), lshape)
+    table = _table_from_resolver(relations)
+    raw_columns = list(final_columns)
+    if debug:
+        for j, f in enumerate(raw_columns):
+            with open("debug_images/%s/%d.json" % (savename, f), "w") as fh:
+                json.dump(_debug_artefact(f, _state["records"][f], table[:, j], _state["K"]), fh)
+    e2sec, esec = esec_to_e2sec(table, relations)
+    np.save("e2sec_%s.npy" % savename.replace("/", "_"), e2sec)
+    if debug:
+        _clean_debug_images(final_columns, savename)

@@ -4,6 +4,7 @@ Bars (BASELINE.json north_star): relation codes / matrices / counts / indices bi
 radii and touching distances are compared for equality first (the kernels evaluate the reference's float64
 expressions in the reference's operation order), means within 1e-12 relative (tolerance bar: 1e-5).
 """
+import os
 import random
 
 import numpy as np
@@ -274,3 +275,99 @@ def test_synthetic_sharded_equals_whole(engine):
     r = Resolver(p, keep)
     r.feed(whole)
     assert r.n_columns >= 1
+
+
+# ---- the drop-in Python surface ---------------------------------------------------------------------
+def _write_sequence(tmp, frames, every=3):
+    """Pushing_06 fixture frames as files named like the MANIAC recordings: <stem>_pc.pcd (binary PCD) and
+    <stem>_left-labels.dat; the frames the reference skips (i % 3 != 0, :2272) are empty placeholders."""
+    pcl, lab = tmp / "pcl", tmp / "lab"
+    pcl.mkdir()
+    lab.mkdir()
+    head = ("# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\nCOUNT 1 1 1\n"
+            "WIDTH 640\nHEIGHT 480\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS 307200\nDATA binary\n").encode()
+    by_id = {int(f): k for k, f in enumerate(frames.frame_ids)}
+    last = int(frames.frame_ids[-1])
+    for i in range(last + 1):
+        stem = "%05d" % (505 + i)
+        if i % every or i not in by_id:
+            (pcl / (stem + "_pc.pcd")).write_bytes(b"")
+            continue
+        xyz, labels = frames.dense(by_id[i])
+        with open(pcl / (stem + "_pc.pcd"), "wb") as f:
+            f.write(head)
+            f.write(np.ascontiguousarray(xyz, "<f4").tobytes())
+        rows = labels.reshape(480, 640).copy()
+        # the sparse fixture dropped border / ground pixels: put their labels back on point-less (NaN) pixels so that
+        # np.unique(frame-0 labels) gives the reference's total_unique_labels [0, 2, 4, 5, 6, 11] (:1406-1426)
+        rows[0][rows[0] == 255] = 0
+        rows[1][rows[1] == 255] = 2
+        with open(lab / (stem + "_left-labels.dat"), "w") as f:
+            f.write("\n".join(" ".join(map(str, r)) for r in rows.tolist()) + "\n")
+    return str(pcl) + "/", str(lab) + "/"
+
+
+def test_dropin_analyse_maniac_manipulation(tmp_path, monkeypatch):
+    """The reference's entry point, called like notebook cell 4 (icp=False): the saved e2sec_<savename>.npy equals the
+    matrix the reference's own code produced, debug artefacts are pruned to final_columns."""
+    from manipulationlibrary_b200 import manipulation_analyser as ma
+    frames = Pushing06Frames()
+    fx = load_golden("pushing06_fixture")
+    gold = load_golden("pushing06_closure")
+    pcl, lab = _write_sequence(tmp_path, frames)
+    monkeypatch.chdir(tmp_path)
+    ma.set_frame0(fx["translation"], fx["roll"], fx["ground"])
+    # the fixture's labels are already upscaled and replaced; 255 marks untracked pixels -> ignored_labels
+    out = ma.analyse_maniac_manipulation(pcl, lab, 2, 11, None, 3, False, [], [], [255], 0.07, debug=True, icp=False,
+                                         savename="Pushing_06")
+    assert out is None
+    e2 = np.load(tmp_path / "e2sec_Pushing_06.npy")
+    assert e2.shape == gold["e2sec"].shape and e2.dtype.kind == "S"
+    assert (e2.astype("U5") == gold["e2sec"]).all()
+    assert list(ma.final_columns) == list(gold["final_columns"])
+    kept = sorted(int(p.name.split(".")[0]) for p in (tmp_path / "debug_images" / "Pushing_06").iterdir())
+    assert kept == sorted(set(int(c) for c in gold["final_columns"]))
+    with pytest.raises(NotImplementedError):
+        ma.analyse_maniac_manipulation(pcl, lab, 2, 11, None, 3, False, [], [], [255], 0.07, icp=True)
+
+
+def test_dropin_process_frame_by_frame(tmp_path, monkeypatch):
+    """_process called per frame like the reference's loop (:2271-2281) builds the same raw eSEC table."""
+    from manipulationlibrary_b200 import manipulation_analyser as ma
+    frames = Pushing06Frames()
+    fx = load_golden("pushing06_fixture")
+    gold = load_golden("pushing06_closure")
+    pcl, lab = _write_sequence(tmp_path, frames)
+    ma.set_frame0(fx["translation"], fx["roll"], fx["ground"])
+    table = np.chararray((30, 1), itemsize=5)
+    table[:] = "-"
+    T = R = 0
+    files = sorted(os.listdir(pcl))
+    for i, f in enumerate(files[:120]):
+        if i % 3 == 0:
+            T, R, table = ma._process(pcl + f[0:-7] + "_pc.pcd", lab + f[0:-7] + "_left-labels.dat", 2, 11, None, T, R, i,
+                                      table, 3, ignored_labels=[255], thresh=0.07, icp=False)
+    gcols = {int(c[0]): row for c, row in zip(gold["columns"], gold["raw_columns"])}
+    assert table.shape[1] == len(ma.final_columns) >= 5
+    for j, fr in enumerate(ma.final_columns):
+        assert (np.char.upper(table[:, j].astype("U5")) == np.char.upper(gcols[fr])).all()
+
+
+def test_dropin_region_filter_cython(engine):
+    from manipulationlibrary_b200.cython_filter_new import filter_cython_new as f
+    rng = np.random.default_rng(11)
+    pts = _cloud(rng, 500)
+    center = np.median(pts, axis=0)
+    radius = eo.pairwise_median(pts)
+    f.set_mode("closure")
+    np.testing.assert_array_equal(np.asarray(f.region_filter_cython(pts.mean(0), pts, 1, center, center, radius)),
+                                  eo.closure_filter(pts, center, radius))
+    f.set_mode("reference_seeded", 99)
+    np.testing.assert_array_equal(np.asarray(f.region_filter_cython(pts.mean(0), pts, 0, center, center, radius * 0.4)),
+                                  eo.region_filter_restated(pts, center, radius * 0.4, random.Random(99)))
+    f.set_mode("closure")
+    assert f.region_filter_cython(pts.mean(0), pts[:2].copy(), 0, center, center, radius).shape == (1, 3)
+    with pytest.raises(ValueError):
+        f.region_filter_cython(pts.mean(0), pts[:, ::-1], 0, center, center, radius)       # not C-contiguous
+    assert f.distance_cython(pts[0].copy(), pts[1].copy()) == float(
+        np.sqrt((pts[0, 0] - pts[1, 0]) ** 2 + (pts[0, 1] - pts[1, 1]) ** 2 + (pts[0, 2] - pts[1, 2]) ** 2))
