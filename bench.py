@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=100, help="frames per step and per GPU")
     ap.add_argument("--pool", type=int, default=300, help="distinct frames resident per GPU (cycled)")
     ap.add_argument("--filter-mode", default="closure", choices=["closure", "reference_seeded"])
+    ap.add_argument("--radius-mode", default="bounded", choices=["bounded", "exact"],
+                    help="bounded: cell-table bounds of np.median(pdist) with exact fallback; exact: always the O(n^2) selection")
     ap.add_argument("--cpu-frames", type=int, default=4, help="frames of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -241,7 +243,8 @@ def run_b200(args):
     dl = hl_t.to(dev, non_blocking=True)
     torch.cuda.synchronize()
 
-    p, keep = nat.make_params(**stream.params(filter_mode=args.filter_mode, filter_seed=20261104))
+    p, keep = nat.make_params(**stream.params(filter_mode=args.filter_mode, filter_seed=20261104,
+                                               radius_mode=args.radius_mode))
     eng = Engine(local)
     eng.configure(p, B, N, keep)
     est = torch.cuda.ExternalStream(eng.stream, device=dev)
@@ -318,6 +321,11 @@ def run_b200(args):
     # the event pair brackets device work AND the host resolver between launches; wall is reported beside it
     frames = K * B * world
     value = frames / (ms * 1e-3)
+    # how many filtered entities of the timed frames needed the exact O(n^2) path (radius field not NaN)
+    Kent = int(p.n_entities)
+    ent = rec_np[W * B: (W + K) * B, nat.REC_HEADER: nat.REC_HEADER + nat.REC_ENTITY * Kent].reshape(-1, Kent, nat.REC_ENTITY)
+    n_filtered = int((ent[:, :, 2] >= 0).sum())
+    n_exact = int(((ent[:, :, 2] >= 0) & ~np.isnan(ent[:, :, 3])).sum())
 
     e2e = None
     if not args.no_e2e:
@@ -345,7 +353,8 @@ def run_b200(args):
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": workload_name(), "frames_per_step_per_gpu": B, "frames_timed": frames,
-                       "pool_frames_per_gpu": pool, "filter_mode": args.filter_mode,
+                       "pool_frames_per_gpu": pool, "filter_mode": args.filter_mode, "radius_mode": args.radius_mode,
+                       "filtered_entities": n_filtered, "exact_path_entities": n_exact,
                        "l2": "inputs larger than L2 (one step reads %d MB)" % (alg // 2 ** 20),
                        "parallelism": "frame-sharded x%d, one record all-gather" % world},
             "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": wall_ms / K, "esec_columns": cols,

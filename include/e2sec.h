@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define E2SEC_ABI_VERSION 1
+#define E2SEC_ABI_VERSION 2
 #define E2SEC_MAX_ENTITIES 64      /* len(total_unique_labels) upper bound                           */
 #define E2SEC_LABEL_LUT 4096       /* raw labels must be integers in [0, E2SEC_LABEL_LUT)            */
 
@@ -41,6 +41,14 @@ extern "C" {
  * filter_seed(base, frame, label_index) = (base + 1000003*frame + 7919*label_index) mod 2^32.        */
 #define E2SEC_FILTER_CLOSURE 0
 #define E2SEC_FILTER_REFERENCE_SEEDED 1
+
+/* How the flood-fill radius np.median(pdist(obj)) (:1524) is obtained in CLOSURE mode.
+ * EXACT: selection over all n(n-1)/2 float64 pair distances.  BOUNDED: guaranteed bounds lo <= median <= hi from a
+ * cell partition of the entity; when the closure provably is the same set for every radius in [lo, hi] it is taken
+ * from the cell table, otherwise that entity falls back to EXACT.  Both give the same filtered clouds; BOUNDED leaves
+ * the record's radius field NaN where it did not need the exact value.  REFERENCE_SEEDED always uses EXACT.       */
+#define E2SEC_RADIUS_EXACT 0
+#define E2SEC_RADIUS_BOUNDED 1
 
 typedef struct e2sec_ctx e2sec_ctx;
 
@@ -59,6 +67,7 @@ typedef struct e2sec_params {
     const double *ground_xyz;                    /* n_ground x 3, row-major, host                      */
     int32_t filter_mode;                         /* E2SEC_FILTER_*                                     */
     uint32_t filter_seed;                        /* base seed for REFERENCE_SEEDED                     */
+    int32_t radius_mode;                         /* E2SEC_RADIUS_*                                     */
 } e2sec_params;
 
 /* ---- records: phase-1 output, one per frame, all doubles (integers are exact in a double) --------
@@ -76,7 +85,9 @@ typedef struct e2sec_params {
  * cross table after it, K x K row-major: [a][b] = the same distance between entity a's filtered cloud in the
  *    previous kept frame and entity b's filtered cloud in this frame.  _process keeps o1/o2/o3 as the clouds
  *    of the previous frame that passed :1551 until :1669-1675 re-assigns them, so the o2 / o3 search of
- *    :1562-1658 measures exactly these cross-frame distances.                                          */
+ *    :1562-1658 measures exactly these cross-frame distances.
+ * radius bounds after it, K x 2: [lo, hi] with float32(lo) <= float32(np.median(pdist())) <= float32(hi) for every
+ *    filtered entity (lo == hi == radius where the exact value was computed), NaN for unfiltered entities.       */
 #define E2SEC_REC_HEADER 4
 #define E2SEC_REC_ENTITY 16
 #define E2SEC_FLAG_HAND_LABEL 1

@@ -16,6 +16,9 @@ FLAG_HAND_POINTS = 2
 FILTER_CLOSURE = 0
 FILTER_REFERENCE_SEEDED = 1
 FILTER_MODES = {"closure": FILTER_CLOSURE, "reference_seeded": FILTER_REFERENCE_SEEDED}
+RADIUS_EXACT = 0
+RADIUS_BOUNDED = 1
+RADIUS_MODES = {"exact": RADIUS_EXACT, "bounded": RADIUS_BOUNDED}
 
 
 class Params(C.Structure):
@@ -24,7 +27,7 @@ class Params(C.Structure):
                 ("n_replace", C.c_int32), ("replace_old", C.c_int32 * 16), ("replace_new", C.c_int32 * 16),
                 ("thresh", C.c_double), ("translation", C.c_double * 16), ("roll", C.c_double * 16),
                 ("n_ground", C.c_int32), ("ground_xyz", C.POINTER(C.c_double)),
-                ("filter_mode", C.c_int32), ("filter_seed", C.c_uint32)]
+                ("filter_mode", C.c_int32), ("filter_seed", C.c_uint32), ("radius_mode", C.c_int32)]
 
 
 class E2SecError(RuntimeError):
@@ -82,7 +85,7 @@ def ptr(a):
 
 
 def make_params(total_unique_labels, hand_label, ground_label, support_hand, thresh, translation, roll, ground,
-                replace=False, old=(), new=(), filter_mode="closure", filter_seed=0):
+                replace=False, old=(), new=(), filter_mode="closure", filter_seed=0, radius_mode="bounded"):
     """-> (Params, keepalive). Labels must be integer valued, as the MANIAC label images are."""
     tul = np.asarray(total_unique_labels, np.float64)
     if len(tul) > MAX_ENTITIES:
@@ -111,6 +114,7 @@ def make_params(total_unique_labels, hand_label, ground_label, support_hand, thr
     p.ground_xyz = g.ctypes.data_as(C.POINTER(C.c_double))
     p.filter_mode = FILTER_MODES[filter_mode] if isinstance(filter_mode, str) else int(filter_mode)
     p.filter_seed = int(filter_seed) & 0xFFFFFFFF
+    p.radius_mode = RADIUS_MODES[radius_mode] if isinstance(radius_mode, str) else int(radius_mode)
     return p, g
 
 

@@ -1,0 +1,443 @@
+// cells.cuh -- the bounded-radius route of the region filter, one CTA per (frame, entity).
+//
+// The reference filters every entity with a flood fill of radius float32(np.median(pdist(obj)))
+// (manipulation_analyser.py:1523-1525, cython_filter_new/filter_cython_new.pyx:9-93).  The median of the
+// n(n-1)/2 pair distances is O(n^2); only the CLOSURE it produces is used downstream.  This kernel partitions
+// the entity's points into cells and works on the cell table:
+//   A  seed (pyx:18-31, float32 strict minimum, first index), mean absolute deviation per axis (robust grid
+//      range, so that far outliers land in overflow cells of their own), AABB of the entity
+//   B  every point -> cell; shared-memory hash of occupied cells; per cell: count + float32 box rounded OUTWARD
+//   C  every cell pair (a <= b): all count_a * count_b point pairs have their float64 squared distance inside
+//      [dmin2(a,b), dmax2(a,b)] (box-box minimum / maximum, evaluated with the reference's own operation order
+//      (dx*dx + dy*dy) + dz*dz, which is monotone in |dx|, |dy|, |dz| under round-to-nearest) -> two weighted
+//      histograms over d^2
+//   D  rank selection: lo <= median <= hi, r_lo = float32(lo) <= float32(median) <= float32(hi) = r_hi
+//   E  cell closure at r_lo: a cell joins when its dmax to a member cell (or to the seed point) is <= r_lo --
+//      then every one of its points is reachable at every radius in [r_lo, r_hi]
+//   F  if no non-member cell has dmin <= r_hi to a member cell, no further point can be reached at any radius in
+//      [r_lo, r_hi]: the closure of the TRUE radius is exactly the union of the member cells.  Otherwise the
+//      entity is flagged ambiguous and the exact path (radius.cuh + filter.cuh) redoes it.
+//   G  stable compaction of the member points (raster order, like the exact path) + AABB / mean / count
+#pragma once
+#include "common.cuh"
+#include "filter.cuh"
+
+#define E2_CELL_THREADS 512
+#define E2_CELL_WARPS (E2_CELL_THREADS / 32)
+#define E2_CELL_MAX 1024          // occupied cells per entity
+#define E2_CELL_HASH 4096         // hash slots (power of two)
+#define E2_CELL_G 24              // cells along the largest robust extent; ids use 5 bits per axis
+#define E2_CELL_BINS 1024         // histogram bins over d^2
+#define E2_CELL_EMPTY 0xffffffffu
+
+struct CellSmem {
+    union {
+        unsigned keys[E2_CELL_HASH];          // B: cell ids
+        u64 hist[2][E2_CELL_BINS];            // C, D: weights by dmin2 / dmax2 bin
+    };
+    unsigned short cidx[E2_CELL_HASH];        // slot -> compact cell index
+    unsigned cnt[E2_CELL_MAX];
+    unsigned box[6][E2_CELL_MAX];             // lo x,y,z, hi x,y,z: order-preserving uint of a float during B, floats after
+    unsigned char member[E2_CELL_MAX];
+    unsigned short front[2][E2_CELL_MAX];
+    double red[9][E2_CELL_WARPS];
+    float best_d[E2_CELL_WARPS];
+    int best_i[E2_CELL_WARPS];
+    unsigned wcnt[E2_CELL_WARPS];
+    unsigned m, n_front, n_new, overflow, amb;
+    int seed;
+    double lo[3], inv_c, scale, d2max, t_lo, t_hi, r_lo, r_hi, seedp[3];
+};
+
+__device__ __forceinline__ unsigned f32_ord(float f)
+{
+    unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord_f32(unsigned u)
+{
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+__device__ __forceinline__ double next_down(double v) { return v > 0.0 ? __longlong_as_double(__double_as_longlong(v) - 1) : 0.0; }
+__device__ __forceinline__ double next_up(double v) { return __longlong_as_double(__double_as_longlong(v) + 1); }
+
+__device__ __forceinline__ int cell_bin(double d2, double scale)
+{
+    double t = d2 * scale;
+    return t >= (double)(E2_CELL_BINS - 1) ? E2_CELL_BINS - 1 : (int)t;
+}
+
+// box-box squared distance bounds from float boxes, float64 arithmetic in pdist's operation order
+__device__ __forceinline__ void cell_pair_d2(const CellSmem &s, int a, int b, double &dmin2, double &dmax2)
+{
+    double g[3], f[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double alo = (double)__uint_as_float(s.box[k][a]), ahi = (double)__uint_as_float(s.box[3 + k][a]);
+        const double blo = (double)__uint_as_float(s.box[k][b]), bhi = (double)__uint_as_float(s.box[3 + k][b]);
+        g[k] = fmax(fmax(alo - bhi, blo - ahi), 0.0);
+        f[k] = fmax(ahi - blo, bhi - alo);
+    }
+    dmin2 = (g[0] * g[0] + g[1] * g[1]) + g[2] * g[2];
+    dmax2 = (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
+}
+// the same between a point and a box
+__device__ __forceinline__ double cell_point_dmax2(const CellSmem &s, const double *p, int b)
+{
+    double f[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double blo = (double)__uint_as_float(s.box[k][b]), bhi = (double)__uint_as_float(s.box[3 + k][b]);
+        f[k] = fmax(p[k] - blo, bhi - p[k]);
+    }
+    return (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
+}
+
+// block-wide reductions over E2_CELL_THREADS threads; `slot` picks a row of s.red
+__device__ __forceinline__ double cell_block_sum(CellSmem &s, int slot, double v)
+{
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) s.red[slot][threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+    for (int w = 0; w < E2_CELL_WARPS; ++w) t += s.red[slot][w];
+    return t;
+}
+__device__ __forceinline__ double cell_block_min(CellSmem &s, int slot, double v)
+{
+    v = warp_min_d(v);
+    if ((threadIdx.x & 31) == 0) s.red[slot][threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = s.red[slot][0];
+    for (int w = 1; w < E2_CELL_WARPS; ++w) t = fmin(t, s.red[slot][w]);
+    return t;
+}
+__device__ __forceinline__ double cell_block_max(CellSmem &s, int slot, double v)
+{
+    v = warp_max_d(v);
+    if ((threadIdx.x & 31) == 0) s.red[slot][threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = s.red[slot][0];
+    for (int w = 1; w < E2_CELL_WARPS; ++w) t = fmax(t, s.red[slot][w]);
+    return t;
+}
+
+// One warp finds the bin holding 0-based rank k of a weighted histogram (cumulative weight > k). Returns
+// E2_CELL_BINS - 1 when the rank lies beyond the total (cannot happen: the weights sum to the pair count).
+__device__ __forceinline__ int cell_rank_bin(const u64 *h, u64 k)
+{
+    const int lane = threadIdx.x & 31;
+    const int per = E2_CELL_BINS / 32;
+    u64 mine = 0;
+    for (int j = 0; j < per; ++j) mine += h[lane * per + j];
+    u64 incl = mine;
+    for (int o = 1; o < 32; o <<= 1) { u64 t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    const unsigned has = __ballot_sync(0xffffffffu, incl > k);
+    int bin = E2_CELL_BINS - 1;
+    if (has) {
+        const int L = __ffs(has) - 1;
+        const u64 before = __shfl_sync(0xffffffffu, incl - mine, L);
+        if (lane == L) {
+            u64 acc = before;
+            for (int j = 0; j < per; ++j) {
+                acc += h[lane * per + j];
+                if (acc > k) { bin = lane * per + j; break; }
+            }
+        }
+        bin = __shfl_sync(0xffffffffu, bin, L);
+    }
+    return bin;
+}
+
+extern __shared__ __align__(16) unsigned char cell_smem_raw[];
+
+// grid F*K CTAs of E2_CELL_THREADS. Needs d.med (axis_median_kernel). Writes, for every filtered entity that it can
+// decide: seed_pos, flist, n_list, aabb, mean, rad_lo / rad_hi, amb = 0; for the others amb = 1 (exact path follows).
+// Entities that are not stored or have <= 3 points are finished here too (raw cloud, :1543-1546).
+__global__ void __launch_bounds__(E2_CELL_THREADS) cell_filter_kernel(Dev d)
+{
+    CellSmem &s = *reinterpret_cast<CellSmem *>(cell_smem_raw);
+    const int fe = blockIdx.x, f = fe / d.K;
+    const int off = d.ent_off[fe], n = d.ent_raw[fe];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double NaN = __longlong_as_double(0x7ff8000000000000ll);
+    if (tid == 0) { d.amb[fe] = 0; d.rad_lo[fe] = NaN; d.rad_hi[fe] = NaN; d.radius[fe] = NaN; }
+    double *aabb = d.aabb + (size_t)fe * 6, *mean = d.mean + (size_t)fe * 3;
+    if (off < 0 || n == 0) {
+        if (tid == 0) { d.n_list[fe] = 0; d.seed_pos[fe] = -1; }
+        if (tid < 6) aabb[tid] = 0.0;          // Open3D: an empty cloud has a zero box and a zero centre
+        if (tid < 3) mean[tid] = 0.0;
+        return;
+    }
+    const size_t pb = (size_t)f * d.cap + off;
+    const double *X = d.px + pb, *Y = d.py + pb, *Z = d.pz + pb;
+    unsigned *flist = d.flist + pb;
+    unsigned short *pcell = d.pcell + pb;
+    const bool filtered = n > 3;               // :1520
+
+    if (filtered) {
+        // ---- A: seed, mean absolute deviation, AABB ------------------------------------------------------------
+        const double cx = d.med[(size_t)fe * 3], cy = d.med[(size_t)fe * 3 + 1], cz = d.med[(size_t)fe * 3 + 2];
+        float bd = 50000.0f;
+        int bi = 0x7fffffff;
+        double ad[3] = {0.0, 0.0, 0.0}, mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+        for (int i = tid; i < n; i += E2_CELL_THREADS) {
+            const double x = X[i], y = Y[i], z = Z[i];
+            const float dt = (float)sqrt(dist2(x, y, z, cx, cy, cz));
+            if (dt < bd) { bd = dt; bi = i; }
+            ad[0] += fabs(x - cx); ad[1] += fabs(y - cy); ad[2] += fabs(z - cz);
+            mn[0] = fmin(mn[0], x); mx[0] = fmax(mx[0], x);
+            mn[1] = fmin(mn[1], y); mx[1] = fmax(mx[1], y);
+            mn[2] = fmin(mn[2], z); mx[2] = fmax(mx[2], z);
+        }
+        for (int o = 16; o; o >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, bd, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; }
+        }
+        if (lane == 0) { s.best_d[warp] = bd; s.best_i[warp] = bi; }
+        double ext2 = 0.0, half[3];
+        for (int k = 0; k < 3; ++k) {
+            const double a = cell_block_sum(s, k, ad[k]);
+            const double l = cell_block_min(s, 3 + k, mn[k]), h = cell_block_max(s, 6 + k, mx[k]);
+            ext2 += (h - l) * (h - l);
+            half[k] = 3.5 * (a / (double)n);
+        }
+        if (tid == 0) {
+            for (int w = 1; w < E2_CELL_WARPS; ++w)
+                if (s.best_d[w] < bd || (s.best_d[w] == bd && s.best_i[w] < bi)) { bd = s.best_d[w]; bi = s.best_i[w]; }
+            s.seed = (bi == 0x7fffffff) ? 0 : bi;
+            double c = fmax(fmax(half[0], half[1]), half[2]) * 2.0 / (double)E2_CELL_G;
+            if (!(c > 1e-300) || !(c < 1e300)) c = 1.0;          // degenerate cloud: one cell
+            s.inv_c = 1.0 / c;
+            s.lo[0] = cx - half[0]; s.lo[1] = cy - half[1]; s.lo[2] = cz - half[2];
+            double top = ext2 * 1.000001;                        // d2 of any pair <= squared AABB diagonal (+ slack)
+            if (!(top > 0.0) || !(top < 1e300)) top = 1.0;
+            s.d2max = top;
+            s.scale = (double)E2_CELL_BINS / top;
+            s.m = 0; s.overflow = 0; s.amb = 0;
+        }
+        for (int i = tid; i < E2_CELL_HASH; i += E2_CELL_THREADS) s.keys[i] = E2_CELL_EMPTY;
+        __syncthreads();
+
+        // ---- B1: insert the cell ids ------------------------------------------------------------------------------
+        const double l0 = s.lo[0], l1 = s.lo[1], l2 = s.lo[2], inv_c = s.inv_c;
+        for (int i = tid; i < n; i += E2_CELL_THREADS) {
+            const double tx = fmin(fmax(floor((X[i] - l0) * inv_c), -1.0), (double)E2_CELL_G);
+            const double ty = fmin(fmax(floor((Y[i] - l1) * inv_c), -1.0), (double)E2_CELL_G);
+            const double tz = fmin(fmax(floor((Z[i] - l2) * inv_c), -1.0), (double)E2_CELL_G);
+            const unsigned id = ((unsigned)((int)tx + 1) << 10) | ((unsigned)((int)ty + 1) << 5) | (unsigned)((int)tz + 1);
+            unsigned slot = (id * 2654435761u) >> 20;
+            int probes = 0;
+            for (;;) {
+                const unsigned prev = atomicCAS(&s.keys[slot], E2_CELL_EMPTY, id);
+                if (prev == E2_CELL_EMPTY || prev == id) break;
+                slot = (slot + 1) & (E2_CELL_HASH - 1);
+                if (++probes >= E2_CELL_HASH) { s.overflow = 1; break; }
+            }
+            pcell[i] = (unsigned short)slot;
+        }
+        __syncthreads();
+        // ---- B2: compact indices in slot order ------------------------------------------------------------------
+        {
+            const int per = E2_CELL_HASH / E2_CELL_THREADS;       // 8 consecutive slots per thread
+            unsigned occ = 0;
+            for (int j = 0; j < per; ++j) occ += (s.keys[tid * per + j] != E2_CELL_EMPTY);
+            unsigned incl = occ;
+            for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+            if (lane == 31) s.wcnt[warp] = incl;
+            __syncthreads();
+            unsigned base = incl - occ;
+            for (int w = 0; w < warp; ++w) base += s.wcnt[w];
+            for (int j = 0; j < per; ++j)
+                if (s.keys[tid * per + j] != E2_CELL_EMPTY) { s.cidx[tid * per + j] = (unsigned short)(base < E2_CELL_MAX ? base : 0); ++base; }
+            if (tid == E2_CELL_THREADS - 1) { s.m = base; if (base > E2_CELL_MAX) s.overflow = 1; }
+        }
+        for (int i = tid; i < E2_CELL_MAX; i += E2_CELL_THREADS) {
+            s.cnt[i] = 0;
+            s.member[i] = 0;
+            for (int k = 0; k < 3; ++k) { s.box[k][i] = 0xffffffffu; s.box[3 + k][i] = 0u; }
+        }
+        __syncthreads();
+    }
+
+    bool decided = true;
+    if (filtered && !s.overflow) {
+        // ---- B3: per-cell count and outward-rounded float box (warp-aggregated shared atomics) -----------------
+        for (int i = tid; i < 2 * E2_CELL_BINS; i += E2_CELL_THREADS) (&s.hist[0][0])[i] = 0;      // keys are dead now
+        for (int base = 0; base < n; base += E2_CELL_THREADS) {
+            const int i = base + tid;
+            const bool live = i < n;
+            unsigned c = 0xffffffffu;
+            unsigned v[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+            if (live) {
+                c = s.cidx[pcell[i]];
+                pcell[i] = (unsigned short)c;
+                const double x = X[i], y = Y[i], z = Z[i];
+                v[0] = f32_ord(__double2float_rd(x)); v[1] = f32_ord(__double2float_rd(y)); v[2] = f32_ord(__double2float_rd(z));
+                v[3] = f32_ord(__double2float_ru(x)); v[4] = f32_ord(__double2float_ru(y)); v[5] = f32_ord(__double2float_ru(z));
+            }
+            unsigned todo = __ballot_sync(0xffffffffu, live);
+            while (todo) {
+                const int leader = __ffs(todo) - 1;
+                const unsigned cl = __shfl_sync(0xffffffffu, c, leader);
+                const unsigned mask = __ballot_sync(0xffffffffu, live && c == cl);
+                if (live && c == cl) {
+                    unsigned r[6];
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) { r[k] = __reduce_min_sync(mask, v[k]); r[3 + k] = __reduce_max_sync(mask, v[3 + k]); }
+                    if (lane == leader) {
+                        atomicAdd(&s.cnt[cl], (unsigned)__popc(mask));
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) { atomicMin(&s.box[k][cl], r[k]); atomicMax(&s.box[3 + k][cl], r[3 + k]); }
+                    }
+                }
+                todo &= ~mask;
+            }
+        }
+        __syncthreads();
+        const int m = (int)s.m;
+        for (int i = tid; i < m; i += E2_CELL_THREADS)
+            for (int k = 0; k < 6; ++k) s.box[k][i] = __float_as_uint(ord_f32(s.box[k][i]));
+        __syncthreads();
+
+        // ---- C: cell-pair histograms over d^2 ----------------------------------------------------------------------
+        const double scale = s.scale;
+        for (int a = warp; a < m; a += E2_CELL_WARPS) {
+            const u64 ca = s.cnt[a];
+            for (int b = a + lane; b < m; b += 32) {
+                double dmin2, dmax2;
+                cell_pair_d2(s, a, b, dmin2, dmax2);
+                const u64 w = (a == b) ? ca * (ca - 1) / 2 : ca * (u64)s.cnt[b];
+                if (a == b) dmin2 = 0.0;
+                if (w) {
+                    atomicAdd(&s.hist[0][cell_bin(dmin2, scale)], w);
+                    atomicAdd(&s.hist[1][cell_bin(dmax2, scale)], w);
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- D: lo <= median <= hi ---------------------------------------------------------------------------------
+        if (warp < 2) {
+            const u64 P = (u64)n * (u64)(n - 1) / 2;
+            const u64 k2 = P / 2, k1 = (P & 1) ? k2 : k2 - 1;
+            const int B = cell_rank_bin(s.hist[warp], warp == 0 ? k1 : k2);
+            if (lane == 0) {
+                if (warp == 0) {
+                    double lo2 = (double)B / scale;
+                    while (lo2 > 0.0 && cell_bin(lo2, scale) >= B) lo2 = next_down(lo2);      // bin(lo2) < B <= bin(true d2)
+                    if (B == 0) lo2 = 0.0;
+                    const double r = (double)(float)sqrt(lo2);
+                    s.r_lo = r;
+                    s.t_lo = sq_threshold(r);
+                } else {
+                    double hi2;
+                    if (B >= E2_CELL_BINS - 1) hi2 = s.d2max;
+                    else {
+                        hi2 = (double)(B + 1) / scale;
+                        while (cell_bin(hi2, scale) <= B) hi2 = next_up(hi2);                   // bin(hi2) > B >= bin(true d2)
+                    }
+                    const double r = (double)(float)sqrt(hi2);
+                    s.r_hi = r;
+                    s.t_hi = sq_threshold(r);
+                }
+            }
+        }
+        if (tid == 64) { s.seedp[0] = X[s.seed]; s.seedp[1] = Y[s.seed]; s.seedp[2] = Z[s.seed]; s.n_front = 0; s.n_new = 0; }
+        __syncthreads();
+
+        // ---- E: cell closure at r_lo ---------------------------------------------------------------------------------
+        const double t_lo = s.t_lo, t_hi = s.t_hi;
+        {
+            const double sp[3] = {s.seedp[0], s.seedp[1], s.seedp[2]};
+            for (int b = tid; b < m; b += E2_CELL_THREADS)
+                if (cell_point_dmax2(s, sp, b) <= t_lo) { s.member[b] = 1; s.front[0][atomicAdd(&s.n_new, 1u)] = (unsigned short)b; }
+        }
+        __syncthreads();
+        int cur = 0;
+        for (;;) {
+            const unsigned nf = s.n_new;
+            __syncthreads();
+            if (nf == 0) break;
+            if (tid == 0) s.n_new = 0;
+            __syncthreads();
+            for (int b = tid; b < m; b += E2_CELL_THREADS) {
+                if (s.member[b]) continue;
+                for (unsigned q = 0; q < nf; ++q) {
+                    double dmin2, dmax2;
+                    cell_pair_d2(s, (int)s.front[cur][q], b, dmin2, dmax2);
+                    if (dmax2 <= t_lo) { s.member[b] = 1; s.front[cur ^ 1][atomicAdd(&s.n_new, 1u)] = (unsigned short)b; break; }
+                }
+            }
+            cur ^= 1;
+            __syncthreads();
+        }
+        // ---- F: can anything else be reached at r_hi? ------------------------------------------------------------
+        if (tid == 0 && !s.member[pcell[s.seed]]) s.amb = 1;      // the seed's own cell must be certain
+        for (int b = warp; b < m; b += E2_CELL_WARPS) {
+            if (s.member[b]) continue;
+            bool hit = false;
+            for (int a = lane; a < m && !hit; a += 32) {
+                if (!s.member[a]) continue;
+                double dmin2, dmax2;
+                cell_pair_d2(s, a, b, dmin2, dmax2);
+                hit = dmin2 <= t_hi;
+            }
+            if (__any_sync(0xffffffffu, hit) && lane == 0) s.amb = 1;
+        }
+        __syncthreads();
+        decided = !s.amb;
+    } else if (filtered) {
+        decided = false;                                           // too many cells for the table
+    }
+    if (!decided) {
+        if (tid == 0) d.amb[fe] = 1;
+        return;
+    }
+
+    // ---- G: stable compaction of the members + AABB / mean / count (unfiltered clouds: every point) ------------
+    double sum[3] = {0.0, 0.0, 0.0}, mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+    unsigned run = 0;
+    for (int base = 0; base < n; base += E2_CELL_THREADS) {
+        const int i = base + tid;
+        const bool mem = (i < n) && (!filtered || s.member[pcell[i]]);
+        const unsigned bal = __ballot_sync(0xffffffffu, mem);
+        if (lane == 0) s.wcnt[warp] = __popc(bal);
+        __syncthreads();
+        unsigned before = run, tot = 0;
+        for (int w = 0; w < E2_CELL_WARPS; ++w) { const unsigned c = s.wcnt[w]; if (w < warp) before += c; tot += c; }
+        if (mem) {
+            flist[before + __popc(bal & ((1u << lane) - 1u))] = (unsigned)i;
+            const double x = X[i], y = Y[i], z = Z[i];
+            sum[0] += x; sum[1] += y; sum[2] += z;
+            mn[0] = fmin(mn[0], x); mx[0] = fmax(mx[0], x);
+            mn[1] = fmin(mn[1], y); mx[1] = fmax(mx[1], y);
+            mn[2] = fmin(mn[2], z); mx[2] = fmax(mx[2], z);
+        }
+        run += tot;
+        __syncthreads();
+    }
+    double tot[3], l[3], h[3];
+    for (int k = 0; k < 3; ++k) {
+        tot[k] = cell_block_sum(s, k, sum[k]);
+        l[k] = cell_block_min(s, 3 + k, mn[k]);
+        h[k] = cell_block_max(s, 6 + k, mx[k]);
+    }
+    if (tid == 0) {
+        d.n_list[fe] = (int)run;
+        d.seed_pos[fe] = filtered ? s.seed : -1;
+        double cntp = (double)run;
+        if (filtered) {                                            // dicti[0] = first_point (pyx:48): the seed counts twice
+            tot[0] += X[s.seed]; tot[1] += Y[s.seed]; tot[2] += Z[s.seed];
+            cntp += 1.0;
+            d.rad_lo[fe] = s.r_lo;
+            d.rad_hi[fe] = s.r_hi;
+        }
+        for (int k = 0; k < 3; ++k) {
+            aabb[k] = run ? l[k] : 0.0;
+            aabb[3 + k] = run ? h[k] : 0.0;
+            mean[k] = run ? tot[k] / cntp : 0.0;
+        }
+    }
+}

@@ -40,6 +40,7 @@ struct Dev {
     int hand_label;
     int n_ground;
     int filter_mode;
+    int radius_mode;                  // E2SEC_RADIUS_* actually in force (REFERENCE_SEEDED forces EXACT)
     unsigned filter_seed;
     double thresh;
     double T[16], R[16];
@@ -75,6 +76,10 @@ struct Dev {
     unsigned *front_a, *front_b;      // F x cap     frontier lists (positions inside the entity)
     unsigned *flist;                  // F x cap     filtered cloud as positions, output order (seed duplicate excluded)
     int *n_list;                      // F x K       entries of flist
+    // bounded-radius route (cells.cuh)
+    unsigned short *pcell;            // F x cap     cell of each stored point (hash slot, then compact index)
+    double *rad_lo, *rad_hi;          // F x K       float32-rounded bounds of the median pair distance
+    int *amb;                         // F x K       1 = the cell table could not decide: the exact path runs
     // stats + pairs
     double *aabb;                     // F x K x 6
     double *mean;                     // F x K x 3

@@ -11,6 +11,7 @@
 #include "select.cuh"
 #include "radius.cuh"
 #include "filter.cuh"
+#include "cells.cuh"
 #include "pairs.cuh"
 
 #define E2_MAX_REFINE 6        // histogram rounds launched per batch (each narrows the key interval 256x)
@@ -36,7 +37,7 @@ struct e2sec_ctx {
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
-        frame_used, prev_slot, prev_id, halo_info;
+        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb;
     int map_cfg[4] = {0, 0, 0, 0};
     int64_t launches = 0;
     cudaEvent_t ev[8];
@@ -74,7 +75,7 @@ extern "C" int e2sec_abi_version(void) { return E2SEC_ABI_VERSION; }
 
 extern "C" size_t e2sec_record_doubles(int32_t K)
 {
-    return (size_t)E2SEC_REC_HEADER + (size_t)E2SEC_REC_ENTITY * K + (size_t)(K + 1) * (K + 1) + (size_t)K * K;
+    return (size_t)E2SEC_REC_HEADER + (size_t)E2SEC_REC_ENTITY * K + (size_t)(K + 1) * (K + 1) + (size_t)K * K + (size_t)2 * K;
 }
 
 extern "C" const char *e2sec_last_error(const e2sec_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
@@ -100,6 +101,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     ctx->ev_valid = true;
     cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double)));
+    cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
     memset(&ctx->d, 0, sizeof(Dev));
     ctx->bufs = {&ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
@@ -107,7 +109,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
                  &ctx->gz, &ctx->pair_key, &ctx->records, &ctx->error, &ctx->plan_off, &ctx->plan_total,
                  &ctx->below_acc, &ctx->min_above, &ctx->single_count, &ctx->cross_key, &ctx->frame_used, &ctx->prev_slot,
-                 &ctx->prev_id, &ctx->halo_info};
+                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb};
     *out = ctx;
     return E2SEC_OK;
 }
@@ -191,6 +193,10 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     rc |= ensure(ctx, ctx->below_acc, FK * sizeof(u64));
     rc |= ensure(ctx, ctx->min_above, FK * sizeof(u64));
     rc |= ensure(ctx, ctx->single_count, FK * sizeof(u64));
+    rc |= ensure(ctx, ctx->pcell, cap * sizeof(unsigned short));
+    rc |= ensure(ctx, ctx->rad_lo, FK * sizeof(double));
+    rc |= ensure(ctx, ctx->rad_hi, FK * sizeof(double));
+    rc |= ensure(ctx, ctx->amb, FK * sizeof(int));
     if (rc) return E2SEC_ERR_CUDA;
     ctx->maxF = F;
     ctx->N = N;
@@ -230,6 +236,10 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     d.pair_key = (u64 *)ctx->pair_key.p;
     d.records = (double *)ctx->records.p;
     d.error = (int *)ctx->error.p;
+    d.pcell = (unsigned short *)ctx->pcell.p;
+    d.rad_lo = (double *)ctx->rad_lo.p;
+    d.rad_hi = (double *)ctx->rad_hi.p;
+    d.amb = (int *)ctx->amb.p;
     return E2SEC_OK;
 }
 
@@ -295,6 +305,8 @@ extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t ma
     d.n_ground = G;
     d.filter_mode = p->filter_mode;
     d.filter_seed = p->filter_seed;
+    if (p->radius_mode != E2SEC_RADIUS_EXACT && p->radius_mode != E2SEC_RADIUS_BOUNDED) return fail(ctx, E2SEC_ERR_ARG, "bad radius_mode");
+    d.radius_mode = (p->filter_mode == E2SEC_FILTER_CLOSURE) ? p->radius_mode : E2SEC_RADIUS_EXACT;
     d.thresh = p->thresh;
     memcpy(d.T, p->translation, sizeof(d.T));
     memcpy(d.R, p->roll, sizeof(d.R));
@@ -334,6 +346,9 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
     u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
     if (need_median) { axis_median_kernel<<<dim3(3, FK), E2_SEL_THREADS, 0, st>>>(d); LAUNCHED(); }
     cudaEventRecord(ctx->ev[2], st);
+    if (d.radius_mode == E2SEC_RADIUS_BOUNDED) {
+        cell_filter_kernel<<<FK, E2_CELL_THREADS, sizeof(CellSmem), st>>>(d); LAUNCHED();
+    }
     if (need_radius) {
         CU(cudaMemsetAsync(below_acc, 0, sizeof(u64) * FK, st));
         CU(cudaMemsetAsync(single, 0, sizeof(u64) * FK, st));
@@ -465,6 +480,7 @@ static int load_clouds(e2sec_ctx *ctx, Dev &d, int ne, const double *const *pts,
     }
     if (ctx->halo_info.p) CU(cudaMemsetAsync(ctx->halo_info.p, 0, 4 * sizeof(int), ctx->stream));   // the scratch overwrites the halo
     d = ctx->d;
+    d.radius_mode = E2SEC_RADIUS_EXACT;       // operators work at the reference's own seams: exact values
     d.F = 1;
     d.K = K;
     d.cap = (int)ctx->cap_total;

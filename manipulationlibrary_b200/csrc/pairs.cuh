@@ -19,6 +19,7 @@ __global__ void __launch_bounds__(E2_STATS_THREADS) entity_stats_kernel(Dev d)
     const int fe = blockIdx.x, f = fe / d.K;
     const int off = d.ent_off[fe];
     const int tid = threadIdx.x;
+    if (d.radius_mode == E2SEC_RADIUS_BOUNDED && !d.amb[fe]) return;      // cell_filter_kernel wrote the stats
     double *aabb = d.aabb + (size_t)fe * 6, *mean = d.mean + (size_t)fe * 3;
     const int m = (off < 0) ? 0 : d.n_list[fe];
     if (m == 0) {
@@ -269,5 +270,14 @@ __global__ void assemble_kernel(Dev d)
         const int a = i / K, b = i - a * K;
         const bool ok = a != b && a != 0 && b != 0 && a != d.ground_idx && b != d.ground_idx;
         ct[i] = ok ? sqrt(key2d(d.cross_key[(size_t)f * K * K + i])) : INF;
+    }
+    double *rb = ct + K * K;
+    for (int e = threadIdx.x; e < K; e += blockDim.x) {
+        const int fe = f * K + e;
+        const bool filt = d.ent_off[fe] >= 0 && d.seed_pos[fe] >= 0;
+        const double r = d.radius[fe];
+        const bool exact = filt && !(r != r);
+        rb[2 * e] = !filt ? NaN : exact ? r : d.rad_lo[fe];
+        rb[2 * e + 1] = !filt ? NaN : exact ? r : d.rad_hi[fe];
     }
 }

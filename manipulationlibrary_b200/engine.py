@@ -211,3 +211,9 @@ def rec_pairs(rec, K):
 def rec_cross(rec, K):
     o = nat.REC_HEADER + nat.REC_ENTITY * K + (K + 1) * (K + 1)
     return rec[o: o + K * K].reshape(K, K)
+
+
+def rec_radius_bounds(rec, K):
+    """(K, 2) [lo, hi] with float32(lo) <= float32(np.median(pdist())) <= float32(hi); NaN rows: not filtered."""
+    o = nat.REC_HEADER + nat.REC_ENTITY * K + (K + 1) * (K + 1) + K * K
+    return rec[o: o + 2 * K].reshape(K, 2)

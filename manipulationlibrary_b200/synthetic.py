@@ -251,9 +251,9 @@ class SyntheticStream:
             xyz[i], lab[i] = self.frame(f)
         return xyz, lab
 
-    def params(self, filter_mode="closure", filter_seed=0):
+    def params(self, filter_mode="closure", filter_seed=0, radius_mode="bounded"):
         """Keyword arguments of _native.make_params for this stream."""
         return dict(total_unique_labels=self.total_unique_labels, hand_label=self.hand_label,
                     ground_label=self.ground_label, support_hand=None, thresh=self.thresh,
                     translation=self.translation, roll=self.roll, ground=self.ground,
-                    filter_mode=filter_mode, filter_seed=filter_seed)
+                    filter_mode=filter_mode, filter_seed=filter_seed, radius_mode=radius_mode)

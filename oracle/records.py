@@ -13,7 +13,7 @@ REC_HEADER, REC_ENTITY = 4, 16
 
 
 def record_doubles(K):
-    return REC_HEADER + REC_ENTITY * K + (K + 1) * (K + 1) + K * K
+    return REC_HEADER + REC_ENTITY * K + (K + 1) * (K + 1) + K * K + 2 * K
 
 
 class RecordOracle:
@@ -75,7 +75,10 @@ class RecordOracle:
                         ct[a, b] = self._md(self.prev[1][a], filtered[b])
         off = REC_HEADER + REC_ENTITY * K
         rec[off: off + W * W] = pt.reshape(-1)
-        rec[off + W * W:] = ct.reshape(-1)
+        rec[off + W * W: off + W * W + K * K] = ct.reshape(-1)
+        rb = rec[off + W * W + K * K:].reshape(K, 2)          # radius bounds: the oracle knows the exact value
+        for e in range(K):
+            rb[e] = det[e]["radius"] if (stored[e] and det[e]["filtered"]) else np.nan
         if flags == 3:
             self.prev = (frame, filtered)
         return rec

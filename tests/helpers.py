@@ -46,3 +46,17 @@ class Pushing06Frames:
             # the raw label image held the hand label but every such point was NaN: keep the label visible
             labels[0] = 11
         return full, labels
+
+
+REC_HEADER, REC_ENTITY = 4, 16
+
+
+def upgrade_records(records, K):
+    """Goldens written before ABI 2 lack the radius-bounds tail (K x 2): append lo = hi = the exact radius."""
+    records = np.asarray(records)
+    old = REC_HEADER + REC_ENTITY * K + (K + 1) * (K + 1) + K * K
+    if records.shape[1] == old + 2 * K:
+        return records
+    assert records.shape[1] == old, records.shape
+    rad = records[:, REC_HEADER + 3: REC_HEADER + REC_ENTITY * K: REC_ENTITY]
+    return np.concatenate([records, np.repeat(rad, 2, axis=1)], axis=1)
