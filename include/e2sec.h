@@ -82,8 +82,9 @@ typedef struct e2sec_params {
  * pair table at record[4 + 16*K ..], (K+1) x (K+1) row-major, index K = the ground cloud:
  *    exact minimum point-to-point distance when it is < thresh; otherwise some value >= thresh
  *    (+inf when either cloud is empty).  Entities 0 (border) and ground_label's own index hold +inf.
- * cross table after it, K x K row-major: [a][b] = the same distance between entity a's filtered cloud in the
- *    previous kept frame and entity b's filtered cloud in this frame.  _process keeps o1/o2/o3 as the clouds
+ * cross table after it, K x K row-major: [a][b] = contact flag between entity a's filtered cloud in the previous
+ *    kept frame and entity b's filtered cloud in this frame: 0.0 when their minimum distance is < thresh, otherwise
+ *    some value >= thresh (+inf when either is empty; only `< thresh` is ever asked of these, :1600-1653).  _process keeps o1/o2/o3 as the clouds
  *    of the previous frame that passed :1551 until :1669-1675 re-assigns them, so the o2 / o3 search of
  *    :1562-1658 measures exactly these cross-frame distances.
  * radius bounds after it, K x 2: [lo, hi] with float32(lo) <= float32(np.median(pdist())) <= float32(hi) for every

@@ -124,7 +124,8 @@ __device__ __forceinline__ double cell_block_max(CellSmem &s, int slot, double v
 
 // One warp finds the bin holding 0-based rank k of a weighted histogram (cumulative weight > k). Returns
 // E2_CELL_BINS - 1 when the rank lies beyond the total (cannot happen: the weights sum to the pair count).
-__device__ __forceinline__ int cell_rank_bin(const u64 *h, u64 k)
+template <class T>
+__device__ __forceinline__ int cell_rank_bin(const T *h, u64 k)
 {
     const int lane = threadIdx.x & 31;
     const int per = E2_CELL_BINS / 32;
@@ -154,7 +155,7 @@ extern __shared__ __align__(16) unsigned char cell_smem_raw[];
 // grid F*K CTAs of E2_CELL_THREADS. Needs d.med (axis_median_kernel). Writes, for every filtered entity that it can
 // decide: seed_pos, flist, n_list, aabb, mean, rad_lo / rad_hi, amb = 0; for the others amb = 1 (exact path follows).
 // Entities that are not stored or have <= 3 points are finished here too (raw cloud, :1543-1546).
-__global__ void __launch_bounds__(E2_CELL_THREADS) cell_filter_kernel(Dev d)
+__global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
 {
     CellSmem &s = *reinterpret_cast<CellSmem *>(cell_smem_raw);
     const int fe = blockIdx.x, f = fe / d.K;
@@ -302,7 +303,13 @@ __global__ void __launch_bounds__(E2_CELL_THREADS) cell_filter_kernel(Dev d)
         __syncthreads();
 
         // ---- C: cell-pair histograms over d^2 ----------------------------------------------------------------------
+        // Weights are pair counts: while the entity has fewer than 2^32 pairs the bins are 32-bit words (native shared
+        // atomics; a 64-bit shared atomicAdd is a compare-and-swap loop and collapses under the contention of the
+        // dmin2 = 0 bin), otherwise 64-bit.
         const double scale = s.scale;
+        const u64 P = (u64)n * (u64)(n - 1) / 2;
+        const bool small = P < 0x100000000ull;
+        unsigned *h32 = reinterpret_cast<unsigned *>(&s.hist[0][0]);
         for (int a = warp; a < m; a += E2_CELL_WARPS) {
             const u64 ca = s.cnt[a];
             for (int b = a + lane; b < m; b += 32) {
@@ -311,8 +318,9 @@ __global__ void __launch_bounds__(E2_CELL_THREADS) cell_filter_kernel(Dev d)
                 const u64 w = (a == b) ? ca * (ca - 1) / 2 : ca * (u64)s.cnt[b];
                 if (a == b) dmin2 = 0.0;
                 if (w) {
-                    atomicAdd(&s.hist[0][cell_bin(dmin2, scale)], w);
-                    atomicAdd(&s.hist[1][cell_bin(dmax2, scale)], w);
+                    const int b0 = cell_bin(dmin2, scale), b1 = cell_bin(dmax2, scale);
+                    if (small) { atomicAdd(&h32[b0], (unsigned)w); atomicAdd(&h32[E2_CELL_BINS + b1], (unsigned)w); }
+                    else { atomicAdd(&s.hist[0][b0], w); atomicAdd(&s.hist[1][b1], w); }
                 }
             }
         }
@@ -320,9 +328,9 @@ __global__ void __launch_bounds__(E2_CELL_THREADS) cell_filter_kernel(Dev d)
 
         // ---- D: lo <= median <= hi ---------------------------------------------------------------------------------
         if (warp < 2) {
-            const u64 P = (u64)n * (u64)(n - 1) / 2;
             const u64 k2 = P / 2, k1 = (P & 1) ? k2 : k2 - 1;
-            const int B = cell_rank_bin(s.hist[warp], warp == 0 ? k1 : k2);
+            const int B = small ? cell_rank_bin(h32 + warp * E2_CELL_BINS, warp == 0 ? k1 : k2)
+                                : cell_rank_bin(s.hist[warp], warp == 0 ? k1 : k2);
             if (lane == 0) {
                 if (warp == 0) {
                     double lo2 = (double)B / scale;

@@ -1,0 +1,289 @@
+// contact.cuh -- all-pairs touching distances, work-list version (replaces one-CTA-per-pair for the per-frame pass).
+//
+//   np.min(a.compute_point_cloud_distance(b)) (manipulation_analyser.py:397-484 T/N rows, :1570-1653 o1/o2/o3 search)
+//   for every pair of stored entities of a frame, every (entity, ground) pair and every cross pair (entity a of the
+//   previous kept frame, entity b of this frame).
+//
+//   contact_plan_kernel  one thread per (frame, pair slot): empty clouds -> +inf; boxes further apart than thresh -> the
+//                        box gap (a value >= thresh, which is all the relation rows need); otherwise the slot is
+//                        initialised to max(gap, thresh)^2 and gets ceil(n_a / E2_CT_CHUNK) work items
+//   contact_scan_kernel  exclusive prefix of the item counts (single CTA)
+//   contact_work_kernel  persistent CTAs pull items from an atomic counter.  An item = 1024 consecutive points of A:
+//                        those within thresh of B's box are compacted and get their own tight box; B's points within
+//                        thresh of THAT box are staged tile by tile as float32 coordinates relative to the box centre.
+//                        The O(n_a * n_b) sweep runs in float32 with 4 A points per thread; a pair is re-evaluated in
+//                        float64 (the reference's own expression) only when its float32 d^2 is within a proven guard
+//                        band of the thread's current minimum, so the result is the exact float64 minimum.
+//                        Results merge with atomicMin on the float64 bit pattern (order-preserving for d^2 >= 0).
+//   In-frame pairs report the exact minimum whenever it is < thresh.  Cross pairs only feed `< thresh` tests of the
+//   o2 / o3 search (:1600-1653), so they stop at the first witness and the slot is a contact flag: 0.0 iff some
+//   pair of points is closer than thresh, otherwise a value >= thresh (deterministic whatever the item order).
+#pragma once
+#include "common.cuh"
+#include "pairs.cuh"
+
+#define E2_CT_THREADS 256
+#define E2_CT_CHUNK 1024          // A points per work item (4 per thread)
+#define E2_CT_TILE 1024           // B entries staged per tile
+
+struct ContactPlan {
+    unsigned *cnt;        // F * slots      items of the slot (0 = decided by the plan kernel)
+    unsigned *off;        // F * slots + 1  exclusive prefix
+    unsigned *next;       // work counter
+    int slots;            // pair slots per frame: K(K-1)/2 + K + K*K
+};
+
+struct ContactSlot { int a, b, fa; bool cross; u64 *out; };
+
+__device__ __forceinline__ ContactSlot contact_decode(const Dev &d, int f, int slot)
+{
+    const int K = d.K, npairs = K * (K - 1) / 2;
+    ContactSlot s;
+    s.fa = f;
+    s.cross = false;
+    if (slot < npairs) {
+        int a = 0, row = K - 1;
+        while (slot >= row) { slot -= row; --row; ++a; }
+        s.a = a;
+        s.b = a + 1 + slot;
+        s.out = d.pair_key + ((size_t)f * (K + 1) + s.a) * (K + 1) + s.b;
+    } else if (slot < npairs + K) {
+        s.a = slot - npairs;
+        s.b = K;
+        s.out = d.pair_key + ((size_t)f * (K + 1) + s.a) * (K + 1) + K;
+    } else {
+        slot -= npairs + K;
+        s.a = slot / K;
+        s.b = slot - s.a * K;
+        s.out = d.cross_key + ((size_t)f * K + s.a) * K + s.b;
+        s.fa = d.prev_slot[f];
+        s.cross = true;
+    }
+    return s;
+}
+
+__global__ void contact_plan_kernel(Dev d, ContactPlan plan)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx == 0) *plan.next = 0;
+    if (idx >= d.F * plan.slots) return;
+    const int f = idx / plan.slots, slot = idx - f * plan.slots, K = d.K;
+    const u64 INF = 0x7ff0000000000000ull;
+    const ContactSlot s = contact_decode(d, f, slot);
+    unsigned items = 0;
+    u64 init = INF;
+    if (!(s.cross && (s.fa < 0 || s.a == s.b))) {
+        const int offa = d.ent_off[s.fa * K + s.a];
+        const int na = (offa < 0) ? 0 : d.n_list[s.fa * K + s.a];
+        int nb;
+        if (s.b == K) nb = d.n_ground;
+        else { const int offb = d.ent_off[f * K + s.b]; nb = (offb < 0) ? 0 : d.n_list[f * K + s.b]; }
+        if (na > 0 && nb > 0) {
+            const double *ba = d.aabb + (size_t)(s.fa * K + s.a) * 6;
+            const double *bb = (s.b == K) ? d.gaabb : d.aabb + (size_t)(f * K + s.b) * 6;
+            const double lim2 = d.thresh * d.thresh * 1.000001 + 1e-300;
+            const double gap2 = box_box_d2(ba, bb);
+            init = d2key(fmax(gap2, d.thresh * d.thresh));
+            if (!(gap2 > lim2)) items = (unsigned)((na + E2_CT_CHUNK - 1) / E2_CT_CHUNK);
+        }
+    }
+    *s.out = init;
+    plan.cnt[idx] = items;
+}
+
+// single CTA of 1024 threads: exclusive scan of plan.cnt -> plan.off
+__global__ void __launch_bounds__(1024) contact_scan_kernel(ContactPlan plan, int n)
+{
+    __shared__ unsigned warp_tot[32];
+    __shared__ unsigned carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        const unsigned items = (i < n) ? plan.cnt[i] : 0u;
+        unsigned v = items;
+        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, v, o); if ((threadIdx.x & 31) >= o) v += t; }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            unsigned w = warp_tot[threadIdx.x];
+            for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, w, o); if (threadIdx.x >= o) w += t; }
+            warp_tot[threadIdx.x] = w;
+        }
+        __syncthreads();
+        const unsigned excl = carry + v - items + ((threadIdx.x >> 5) ? warp_tot[(threadIdx.x >> 5) - 1] : 0u);
+        if (i < n) plan.off[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + items;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) plan.off[n] = carry;
+}
+
+struct ContactSmem {
+    double dx[E2_CT_TILE], dy[E2_CT_TILE], dz[E2_CT_TILE];     // compacted candidates (A chunk, then B tile), float64
+    float fx[E2_CT_TILE], fy[E2_CT_TILE], fz[E2_CT_TILE];      // B tile relative to the chunk box centre, float32
+    double red[6][E2_CT_THREADS / 32];
+    unsigned wcnt[E2_CT_THREADS / 32];
+    unsigned item, skip;
+    double box[6];
+};
+
+// float32 acceptance bound for a float64 minimum `best`: every pair whose float64 d^2 is < best has a float32 d^2
+// (coordinates rounded to float32 relative to an origin, |coordinate| <= M, e = M * 2^-22) below this value
+__device__ __forceinline__ float contact_guard(double best, double e)
+{
+    return __double2float_ru(best * 1.00001 + 4.0 * e * sqrt(best) + 12.0 * e * e);
+}
+
+// Block-wide stable-enough compaction step: thread contributes (x, y, z) when `take`; returns the new count.
+__device__ __forceinline__ unsigned contact_push(ContactSmem &s, bool take, double x, double y, double z, unsigned count,
+                                                 bool with_f32, double ox, double oy, double oz)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned bal = __ballot_sync(0xffffffffu, take);
+    if (lane == 0) s.wcnt[warp] = __popc(bal);
+    __syncthreads();
+    unsigned before = count, tot = 0;
+    for (int w = 0; w < E2_CT_THREADS / 32; ++w) { const unsigned c = s.wcnt[w]; if (w < warp) before += c; tot += c; }
+    if (take) {
+        const unsigned p = before + __popc(bal & ((1u << lane) - 1u));
+        s.dx[p] = x; s.dy[p] = y; s.dz[p] = z;
+        if (with_f32) { s.fx[p] = (float)(x - ox); s.fy[p] = (float)(y - oy); s.fz[p] = (float)(z - oz); }
+    }
+    __syncthreads();
+    return count + tot;
+}
+
+__global__ void __launch_bounds__(E2_CT_THREADS) contact_work_kernel(Dev d, ContactPlan plan)
+{
+    __shared__ ContactSmem s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, K = d.K;
+    const int n_idx = d.F * plan.slots;
+    const unsigned total = plan.off[n_idx];
+    const double lim2 = d.thresh * d.thresh * 1.000001 + 1e-300;            // anything with sqrt(d2) < thresh is below this
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s.item = atomicAdd(plan.next, 1u);
+        __syncthreads();
+        const unsigned item = s.item;
+        if (item >= total) break;
+        int lo = 0, hi = n_idx;                               // last idx with off[idx] <= item
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (plan.off[mid] <= item) lo = mid; else hi = mid;
+        }
+        const int f = lo / plan.slots;
+        const ContactSlot cs = contact_decode(d, f, lo - f * plan.slots);
+        const int chunk = (int)(item - plan.off[lo]);
+        if (tid == 0) s.skip = cs.cross && *((volatile u64 *)cs.out) == 0ull;   // another item already found a witness
+        __syncthreads();
+        if (s.skip) continue;
+        const int offa = d.ent_off[cs.fa * K + cs.a], na = d.n_list[cs.fa * K + cs.a];
+        const size_t pa = (size_t)cs.fa * d.cap + offa;
+        const double *AX = d.px + pa, *AY = d.py + pa, *AZ = d.pz + pa;
+        const unsigned *fla = d.flist + pa;
+        const double *BX, *BY, *BZ;
+        const unsigned *flb = nullptr;
+        int nb;
+        double bb[6];
+        if (cs.b == K) {
+            BX = d.gx; BY = d.gy; BZ = d.gz; nb = d.n_ground;
+            for (int k = 0; k < 6; ++k) bb[k] = d.gaabb[k];
+        } else {
+            const int offb = d.ent_off[f * K + cs.b];
+            const size_t pbb = (size_t)f * d.cap + offb;
+            BX = d.px + pbb; BY = d.py + pbb; BZ = d.pz + pbb;
+            flb = d.flist + pbb;
+            nb = d.n_list[f * K + cs.b];
+            for (int k = 0; k < 6; ++k) bb[k] = d.aabb[(size_t)(f * K + cs.b) * 6 + k];
+        }
+        // ---- A chunk: points within thresh of B's box, and their own tight box ---------------------------------
+        unsigned nA = 0;
+        double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+        for (int k = 0; k < E2_CT_CHUNK / E2_CT_THREADS; ++k) {
+            const int i = chunk * E2_CT_CHUNK + k * E2_CT_THREADS + tid;
+            bool take = false;
+            double x = 0, y = 0, z = 0;
+            if (i < na) {
+                const unsigned p = fla[i];
+                x = AX[p]; y = AY[p]; z = AZ[p];
+                take = point_box_d2(x, y, z, bb) <= lim2;
+                if (take) {
+                    mn[0] = fmin(mn[0], x); mx[0] = fmax(mx[0], x);
+                    mn[1] = fmin(mn[1], y); mx[1] = fmax(mx[1], y);
+                    mn[2] = fmin(mn[2], z); mx[2] = fmax(mx[2], z);
+                }
+            }
+            nA = contact_push(s, take, x, y, z, nA, false, 0, 0, 0);
+        }
+        if (nA == 0) continue;
+        for (int k = 0; k < 3; ++k) {
+            const double l = warp_min_d(mn[k]), h = warp_max_d(mx[k]);
+            if (lane == 0) { s.red[k][warp] = l; s.red[3 + k][warp] = h; }
+        }
+        __syncthreads();
+        if (tid < 3) {
+            double l = s.red[tid][0], h = s.red[3 + tid][0];
+            for (int w = 1; w < E2_CT_THREADS / 32; ++w) { l = fmin(l, s.red[tid][w]); h = fmax(h, s.red[3 + tid][w]); }
+            s.box[tid] = l; s.box[3 + tid] = h;
+        }
+        __syncthreads();
+        double cb[6];
+        for (int k = 0; k < 6; ++k) cb[k] = s.box[k];
+        const double ox = 0.5 * (cb[0] + cb[3]), oy = 0.5 * (cb[1] + cb[4]), oz = 0.5 * (cb[2] + cb[5]);
+        const double hx = cb[3] - cb[0], hy = cb[4] - cb[1], hz = cb[5] - cb[2];
+        const double M = 0.5 * sqrt(hx * hx + hy * hy + hz * hz) + sqrt(lim2);       // |relative coordinate| bound
+        const double e = M * 2.4e-7;
+        // this thread's A points: float64 for the recheck, float32 relative for the sweep
+        double ax[4], ay[4], az[4];
+        float rx[4], ry[4], rz[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned j = (unsigned)(tid + k * E2_CT_THREADS);
+            if (j < nA) {
+                ax[k] = s.dx[j]; ay[k] = s.dy[j]; az[k] = s.dz[j];
+                rx[k] = (float)(ax[k] - ox); ry[k] = (float)(ay[k] - oy); rz[k] = (float)(az[k] - oz);
+            } else {
+                ax[k] = ay[k] = az[k] = 1e300;
+                rx[k] = ry[k] = rz[k] = 1e18f;                  // float32 d^2 overflows to +inf: never accepted
+            }
+        }
+        double best = lim2;
+        float guard = contact_guard(best, e);
+        // ---- B tiles -----------------------------------------------------------------------------------------------
+        for (int base = 0; base < nb; base += E2_CT_TILE) {
+            __syncthreads();                                     // the previous tile (or the A staging) is consumed
+            unsigned mB = 0;
+            for (int k = 0; k < E2_CT_TILE / E2_CT_THREADS; ++k) {
+                const int j = base + k * E2_CT_THREADS + tid;
+                bool take = false;
+                double x = 0, y = 0, z = 0;
+                if (j < nb) {
+                    const unsigned q = flb ? flb[j] : (unsigned)j;
+                    x = BX[q]; y = BY[q]; z = BZ[q];
+                    take = point_box_d2(x, y, z, cb) <= lim2;
+                }
+                mB = contact_push(s, take, x, y, z, mB, true, ox, oy, oz);
+            }
+            for (unsigned j = 0; j < mB; ++j) {
+                const float bx = s.fx[j], by = s.fy[j], bz = s.fz[j];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float ux = rx[k] - bx, uy = ry[k] - by, uz = rz[k] - bz;
+                    const float d32 = fmaf(uz, uz, fmaf(uy, uy, ux * ux));
+                    if (d32 <= guard) {
+                        const double dd = dist2(ax[k], ay[k], az[k], s.dx[j], s.dy[j], s.dz[j]);
+                        if (dd < best) { best = dd; guard = contact_guard(best, e); }
+                    }
+                }
+            }
+            if (cs.cross && __syncthreads_or(sqrt(best) < d.thresh)) break;     // a witness is enough for a cross pair
+        }
+        best = warp_min_d(best);
+        if (lane == 0) {
+            if (cs.cross) { if (sqrt(best) < d.thresh) atomicMin(cs.out, 0ull); }     // contact flag: 0.0 = closer than thresh
+            else if (best < lim2) atomicMin(cs.out, d2key(best));
+        }
+    }
+}

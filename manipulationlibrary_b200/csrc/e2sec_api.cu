@@ -13,6 +13,7 @@
 #include "filter.cuh"
 #include "cells.cuh"
 #include "pairs.cuh"
+#include "contact.cuh"
 
 #define E2_MAX_REFINE 6        // histogram rounds launched per batch (each narrows the key interval 256x)
 
@@ -37,7 +38,7 @@ struct e2sec_ctx {
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
-        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb;
+        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next;
     int map_cfg[4] = {0, 0, 0, 0};
     int64_t launches = 0;
     cudaEvent_t ev[8];
@@ -102,6 +103,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double)));
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
+    cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
     ctx->bufs = {&ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
@@ -109,7 +111,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
                  &ctx->gz, &ctx->pair_key, &ctx->records, &ctx->error, &ctx->plan_off, &ctx->plan_total,
                  &ctx->below_acc, &ctx->min_above, &ctx->single_count, &ctx->cross_key, &ctx->frame_used, &ctx->prev_slot,
-                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb};
+                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next};
     *out = ctx;
     return E2SEC_OK;
 }
@@ -197,6 +199,10 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     rc |= ensure(ctx, ctx->rad_lo, FK * sizeof(double));
     rc |= ensure(ctx, ctx->rad_hi, FK * sizeof(double));
     rc |= ensure(ctx, ctx->amb, FK * sizeof(int));
+    const size_t slots = (size_t)K * (K - 1) / 2 + K + (size_t)K * K;
+    rc |= ensure(ctx, ctx->ct_cnt, (size_t)F * slots * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->ct_off, ((size_t)F * slots + 1) * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->ct_next, sizeof(unsigned));
     if (rc) return E2SEC_ERR_CUDA;
     ctx->maxF = F;
     ctx->N = N;
@@ -371,7 +377,12 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
     cudaEventRecord(ctx->ev[5], st);
     if (do_pairs) {
         prev_kept_kernel<<<1, 32, 0, st>>>(d); LAUNCHED();
-        pair_distance_kernel<<<dim3(d.K * (d.K - 1) / 2 + d.K + d.K * d.K, d.F), E2_PD_THREADS, 0, st>>>(d); LAUNCHED();
+        ContactPlan cp{(unsigned *)ctx->ct_cnt.p, (unsigned *)ctx->ct_off.p, (unsigned *)ctx->ct_next.p,
+                       d.K * (d.K - 1) / 2 + d.K + d.K * d.K};
+        const int n_idx = d.F * cp.slots;
+        contact_plan_kernel<<<(n_idx + 255) / 256, 256, 0, st>>>(d, cp); LAUNCHED();
+        contact_scan_kernel<<<1, 1024, 0, st>>>(cp, n_idx); LAUNCHED();
+        contact_work_kernel<<<ctx->sm_count * 4, E2_CT_THREADS, 0, st>>>(d, cp); LAUNCHED();
         halo_save_kernel<<<64, 256, 0, st>>>(d); LAUNCHED();
         halo_commit_kernel<<<1, 1, 0, st>>>(d); LAUNCHED();
     }
