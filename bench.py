@@ -258,15 +258,15 @@ def run_b200(args):
         s = (i * B) % pool
         ids = ids_all[i * B: (i + 1) * B]
         out = rec_np[i * B: (i + 1) * B]
+        # batches are queued back to back on the context's stream; finish() waits once (e2sec_sync) before the resolver
         if on_device:
-            eng.process_batch_device(dx[s].data_ptr(), dl[s].data_ptr(), B, ids, N, records=out)
+            eng.process_batch_device_async(dx[s].data_ptr(), dl[s].data_ptr(), B, ids, N, records=out)
         else:
-            rc = nat.lib.e2sec_process_batch(eng._h, hx_t[s].data_ptr(), hl_t[s].data_ptr(), B, N, 1, N, 1, nat.ptr(ids), 0,
-                                             nat.ptr(out))
-            eng._check(rc, "e2sec_process_batch")
+            eng.process_batch_device_async(hx_t[s].data_ptr(), hl_t[s].data_ptr(), B, ids, N, records=out, on_device=False)
 
     def finish(n_steps, first_step):
         """one gather of the records (N > 1) + the sequential phase 2 on rank 0"""
+        eng.sync()                                     # all queued batches done, records on the host, errors raised
         local_rec = rec_np[first_step * B: (first_step + n_steps) * B]
         if world > 1:
             full = gather_records(local_rec, n_steps * B * world, world, device=dev)
@@ -312,6 +312,7 @@ def run_b200(args):
     eng.reset_sequence()
     for i in range(W):
         step(i, True)
+    eng.sync()
     uuid = str(torch.cuda.get_device_properties(dev).uuid)
     sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if rank == 0 else None
     time.sleep(0.3 if sampler else 0.0)
@@ -331,6 +332,7 @@ def run_b200(args):
     if not args.no_e2e:
         eng.reset_sequence()
         step(0, False)
+        eng.sync()
         ems, ewall, _, _, _ = timed(False, W, K)
         e2e = {"value": frames / (ewall * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * N * BYTES_PER_POINT,
                "d2h_bytes_per_step": B * rec_w * 8, "timing": "wall clock around the C-ABI calls, pinned host buffers"}

@@ -124,7 +124,14 @@ int e2sec_reset_sequence(e2sec_ctx *ctx);
 int e2sec_process_batch(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
                         int32_t label_w, int32_t label_h, int32_t width, int32_t height,
                         const int32_t *frame_ids, int on_device, double *records);
+/* The same, stream-ordered and WITHOUT waiting: `records` (pinned host memory, or NULL) is filled by an asynchronous
+ * copy, host inputs must stay untouched and device-side errors are reported by the next e2sec_sync / e2sec_process_batch.
+ * Lets a caller queue several batches back to back (bench.py) -- the reference's loop (:2271-2281) has no equivalent. */
+int e2sec_process_batch_async(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
+                              int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                              const int32_t *frame_ids, int on_device, double *records);
 const double *e2sec_records_dev(e2sec_ctx *ctx);
+/* Waits for the context's stream; returns the first device-side error of the batches queued since the last check. */
 int e2sec_sync(e2sec_ctx *ctx);
 /* number of kernels launched by this context so far (bench.py's gpu_launches) */
 int64_t e2sec_launch_count(const e2sec_ctx *ctx);

@@ -16,7 +16,9 @@
 //      then every one of its points is reachable at every radius in [r_lo, r_hi]
 //   F  if no non-member cell has dmin <= r_hi to a member cell, no further point can be reached at any radius in
 //      [r_lo, r_hi]: the closure of the TRUE radius is exactly the union of the member cells.  Otherwise the
-//      entity is flagged ambiguous and the exact path (radius.cuh + filter.cuh) redoes it.
+//      points of the cells that could still be reached (few) are settled one by one with exact float64 distances
+//      to the member points: <= r_lo joins, > r_hi stays out; a point in between makes the entity ambiguous and
+//      the exact path (radius.cuh + filter.cuh) redoes it.
 //   G  stable compaction of the member points (raster order, like the exact path) + AABB / mean / count
 #pragma once
 #include "common.cuh"
@@ -29,6 +31,8 @@
 #define E2_CELL_G 24              // cells along the largest robust extent; ids use 5 bits per axis
 #define E2_CELL_BINS 1024         // histogram bins over d^2
 #define E2_CELL_EMPTY 0xffffffffu
+#define E2_CELL_JOIN (E2_CELL_MAX - 1)   // virtual cell of candidate points that were settled as members one by one
+#define E2_CELL_UMAX 256          // candidate points settled at point level before giving up
 
 struct CellSmem {
     union {
@@ -44,7 +48,11 @@ struct CellSmem {
     float best_d[E2_CELL_WARPS];
     int best_i[E2_CELL_WARPS];
     unsigned wcnt[E2_CELL_WARPS];
-    unsigned m, n_front, n_new, overflow, amb;
+    unsigned char cand[E2_CELL_MAX];
+    unsigned ulist[E2_CELL_UMAX];
+    unsigned char joined[E2_CELL_UMAX];
+    double udist[E2_CELL_UMAX];
+    unsigned m, n_front, n_new, n_cand, overflow, amb;
     int seed;
     double lo[3], inv_c, scale, d2max, t_lo, t_hi, r_lo, r_hi, seedp[3];
 };
@@ -252,7 +260,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
             for (int w = 0; w < warp; ++w) base += s.wcnt[w];
             for (int j = 0; j < per; ++j)
                 if (s.keys[tid * per + j] != E2_CELL_EMPTY) { s.cidx[tid * per + j] = (unsigned short)(base < E2_CELL_MAX ? base : 0); ++base; }
-            if (tid == E2_CELL_THREADS - 1) { s.m = base; if (base > E2_CELL_MAX) s.overflow = 1; }
+            if (tid == E2_CELL_THREADS - 1) { s.m = base; if (base > E2_CELL_JOIN) s.overflow = 1; }
         }
         for (int i = tid; i < E2_CELL_MAX; i += E2_CELL_THREADS) {
             s.cnt[i] = 0;
@@ -352,7 +360,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
                 }
             }
         }
-        if (tid == 64) { s.seedp[0] = X[s.seed]; s.seedp[1] = Y[s.seed]; s.seedp[2] = Z[s.seed]; s.n_front = 0; s.n_new = 0; }
+        if (tid == 64) { s.seedp[0] = X[s.seed]; s.seedp[1] = Y[s.seed]; s.seedp[2] = Z[s.seed]; s.n_front = 0; s.n_new = 0; s.n_cand = 0; }
         __syncthreads();
 
         // ---- E: cell closure at r_lo ---------------------------------------------------------------------------------
@@ -381,18 +389,63 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
             cur ^= 1;
             __syncthreads();
         }
-        // ---- F: can anything else be reached at r_hi? ------------------------------------------------------------
+        // ---- F: can anything else be reached at r_hi? --------------------------------------------------------------
+        // Candidate cells: non-members within r_hi of a member or of another candidate (transitively).  Cells that are
+        // not candidates cannot be reached at any radius <= r_hi, whatever happens to the candidates.
         if (tid == 0 && !s.member[pcell[s.seed]]) s.amb = 1;      // the seed's own cell must be certain
-        for (int b = warp; b < m; b += E2_CELL_WARPS) {
-            if (s.member[b]) continue;
-            bool hit = false;
-            for (int a = lane; a < m && !hit; a += 32) {
-                if (!s.member[a]) continue;
-                double dmin2, dmax2;
-                cell_pair_d2(s, a, b, dmin2, dmax2);
-                hit = dmin2 <= t_hi;
+        for (int b = tid; b < E2_CELL_MAX; b += E2_CELL_THREADS) s.cand[b] = 0;
+        __syncthreads();
+        for (;;) {
+            if (tid == 0) s.n_new = 0;
+            __syncthreads();
+            for (int b = warp; b < m; b += E2_CELL_WARPS) {
+                if (s.member[b] || s.cand[b]) continue;
+                bool hit = false;
+                for (int a = lane; a < m && !hit; a += 32) {
+                    if (!s.member[a] && !s.cand[a]) continue;
+                    double dmin2, dmax2;
+                    cell_pair_d2(s, a, b, dmin2, dmax2);
+                    hit = dmin2 <= t_hi;
+                }
+                if (__any_sync(0xffffffffu, hit) && lane == 0) { s.cand[b] = 1; atomicAdd(&s.n_new, s.cnt[b]); atomicAdd(&s.n_cand, s.cnt[b]); }
             }
-            if (__any_sync(0xffffffffu, hit) && lane == 0) s.amb = 1;
+            __syncthreads();
+            const unsigned grew = s.n_new;
+            __syncthreads();
+            if (!grew) break;
+        }
+        // ---- F2: settle the candidate points one by one against the member POINTS (exact float64 distances) ------
+        const unsigned nU = s.n_cand;
+        if (nU > E2_CELL_UMAX) { if (tid == 0) s.amb = 1; }
+        else if (nU > 0 && !s.amb) {
+            for (int i = tid; i < n; i += E2_CELL_THREADS)
+                if (s.cand[pcell[i]]) s.ulist[atomicAdd(&s.n_front, 1u)] = (unsigned)i;
+            if (tid < E2_CELL_UMAX) s.joined[tid] = 0;
+            if (tid == 0) s.member[E2_CELL_JOIN] = 1;            // virtual cell of the points that join here
+            __syncthreads();
+            for (;;) {
+                if (tid == 0) s.n_new = 0;
+                __syncthreads();
+                for (unsigned u = warp; u < nU; u += E2_CELL_WARPS) {
+                    if (s.joined[u]) continue;
+                    const unsigned p = s.ulist[u];
+                    const double x = X[p], y = Y[p], z = Z[p];
+                    double best = 1e300;
+                    for (int q = lane; q < n; q += 32)
+                        if (s.member[pcell[q]]) best = fmin(best, dist2(x, y, z, X[q], Y[q], Z[q]));
+                    best = warp_min_d(best);
+                    if (lane == 0) {
+                        s.udist[u] = best;
+                        if (best <= t_lo) { s.joined[u] = 1; pcell[p] = (unsigned short)E2_CELL_JOIN; s.n_new = 1; }   // reachable at every radius >= r_lo
+                    }
+                }
+                __syncthreads();
+                const unsigned grew = s.n_new;
+                __syncthreads();
+                if (!grew) break;
+            }
+            // the last round changed nothing: udist is measured against the final member set
+            if (tid < nU && !s.joined[tid] && s.udist[tid] <= t_hi) s.amb = 1;      // reachable at r_hi but not at r_lo
         }
         __syncthreads();
         decided = !s.amb;

@@ -27,6 +27,10 @@ struct DevBuf {
 struct e2sec_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;      // H2D of host inputs, double-buffered against the kernels of the previous batch
+    cudaEvent_t copy_done[2], slot_free[2];
+    bool slot_used[2] = {false, false};
+    unsigned stage_idx = 0;
     std::string err;
     e2sec_params params;
     std::vector<double> ground;
@@ -99,6 +103,11 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 2; ++i) {
+        cudaEventCreateWithFlags(&ctx->copy_done[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ctx->slot_free[i], cudaEventDisableTiming);
+    }
     ctx->ev_valid = true;
     cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double)));
@@ -125,6 +134,11 @@ extern "C" void e2sec_destroy(e2sec_ctx *ctx)
         if (b->p) cudaFree(b->p);
     if (ctx->ev_valid)
         for (auto &ev : ctx->ev) cudaEventDestroy(ev);
+    if (ctx->copy_stream) {
+        cudaStreamSynchronize(ctx->copy_stream);
+        for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->copy_done[i]); cudaEventDestroy(ctx->slot_free[i]); }
+        cudaStreamDestroy(ctx->copy_stream);
+    }
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -133,11 +147,13 @@ extern "C" void *e2sec_stream(e2sec_ctx *ctx) { return ctx ? (void *)ctx->stream
 extern "C" int64_t e2sec_launch_count(const e2sec_ctx *ctx) { return ctx ? ctx->launches : 0; }
 extern "C" const double *e2sec_records_dev(e2sec_ctx *ctx) { return ctx ? (const double *)ctx->records.p : nullptr; }
 
+static int check_device_error(e2sec_ctx *ctx);
+
 extern "C" int e2sec_sync(e2sec_ctx *ctx)
 {
     if (!ctx) return E2SEC_ERR_ARG;
-    CU(cudaStreamSynchronize(ctx->stream));
-    return E2SEC_OK;
+    if (!ctx->error.p) { CU(cudaStreamSynchronize(ctx->stream)); return E2SEC_OK; }
+    return check_device_error(ctx);       // waits for the stream, reports (and clears) a device-side error of any batch since
 }
 
 extern "C" int e2sec_reset_sequence(e2sec_ctx *ctx)
@@ -156,8 +172,8 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     const int S = (N + E2_SEG - 1) / E2_SEG;
     const size_t FK = (size_t)(F + 1) * K;
     int rc = 0;
-    rc |= ensure(ctx, ctx->xyz_stage, (size_t)F * N * 3 * sizeof(float));
-    rc |= ensure(ctx, ctx->lab_stage, (size_t)F * N * sizeof(int));
+    rc |= ensure(ctx, ctx->xyz_stage, (size_t)2 * F * N * 3 * sizeof(float));     // two staging slots
+    rc |= ensure(ctx, ctx->lab_stage, (size_t)2 * F * N * sizeof(int));
     rc |= ensure(ctx, ctx->cross_key, (size_t)F * K * K * sizeof(u64));
     rc |= ensure(ctx, ctx->frame_used, (size_t)(F + 1) * sizeof(int));
     rc |= ensure(ctx, ctx->prev_slot, (size_t)F * sizeof(int));
@@ -204,6 +220,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     rc |= ensure(ctx, ctx->ct_off, ((size_t)F * slots + 1) * sizeof(unsigned));
     rc |= ensure(ctx, ctx->ct_next, sizeof(unsigned));
     if (rc) return E2SEC_ERR_CUDA;
+    CU(cudaMemset(ctx->error.p, 0, sizeof(int)));
     ctx->maxF = F;
     ctx->N = N;
     ctx->K = K;
@@ -376,7 +393,7 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
     entity_stats_kernel<<<FK, E2_STATS_THREADS, 0, st>>>(d); LAUNCHED();
     cudaEventRecord(ctx->ev[5], st);
     if (do_pairs) {
-        prev_kept_kernel<<<1, 32, 0, st>>>(d); LAUNCHED();
+        prev_kept_kernel<<<1, 1024, 0, st>>>(d); LAUNCHED();
         ContactPlan cp{(unsigned *)ctx->ct_cnt.p, (unsigned *)ctx->ct_off.p, (unsigned *)ctx->ct_next.p,
                        d.K * (d.K - 1) / 2 + d.K + d.K * d.K};
         const int n_idx = d.F * cp.slots;
@@ -397,6 +414,7 @@ static int check_device_error(e2sec_ctx *ctx)
 {
     int err = 0;
     CU(cudaMemcpyAsync(&err, ctx->error.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemsetAsync(ctx->error.p, 0, sizeof(int), ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     if (err == E2SEC_ERR_CAPACITY) return fail(ctx, err, "stored points exceed the frame capacity");
     if (err == E2SEC_ERR_STATE) return fail(ctx, err, "radius selection lost its rank (internal error)");
@@ -404,9 +422,9 @@ static int check_device_error(e2sec_ctx *ctx)
     return E2SEC_OK;
 }
 
-extern "C" int e2sec_process_batch(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
-                                   int32_t label_w, int32_t label_h, int32_t width, int32_t height,
-                                   const int32_t *frame_ids, int on_device, double *records)
+static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
+                              int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                              const int32_t *frame_ids, int on_device, double *records, bool wait)
 {
     if (!ctx) return E2SEC_ERR_ARG;
     cudaSetDevice(ctx->device);
@@ -433,29 +451,52 @@ extern "C" int e2sec_process_batch(e2sec_ctx *ctx, const float *xyz, const int32
     d.colmap = upscale ? (const int *)ctx->colmap.p : nullptr;
     d.width = upscale ? width : N;
     d.label_w = label_w;
+    int stage_slot = -1;
     cudaEventRecord(ctx->ev[0], st);
     if (on_device) {
         d.xyz = xyz;
         d.labels = labels;
     } else {
-        CU(cudaMemcpyAsync(ctx->xyz_stage.p, xyz, (size_t)n_frames * N * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(ctx->lab_stage.p, labels, (size_t)n_frames * lsz * sizeof(int), cudaMemcpyHostToDevice, st));
-        d.xyz = (const float *)ctx->xyz_stage.p;
-        d.labels = (const int *)ctx->lab_stage.p;
+        // slot s is refilled on the copy stream as soon as the kernels that read it two batches ago are done, so the
+        // upload of this batch overlaps the kernels of the previous one when batches are queued asynchronously
+        stage_slot = (int)(ctx->stage_idx++ & 1u);
+        float *xs = (float *)ctx->xyz_stage.p + (size_t)stage_slot * ctx->maxF * N * 3;
+        int *ls = (int *)ctx->lab_stage.p + (size_t)stage_slot * ctx->maxF * N;
+        if (ctx->slot_used[stage_slot]) CU(cudaStreamWaitEvent(ctx->copy_stream, ctx->slot_free[stage_slot], 0));
+        CU(cudaMemcpyAsync(xs, xyz, (size_t)n_frames * N * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->copy_stream));
+        CU(cudaMemcpyAsync(ls, labels, (size_t)n_frames * lsz * sizeof(int), cudaMemcpyHostToDevice, ctx->copy_stream));
+        CU(cudaEventRecord(ctx->copy_done[stage_slot], ctx->copy_stream));
+        CU(cudaStreamWaitEvent(st, ctx->copy_done[stage_slot], 0));
+        d.xyz = xs;
+        d.labels = ls;
     }
     CU(cudaMemcpyAsync(ctx->frame_ids.p, frame_ids, n_frames * sizeof(int), cudaMemcpyHostToDevice, st));
-    CU(cudaMemsetAsync(ctx->flags.p, 0, n_frames * sizeof(int), st));
-    CU(cudaMemsetAsync(ctx->error.p, 0, sizeof(int), st));
+    CU(cudaMemsetAsync(ctx->flags.p, 0, n_frames * sizeof(int), st));      // the device error flag is sticky until checked
     const dim3 sgrid((d.S + E2_SEG_WARPS - 1) / E2_SEG_WARPS, n_frames);
     seg_count_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
     seg_scan_kernel<<<n_frames, E2SEC_MAX_ENTITIES, 0, st>>>(d); LAUNCHED();
     seg_scatter_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
+    if (stage_slot >= 0) { CU(cudaEventRecord(ctx->slot_free[stage_slot], st)); ctx->slot_used[stage_slot] = true; }   // inputs consumed
     cudaEventRecord(ctx->ev[1], st);
     int rc = run_entity_stages(ctx, d, true, true, true, true);
     if (rc) return rc;
     if (records)
         CU(cudaMemcpyAsync(records, ctx->records.p, (size_t)n_frames * d.rec_doubles * sizeof(double), cudaMemcpyDeviceToHost, st));
-    return check_device_error(ctx);
+    return wait ? check_device_error(ctx) : E2SEC_OK;
+}
+
+extern "C" int e2sec_process_batch(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
+                                   int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                                   const int32_t *frame_ids, int on_device, double *records)
+{
+    return process_batch_impl(ctx, xyz, labels, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, true);
+}
+
+extern "C" int e2sec_process_batch_async(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
+                                         int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                                         const int32_t *frame_ids, int on_device, double *records)
+{
+    return process_batch_impl(ctx, xyz, labels, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, false);
 }
 
 extern "C" int e2sec_stage_ms(e2sec_ctx *ctx, float out[8])

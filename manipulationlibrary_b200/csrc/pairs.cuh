@@ -82,20 +82,34 @@ __device__ __forceinline__ double box_box_d2(const double *a, const double *b)
 // One thread: which frame slot holds the previous KEPT frame of every frame of the batch (kept = hand label in
 // the labels (:1429) and a non-empty filtered hand (:1475, :1551)); slot maxF is the halo carried over from
 // the previous batches.
-__global__ void prev_kept_kernel(Dev d)
+__global__ void __launch_bounds__(1024) prev_kept_kernel(Dev d)
 {
-    if (threadIdx.x || blockIdx.x) return;
-    int slot = d.halo_info[0] ? d.maxF : -1;
-    int id = d.halo_info[0] ? d.halo_info[1] : -1;
-    int last = -1;
-    for (int f = 0; f < d.F; ++f) {
-        d.prev_slot[f] = slot;
-        d.prev_id[f] = id;
-        const bool kept = (d.flags[f] & E2SEC_FLAG_HAND_LABEL) && d.ent_off[f * d.K + d.hand_idx] >= 0 &&
-                          d.n_list[f * d.K + d.hand_idx] > 0;
-        if (kept) { slot = f; id = d.frame_ids[f]; last = f; }
+    __shared__ unsigned char kept[1024];
+    __shared__ int slot_s, id_s, last_s;
+    if (threadIdx.x == 0) {
+        slot_s = d.halo_info[0] ? d.maxF : -1;
+        id_s = d.halo_info[0] ? d.halo_info[1] : -1;
+        last_s = -1;
     }
-    d.halo_info[2] = last;
+    for (int base = 0; base < d.F; base += 1024) {           // flags in parallel, the running "previous" by one thread
+        const int f = base + threadIdx.x;
+        if (f < d.F)
+            kept[threadIdx.x] = (d.flags[f] & E2SEC_FLAG_HAND_LABEL) && d.ent_off[f * d.K + d.hand_idx] >= 0 &&
+                                d.n_list[f * d.K + d.hand_idx] > 0;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int slot = slot_s, id = id_s, last = last_s;
+            const int m = min(1024, d.F - base);
+            for (int i = 0; i < m; ++i) {
+                d.prev_slot[base + i] = slot;
+                d.prev_id[base + i] = id;
+                if (kept[i]) { slot = base + i; id = d.frame_ids[base + i]; last = base + i; }
+            }
+            slot_s = slot; id_s = id; last_s = last;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) d.halo_info[2] = last_s;
 }
 
 // Copies the last kept frame of the batch into the halo slot (grid-stride over its stored points).

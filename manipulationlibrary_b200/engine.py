@@ -69,6 +69,18 @@ class Engine:
                     "e2sec_process_batch")
         return records
 
+    def process_batch_device_async(self, xyz_ptr, labels_ptr, n_frames, frame_ids, label_size, records=None,
+                                   label_shape=None, image_shape=None, on_device=True):
+        """Queues a batch without waiting (e2sec_process_batch_async): `records` must be pinned host memory that stays
+        alive, inputs must stay untouched until sync(); device-side errors surface at the next sync()."""
+        fid = np.ascontiguousarray(frame_ids, np.int32)
+        lw, lh, w, h = self._shapes(label_size, label_shape, image_shape)
+        self._check(lib.e2sec_process_batch_async(self._h, C.c_void_p(xyz_ptr), C.c_void_p(labels_ptr), int(n_frames), lw,
+                                                  lh, w, h, ptr(fid), 1 if on_device else 0,
+                                                  ptr(records) if records is not None else None),
+                    "e2sec_process_batch_async")
+        return records
+
     def _shapes(self, label_size, label_shape, image_shape):
         if label_size == self.n_points:
             return label_size, 1, self.n_points, 1
