@@ -44,6 +44,7 @@ struct CellSmem {
     unsigned box[6][E2_CELL_MAX];             // lo x,y,z, hi x,y,z: order-preserving uint of a float during B, floats after
     unsigned char member[E2_CELL_MAX];
     unsigned short front[2][E2_CELL_MAX];
+    unsigned short rest[E2_CELL_MAX];
     double red[9][E2_CELL_WARPS];
     float best_d[E2_CELL_WARPS];
     int best_i[E2_CELL_WARPS];
@@ -52,7 +53,7 @@ struct CellSmem {
     unsigned ulist[E2_CELL_UMAX];
     unsigned char joined[E2_CELL_UMAX];
     double udist[E2_CELL_UMAX];
-    unsigned m, n_front, n_new, n_cand, overflow, amb;
+    unsigned m, n_front, n_new, n_cand, n_rest, overflow, amb;
     int seed;
     double lo[3], inv_c, scale, d2max, t_lo, t_hi, r_lo, r_hi, seedp[3];
 };
@@ -88,6 +89,28 @@ __device__ __forceinline__ void cell_pair_d2(const CellSmem &s, int a, int b, do
     }
     dmin2 = (g[0] * g[0] + g[1] * g[1]) + g[2] * g[2];
     dmax2 = (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
+}
+__device__ __forceinline__ double cell_pair_dmax2(const CellSmem &s, int a, int b)
+{
+    double f[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double alo = (double)__uint_as_float(s.box[k][a]), ahi = (double)__uint_as_float(s.box[3 + k][a]);
+        const double blo = (double)__uint_as_float(s.box[k][b]), bhi = (double)__uint_as_float(s.box[3 + k][b]);
+        f[k] = fmax(ahi - blo, bhi - alo);
+    }
+    return (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
+}
+__device__ __forceinline__ double cell_pair_dmin2(const CellSmem &s, int a, int b)
+{
+    double g[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double alo = (double)__uint_as_float(s.box[k][a]), ahi = (double)__uint_as_float(s.box[3 + k][a]);
+        const double blo = (double)__uint_as_float(s.box[k][b]), bhi = (double)__uint_as_float(s.box[3 + k][b]);
+        g[k] = fmax(fmax(alo - bhi, blo - ahi), 0.0);
+    }
+    return (g[0] * g[0] + g[1] * g[1]) + g[2] * g[2];
 }
 // the same between a point and a box
 __device__ __forceinline__ double cell_point_dmax2(const CellSmem &s, const double *p, int b)
@@ -189,11 +212,15 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
         const double cx = d.med[(size_t)fe * 3], cy = d.med[(size_t)fe * 3 + 1], cz = d.med[(size_t)fe * 3 + 2];
         float bd = 50000.0f;
         int bi = 0x7fffffff;
+        double bd2_guard = 2.5e9 * 1.0000003;         // (float)sqrt(d2) < bd implies d2 < bd^2 * (1 + 2^-22)
         double ad[3] = {0.0, 0.0, 0.0}, mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
         for (int i = tid; i < n; i += E2_CELL_THREADS) {
             const double x = X[i], y = Y[i], z = Z[i];
-            const float dt = (float)sqrt(dist2(x, y, z, cx, cy, cz));
-            if (dt < bd) { bd = dt; bi = i; }
+            const double d2 = dist2(x, y, z, cx, cy, cz);
+            if (d2 <= bd2_guard) {                    // only then can float32(sqrt(d2)) be < the current minimum
+                const float dt = (float)sqrt(d2);
+                if (dt < bd) { bd = dt; bi = i; bd2_guard = (double)bd * (double)bd * 1.0000003; }
+            }
             ad[0] += fabs(x - cx); ad[1] += fabs(y - cy); ad[2] += fabs(z - cz);
             mn[0] = fmin(mn[0], x); mx[0] = fmax(mx[0], x);
             mn[1] = fmin(mn[1], y); mx[1] = fmax(mx[1], y);
@@ -371,6 +398,13 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
                 if (cell_point_dmax2(s, sp, b) <= t_lo) { s.member[b] = 1; s.front[0][atomicAdd(&s.n_new, 1u)] = (unsigned short)b; }
         }
         __syncthreads();
+        // later rounds: one warp per remaining cell, lanes over the frontier of the previous round
+        if (tid == 0) s.n_rest = 0;
+        __syncthreads();
+        for (int b = tid; b < m; b += E2_CELL_THREADS)
+            if (!s.member[b]) s.rest[atomicAdd(&s.n_rest, 1u)] = (unsigned short)b;
+        __syncthreads();
+        const unsigned n_rest = s.n_rest;
         int cur = 0;
         for (;;) {
             const unsigned nf = s.n_new;
@@ -378,13 +412,12 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
             if (nf == 0) break;
             if (tid == 0) s.n_new = 0;
             __syncthreads();
-            for (int b = tid; b < m; b += E2_CELL_THREADS) {
+            for (unsigned r = warp; r < n_rest; r += E2_CELL_WARPS) {
+                const int b = s.rest[r];
                 if (s.member[b]) continue;
-                for (unsigned q = 0; q < nf; ++q) {
-                    double dmin2, dmax2;
-                    cell_pair_d2(s, (int)s.front[cur][q], b, dmin2, dmax2);
-                    if (dmax2 <= t_lo) { s.member[b] = 1; s.front[cur ^ 1][atomicAdd(&s.n_new, 1u)] = (unsigned short)b; break; }
-                }
+                bool hit = false;
+                for (unsigned q = lane; q < nf && !hit; q += 32) hit = cell_pair_dmax2(s, (int)s.front[cur][q], b) <= t_lo;
+                if (__any_sync(0xffffffffu, hit) && lane == 0) { s.member[b] = 1; s.front[cur ^ 1][atomicAdd(&s.n_new, 1u)] = (unsigned short)b; }
             }
             cur ^= 1;
             __syncthreads();
@@ -403,9 +436,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
                 bool hit = false;
                 for (int a = lane; a < m && !hit; a += 32) {
                     if (!s.member[a] && !s.cand[a]) continue;
-                    double dmin2, dmax2;
-                    cell_pair_d2(s, a, b, dmin2, dmax2);
-                    hit = dmin2 <= t_hi;
+                    hit = cell_pair_dmin2(s, a, b) <= t_hi;
                 }
                 if (__any_sync(0xffffffffu, hit) && lane == 0) { s.cand[b] = 1; atomicAdd(&s.n_new, s.cnt[b]); atomicAdd(&s.n_cand, s.cnt[b]); }
             }

@@ -129,11 +129,12 @@ struct ContactSmem {
     double box[6];
 };
 
-// float32 acceptance bound for a float64 minimum `best`: every pair whose float64 d^2 is < best has a float32 d^2
-// (coordinates rounded to float32 relative to an origin, |coordinate| <= M, e = M * 2^-22) below this value
-__device__ __forceinline__ float contact_guard(double best, double e)
+// float32 acceptance bound for a float64 minimum `best` <= lim2: every pair whose float64 d^2 is < best has a float32 d^2
+// (coordinates rounded to float32 relative to an origin, |coordinate| <= M, e = M * 2^-22) below
+//   best * (1 + 1e-5) + 4 e sqrt(best) + 12 e^2  <=  best * 1.00001 + c0,   c0 = 4 e sqrt(lim2) + 12 e^2
+__device__ __forceinline__ float contact_guard(double best, double c0)
 {
-    return __double2float_ru(best * 1.00001 + 4.0 * e * sqrt(best) + 12.0 * e * e);
+    return __double2float_ru(best * 1.00001 + c0);
 }
 
 // Block-wide stable-enough compaction step: thread contributes (x, y, z) when `take`; returns the new count.
@@ -249,8 +250,9 @@ __global__ void __launch_bounds__(E2_CT_THREADS) contact_work_kernel(Dev d, Cont
                 rx[k] = ry[k] = rz[k] = 1e18f;                  // float32 d^2 overflows to +inf: never accepted
             }
         }
-        double best = lim2;
-        float guard = contact_guard(best, e);
+        const double c0 = 4.0 * e * sqrt(lim2) + 12.0 * e * e;
+        double best = lim2;                                      // block-uniform at every tile boundary
+        float guard = contact_guard(best, c0);
         // ---- B tiles -----------------------------------------------------------------------------------------------
         for (int base = 0; base < nb; base += E2_CT_TILE) {
             __syncthreads();                                     // the previous tile (or the A staging) is consumed
@@ -262,26 +264,35 @@ __global__ void __launch_bounds__(E2_CT_THREADS) contact_work_kernel(Dev d, Cont
                 if (j < nb) {
                     const unsigned q = flb ? flb[j] : (unsigned)j;
                     x = BX[q]; y = BY[q]; z = BZ[q];
-                    take = point_box_d2(x, y, z, cb) <= lim2;
+                    take = point_box_d2(x, y, z, cb) <= best;   // nothing farther than the current minimum can improve it
                 }
                 mB = contact_push(s, take, x, y, z, mB, true, ox, oy, oz);
             }
             for (unsigned j = 0; j < mB; ++j) {
                 const float bx = s.fx[j], by = s.fy[j], bz = s.fz[j];
+                float d32[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const float ux = rx[k] - bx, uy = ry[k] - by, uz = rz[k] - bz;
-                    const float d32 = fmaf(uz, uz, fmaf(uy, uy, ux * ux));
-                    if (d32 <= guard) {
-                        const double dd = dist2(ax[k], ay[k], az[k], s.dx[j], s.dy[j], s.dz[j]);
-                        if (dd < best) { best = dd; guard = contact_guard(best, e); }
-                    }
+                    d32[k] = fmaf(uz, uz, fmaf(uy, uy, ux * ux));
+                }
+                if (fminf(fminf(d32[0], d32[1]), fminf(d32[2], d32[3])) <= guard) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (d32[k] <= guard) best = fmin(best, dist2(ax[k], ay[k], az[k], s.dx[j], s.dy[j], s.dz[j]));
+                    guard = contact_guard(best, c0);
                 }
             }
-            if (cs.cross && __syncthreads_or(sqrt(best) < d.thresh)) break;     // a witness is enough for a cross pair
+            // share the minimum: every thread continues with the block's best, which tightens guard and the B filter
+            const double wb = warp_min_d(best);
+            if (lane == 0) s.red[0][warp] = wb;
+            __syncthreads();
+            best = s.red[0][0];
+            for (int w = 1; w < E2_CT_THREADS / 32; ++w) best = fmin(best, s.red[0][w]);
+            guard = contact_guard(best, c0);
+            if (cs.cross && sqrt(best) < d.thresh) break;        // a witness is enough for a cross pair (best is uniform)
         }
-        best = warp_min_d(best);
-        if (lane == 0) {
+        if (tid == 0) {
             if (cs.cross) { if (sqrt(best) < d.thresh) atomicMin(cs.out, 0ull); }     // contact flag: 0.0 = closer than thresh
             else if (best < lim2) atomicMin(cs.out, d2key(best));
         }

@@ -97,6 +97,7 @@ struct FilterSmem {
     unsigned n_out, n_keep, any_hit;
     double r2max;
     double pv[3];
+    double fx[E2_FILTER_THREADS], fy[E2_FILTER_THREADS], fz[E2_FILTER_THREADS];   // frontier tile (CLOSURE)
 };
 
 // grid F*K CTAs. flist / front_a / front_b / member are indexed like the stored points (f*cap + off + i).
@@ -155,15 +156,24 @@ __global__ void __launch_bounds__(E2_FILTER_THREADS) region_filter_kernel(Dev d)
         __syncthreads();
         for (;;) {
             const unsigned nf = sm.n_front;
-            for (int i = tid; i < n; i += E2_FILTER_THREADS) {
-                if (member[i]) continue;
-                const double x = X[i], y = Y[i], z = Z[i];
-                for (unsigned q = 0; q < nf; ++q) {
-                    const unsigned j = fa[q];
-                    if (dist2(x, y, z, X[j], Y[j], Z[j]) <= r2max) {
-                        member[i] = 1;
-                        fb[atomicAdd(&sm.n_new, 1u)] = (unsigned)i;
-                        break;
+            // the frontier is staged tile by tile in shared memory; every thread sweeps its not-yet-member points over it
+            for (unsigned tile = 0; tile < nf; tile += E2_FILTER_THREADS) {
+                __syncthreads();
+                if (tile + tid < nf) {
+                    const unsigned j = fa[tile + tid];
+                    sm.fx[tid] = X[j]; sm.fy[tid] = Y[j]; sm.fz[tid] = Z[j];
+                }
+                __syncthreads();
+                const unsigned cnt = min((unsigned)E2_FILTER_THREADS, nf - tile);
+                for (int i = tid; i < n; i += E2_FILTER_THREADS) {
+                    if (member[i]) continue;
+                    const double x = X[i], y = Y[i], z = Z[i];
+                    for (unsigned q = 0; q < cnt; ++q) {
+                        if (dist2(x, y, z, sm.fx[q], sm.fy[q], sm.fz[q]) <= r2max) {
+                            member[i] = 1;
+                            fb[atomicAdd(&sm.n_new, 1u)] = (unsigned)i;
+                            break;
+                        }
                     }
                 }
             }

@@ -233,19 +233,30 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
             const u64 ka = d2key(dist2(x0, y0, z0, xj, yj, zj));
             const u64 kb = d2key(dist2(x1, y1, z1, xj, yj, zj));
             const u64 ta = ka - klo, tb = kb - klo;
-            if (gj > lim0) {
-                if (ta < width) {
-                    if (!COLLECT) cnt[(unsigned)(ta >> shift) * E2_PAIR_THREADS + slot] += 1;
-                    else { unsigned pos = atomicAdd(d.cand_n + it.fe, 1u); if (pos < E2_CAND_CAP) d.cand[(size_t)it.fe * E2_CAND_CAP + pos] = ka; }
-                } else if (ka < klo) { if (!COLLECT) ++below; }
-                else if (COLLECT && ka < above_min) above_min = ka;
-            }
-            if (gj > lim1) {
-                if (tb < width) {
-                    if (!COLLECT) cnt[(unsigned)(tb >> shift) * E2_PAIR_THREADS + slot] += 1;
-                    else { unsigned pos = atomicAdd(d.cand_n + it.fe, 1u); if (pos < E2_CAND_CAP) d.cand[(size_t)it.fe * E2_CAND_CAP + pos] = kb; }
-                } else if (kb < klo) { if (!COLLECT) ++below; }
-                else if (COLLECT && kb < above_min) above_min = kb;
+            if (!COLLECT) {
+                if (gj > lim0) {
+                    if (ta < width) cnt[(unsigned)(ta >> shift) * E2_PAIR_THREADS + slot] += 1;
+                    else if (ka < klo) ++below;
+                }
+                if (gj > lim1) {
+                    if (tb < width) cnt[(unsigned)(tb >> shift) * E2_PAIR_THREADS + slot] += 1;
+                    else if (kb < klo) ++below;
+                }
+            } else {
+                // candidates are appended with one global atomic per warp (the j loop is uniform across the CTA)
+                const bool ha = gj > lim0 && ta < width, hb = gj > lim1 && tb < width;
+                const unsigned ba = __ballot_sync(0xffffffffu, ha), bb = __ballot_sync(0xffffffffu, hb);
+                if (ba | bb) {
+                    const int lane = tid & 31;
+                    unsigned base = 0;
+                    if (lane == 0) base = atomicAdd(d.cand_n + it.fe, (unsigned)(__popc(ba) + __popc(bb)));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    const unsigned lt = (1u << lane) - 1u;
+                    if (ha) { const unsigned pos = base + __popc(ba & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)it.fe * E2_CAND_CAP + pos] = ka; }
+                    if (hb) { const unsigned pos = base + __popc(ba) + __popc(bb & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)it.fe * E2_CAND_CAP + pos] = kb; }
+                }
+                if (gj > lim0 && !(ta < width) && !(ka < klo) && ka < above_min) above_min = ka;
+                if (gj > lim1 && !(tb < width) && !(kb < klo) && kb < above_min) above_min = kb;
             }
         }
     }
