@@ -33,15 +33,31 @@
 #define E2_CELL_EMPTY 0xffffffffu
 #define E2_CELL_JOIN (E2_CELL_MAX - 1)   // virtual cell of candidate points that were settled as members one by one
 #define E2_CELL_UMAX 256          // candidate points settled at point level before giving up
+#define E2_CELL_MCAP 512          // median selection: values ranked directly once the middle bin holds no more than this
+#define E2_M_DONE 0
+#define E2_M_HIST 1               // needs a histogram round over [m_lo, m_hi]
+#define E2_M_COLLECT 2            // both middle ranks in bin b1, few values: collect them
+#define E2_M_REFINE 3             // both in bin b1, many values: shrink the range to that bin's values
+#define E2_M_SPLIT 4              // the ranks straddle two bins: a = max of bin b1, b = min of bin b2
 
 struct CellSmem {
     union {
+        unsigned mhist[3][E2_CELL_BINS];      // M: per-axis value histograms of the median selection
         unsigned keys[E2_CELL_HASH];          // B: cell ids
         u64 hist[2][E2_CELL_BINS];            // C, D: weights by dmin2 / dmax2 bin
     };
     unsigned short cidx[E2_CELL_HASH];        // slot -> compact cell index
     unsigned cnt[E2_CELL_MAX];
-    unsigned box[6][E2_CELL_MAX];             // lo x,y,z, hi x,y,z: order-preserving uint of a float during B, floats after
+    union {
+        unsigned box[6][E2_CELL_MAX];         // lo x,y,z, hi x,y,z: order-preserving uint of a float during B, floats after
+        double mcand[3][E2_CELL_MCAP];        // M: values of the bin that holds the middle rank(s)
+    };
+    // M: state of the three selections
+    double m_lo[3], m_hi[3], m_scale[3], m_a[3], m_b[3];
+    unsigned m_below[3], m_before[3], m_ccnt[3];
+    u64 m_bef64[3];
+    int m_mode[3], m_b1[3], m_b2[3];
+    double ebox[6];                           // AABB of the whole entity
     unsigned char member[E2_CELL_MAX];
     unsigned short front[2][E2_CELL_MAX];
     unsigned short rest[E2_CELL_MAX];
@@ -156,7 +172,7 @@ __device__ __forceinline__ double cell_block_max(CellSmem &s, int slot, double v
 // One warp finds the bin holding 0-based rank k of a weighted histogram (cumulative weight > k). Returns
 // E2_CELL_BINS - 1 when the rank lies beyond the total (cannot happen: the weights sum to the pair count).
 template <class T>
-__device__ __forceinline__ int cell_rank_bin(const T *h, u64 k)
+__device__ __forceinline__ int cell_rank_bin(const T *h, u64 k, u64 *before_out = nullptr)
 {
     const int lane = threadIdx.x & 31;
     const int per = E2_CELL_BINS / 32;
@@ -173,12 +189,131 @@ __device__ __forceinline__ int cell_rank_bin(const T *h, u64 k)
             u64 acc = before;
             for (int j = 0; j < per; ++j) {
                 acc += h[lane * per + j];
-                if (acc > k) { bin = lane * per + j; break; }
+                if (acc > k) { bin = lane * per + j; acc -= h[lane * per + j]; break; }
             }
+            if (before_out) *before_out = acc;          // weight strictly before the bin (written by one lane)
         }
         bin = __shfl_sync(0xffffffffu, bin, L);
     }
     return bin;
+}
+
+
+__device__ __forceinline__ int median_bin(double v, double lo, double scale)
+{
+    const double t = (v - lo) * scale;                       // v >= lo: monotone non-decreasing in v
+    return t >= (double)(E2_CELL_BINS - 1) ? E2_CELL_BINS - 1 : (int)t;
+}
+
+// np.median(objects[i], axis=0) (:1523) for the three axes at once, exact.  Each axis narrows a value range
+// [m_lo, m_hi] that holds both middle order statistics (ranks k1 <= k2 = k1 or k1 + 1): histogram of the values in the
+// range -> bins of the two ranks -> either few enough values to rank directly, or the bin's own value span becomes
+// the next range, or the two ranks sit in different bins (then they are that bin's maximum / the other's minimum).
+// Two passes over the points per round; planar clouds (one axis with a tiny spread next to far outliers) take two
+// rounds on that axis, everything else one.  Also leaves the entity's AABB in s.ebox.  Returns false (after raising
+// the device error flag) if a selection does not converge -- only non-finite coordinate spans can do that.
+__device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, const double *Y, const double *Z, int n, double med[3])
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double *A[3] = {X, Y, Z};
+    {
+        double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+        for (int i = tid; i < n; i += E2_CELL_THREADS)
+            for (int a = 0; a < 3; ++a) { const double v = A[a][i]; mn[a] = fmin(mn[a], v); mx[a] = fmax(mx[a], v); }
+        for (int a = 0; a < 3; ++a) {
+            const double l = cell_block_min(s, a, mn[a]), h = cell_block_max(s, 3 + a, mx[a]);
+            if (tid == 0) {
+                s.ebox[a] = l; s.ebox[3 + a] = h;
+                s.m_lo[a] = l; s.m_hi[a] = h; s.m_below[a] = 0;
+                if (h > l) { s.m_scale[a] = (double)E2_CELL_BINS / (h - l); s.m_mode[a] = E2_M_HIST; }
+                else { s.m_a[a] = s.m_b[a] = l; s.m_mode[a] = E2_M_DONE; }
+            }
+        }
+    }
+    __syncthreads();
+    const unsigned k2 = (unsigned)(n / 2), k1 = (n & 1) ? k2 : k2 - 1;
+    for (int round = 0; round < 64; ++round) {
+        int mode[3];
+        double lo[3], hi[3], sc[3];
+        for (int a = 0; a < 3; ++a) { mode[a] = s.m_mode[a]; lo[a] = s.m_lo[a]; hi[a] = s.m_hi[a]; sc[a] = s.m_scale[a]; }
+        if (mode[0] == E2_M_DONE && mode[1] == E2_M_DONE && mode[2] == E2_M_DONE) {
+            for (int a = 0; a < 3; ++a) med[a] = (n & 1) ? s.m_a[a] : (s.m_a[a] + s.m_b[a]) / 2.0;     // numpy: mean of the two middle values
+            return true;
+        }
+        for (int i = tid; i < 3 * E2_CELL_BINS; i += E2_CELL_THREADS) (&s.mhist[0][0])[i] = 0;
+        if (tid < 3) s.m_ccnt[tid] = 0;
+        __syncthreads();
+        // ---- pass H: histograms (one shared atomic per distinct bin of a warp) ----------------------------------
+        for (int base = 0; base < n; base += E2_CELL_THREADS) {
+            const int i = base + tid;
+            for (int a = 0; a < 3; ++a) {
+                if (mode[a] != E2_M_HIST) continue;
+                int bin = -1;
+                if (i < n) { const double v = A[a][i]; if (v >= lo[a] && v <= hi[a]) bin = median_bin(v, lo[a], sc[a]); }
+                const unsigned peers = __match_any_sync(0xffffffffu, bin);
+                if (bin >= 0 && lane == __ffs(peers) - 1) atomicAdd(&s.mhist[a][bin], (unsigned)__popc(peers));
+            }
+        }
+        __syncthreads();
+        if (warp < 3 && mode[warp] == E2_M_HIST) {
+            const int a = warp;
+            const int b1 = cell_rank_bin(s.mhist[a], (u64)(k1 - s.m_below[a]), &s.m_bef64[a]);
+            const int b2 = (k2 == k1) ? b1 : cell_rank_bin(s.mhist[a], (u64)(k2 - s.m_below[a]));
+            if (lane == 0) { s.m_b1[a] = b1; s.m_b2[a] = b2; }
+        }
+        __syncthreads();
+        if (tid < 3 && mode[tid] == E2_M_HIST) {
+            const int a = tid, b1 = s.m_b1[a], b2 = s.m_b2[a];
+            s.m_before[a] = (unsigned)s.m_bef64[a];                 // values of the range below bin b1
+            s.m_mode[a] = (b1 != b2) ? E2_M_SPLIT : (s.mhist[a][b1] <= E2_CELL_MCAP ? E2_M_COLLECT : E2_M_REFINE);
+        }
+        __syncthreads();
+        // ---- pass R: resolve ---------------------------------------------------------------------------------------
+        double tmin[3] = {1e300, 1e300, 1e300}, tmax[3] = {-1e300, -1e300, -1e300};
+        int m2[3], b1[3], b2[3];
+        for (int a = 0; a < 3; ++a) { m2[a] = (mode[a] == E2_M_HIST) ? s.m_mode[a] : E2_M_DONE; b1[a] = s.m_b1[a]; b2[a] = s.m_b2[a]; }
+        for (int i = tid; i < n; i += E2_CELL_THREADS) {
+            for (int a = 0; a < 3; ++a) {
+                if (m2[a] == E2_M_DONE) continue;
+                const double v = A[a][i];
+                if (!(v >= lo[a] && v <= hi[a])) continue;
+                const int bin = median_bin(v, lo[a], sc[a]);
+                if (m2[a] == E2_M_COLLECT) { if (bin == b1[a]) s.mcand[a][atomicAdd(&s.m_ccnt[a], 1u)] = v; }
+                else if (m2[a] == E2_M_REFINE) { if (bin == b1[a]) { tmin[a] = fmin(tmin[a], v); tmax[a] = fmax(tmax[a], v); } }
+                else { if (bin == b1[a]) tmax[a] = fmax(tmax[a], v); else if (bin == b2[a]) tmin[a] = fmin(tmin[a], v); }
+            }
+        }
+        for (int a = 0; a < 3; ++a) {                            // uniform: m2 comes from shared memory
+            if (m2[a] != E2_M_REFINE && m2[a] != E2_M_SPLIT) continue;
+            const double l = cell_block_min(s, a, tmin[a]), h = cell_block_max(s, 3 + a, tmax[a]);
+            if (tid == 0) {
+                if (m2[a] == E2_M_SPLIT) { s.m_a[a] = h; s.m_b[a] = l; s.m_mode[a] = E2_M_DONE; }
+                else {
+                    s.m_below[a] += s.m_before[a];
+                    s.m_lo[a] = l; s.m_hi[a] = h;
+                    if (h > l && (double)E2_CELL_BINS / (h - l) < 1e300) { s.m_scale[a] = (double)E2_CELL_BINS / (h - l); s.m_mode[a] = E2_M_HIST; }
+                    else { s.m_a[a] = l; s.m_b[a] = h; s.m_mode[a] = E2_M_DONE; }      // a single value (or two adjacent ones)
+                }
+            }
+        }
+        __syncthreads();
+        for (int a = 0; a < 3; ++a) {
+            if (m2[a] != E2_M_COLLECT) continue;
+            const unsigned c = s.m_ccnt[a];
+            const unsigned r1 = k1 - s.m_below[a] - s.m_before[a], r2 = k2 - s.m_below[a] - s.m_before[a];
+            if ((unsigned)tid < c) {
+                const double v = s.mcand[a][tid];
+                unsigned rank = 0;
+                for (unsigned j = 0; j < c; ++j) { const double w = s.mcand[a][j]; rank += (w < v) || (w == v && j < (unsigned)tid); }
+                if (rank == r1) s.m_a[a] = v;
+                if (rank == r2) s.m_b[a] = v;
+            }
+            if (tid == 0) s.m_mode[a] = E2_M_DONE;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) atomicExch(d.error, E2SEC_ERR_STATE);
+    return false;
 }
 
 extern __shared__ __align__(16) unsigned char cell_smem_raw[];
@@ -209,11 +344,15 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
 
     if (filtered) {
         // ---- A: seed, mean absolute deviation, AABB ------------------------------------------------------------
-        const double cx = d.med[(size_t)fe * 3], cy = d.med[(size_t)fe * 3 + 1], cz = d.med[(size_t)fe * 3 + 2];
+        // ---- M: per-axis medians = the seed target (:1523) -----------------------------------------------------------
+        double med[3];
+        if (!cell_axis_medians(s, d, X, Y, Z, n, med)) return;
+        if (tid < 3) d.med[(size_t)fe * 3 + tid] = med[tid];
+        const double cx = med[0], cy = med[1], cz = med[2];
         float bd = 50000.0f;
         int bi = 0x7fffffff;
         double bd2_guard = 2.5e9 * 1.0000003;         // (float)sqrt(d2) < bd implies d2 < bd^2 * (1 + 2^-22)
-        double ad[3] = {0.0, 0.0, 0.0}, mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+        double ad[3] = {0.0, 0.0, 0.0};
         for (int i = tid; i < n; i += E2_CELL_THREADS) {
             const double x = X[i], y = Y[i], z = Z[i];
             const double d2 = dist2(x, y, z, cx, cy, cz);
@@ -222,9 +361,6 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
                 if (dt < bd) { bd = dt; bi = i; bd2_guard = (double)bd * (double)bd * 1.0000003; }
             }
             ad[0] += fabs(x - cx); ad[1] += fabs(y - cy); ad[2] += fabs(z - cz);
-            mn[0] = fmin(mn[0], x); mx[0] = fmax(mx[0], x);
-            mn[1] = fmin(mn[1], y); mx[1] = fmax(mx[1], y);
-            mn[2] = fmin(mn[2], z); mx[2] = fmax(mx[2], z);
         }
         for (int o = 16; o; o >>= 1) {
             const float od = __shfl_xor_sync(0xffffffffu, bd, o);
@@ -235,7 +371,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
         double ext2 = 0.0, half[3];
         for (int k = 0; k < 3; ++k) {
             const double a = cell_block_sum(s, k, ad[k]);
-            const double l = cell_block_min(s, 3 + k, mn[k]), h = cell_block_max(s, 6 + k, mx[k]);
+            const double l = s.ebox[k], h = s.ebox[3 + k];
             ext2 += (h - l) * (h - l);
             half[k] = 3.5 * (a / (double)n);
         }

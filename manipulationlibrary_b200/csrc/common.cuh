@@ -14,7 +14,7 @@
 #define E2_SEG_WARPS 8       // warps per CTA there
 #define E2_TILE 256          // points per tile in the pair-distance kernels
 #define E2_NBINS 256         // bins per refinement pass of the radius selection
-#define E2_CAND_CAP 32768    // candidate keys kept for the final exact selection
+#define E2_CAND_CAP 4096     // candidate keys kept for the final exact selection
 
 typedef unsigned long long u64;
 

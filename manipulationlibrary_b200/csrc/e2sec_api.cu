@@ -367,7 +367,8 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
     const int FK = d.F * d.K;
     PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p};
     u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
-    if (need_median) { axis_median_kernel<<<dim3(3, FK), E2_SEL_THREADS, 0, st>>>(d); LAUNCHED(); }
+    // BOUNDED mode selects the medians inside cell_filter_kernel
+    if (need_median && d.radius_mode != E2SEC_RADIUS_BOUNDED) { axis_median_kernel<<<dim3(3, FK), E2_SEL_THREADS, 0, st>>>(d); LAUNCHED(); }
     cudaEventRecord(ctx->ev[2], st);
     if (d.radius_mode == E2SEC_RADIUS_BOUNDED) {
         cell_filter_kernel<<<FK, E2_CELL_THREADS, sizeof(CellSmem), st>>>(d); LAUNCHED();
