@@ -316,6 +316,7 @@ __global__ void __launch_bounds__(E2_SEL_THREADS) radius_final_kernel(Dev d, con
     __shared__ SelectSmem sm;
     const int fe = blockIdx.x;
     RadiusState &rs = d.rs[fe];
+    if (rs.phase == 0 && threadIdx.x == 0) atomicExch(d.error, E2SEC_ERR_STATE);   // the launched refinement rounds did not converge
     if (rs.phase != 1) return;
     const u64 r1 = rs.k1 - rs.below, r2 = rs.k2 - rs.below;
     u64 v1, v2;

@@ -333,6 +333,63 @@ def test_synthetic_sharded_equals_whole(engine):
     assert r.n_columns >= 1
 
 
+def _records_both_modes(engine, stream, ids, batch):
+    from manipulationlibrary_b200 import _native as nat
+    xyz, lab = stream.fetch(ids)
+    out = {}
+    for rm in ("exact", "bounded"):
+        p, keep = nat.make_params(**stream.params(radius_mode=rm))
+        engine.configure(p, batch, stream.N, keep)
+        out[rm] = np.concatenate([engine.process_batch(xyz[i: i + batch], lab[i: i + batch], ids[i: i + batch])
+                                  for i in range(0, len(ids), batch)])
+    return out, xyz, lab
+
+
+def test_config4_pair_stress_vs_oracle(engine):
+    """BASELINE config 4 (20 objects -> 190 pairs, neighbours within +-5 mm of thresh) at a size the oracle finishes in
+    seconds: every in-frame distance below thresh bit-exact, every contact flag right, both radius modes."""
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    from oracle.records import RecordOracle
+    s = SyntheticStream(width=640, height=360, n_objects=20, config=4, near_thresh=True)
+    ids = np.arange(40, 43)
+    recs, xyz, lab = _records_both_modes(engine, s, ids, 3)
+    orc = eo.E2SecOracle(s.ground_label, s.hand_label, None, s.thresh, s.translation, s.roll, s.ground,
+                         s.total_unique_labels, filter_mode="closure")
+    ro = RecordOracle(orc)
+    want = np.stack([ro.frame_record(int(f), xyz[i], lab[i]) for i, f in enumerate(ids)])
+    K = len(s.total_unique_labels)
+    compare_records(recs["exact"], want, K, s.thresh)
+    compare_records(recs["bounded"], want, K, s.thresh, radius_exact=False)
+    pt = want[:, REC_HEADER + REC_ENTITY * K: REC_HEADER + REC_ENTITY * K + (K + 1) * (K + 1)]
+    assert np.count_nonzero(np.abs(pt[np.isfinite(pt)] - s.thresh) < 0.006) >= 4      # the stress is really there
+
+
+@pytest.mark.parametrize("shape", [(1280, 720, 20, 4), (2000, 1000, 30, 5)])
+def test_large_configs_bounded_equals_exact(engine, shape):
+    """BASELINE configs 4 and 5 at full frame size (1280x720 / 20 objects, 2M points / 30 objects): the bounded route
+    gives the exact route's records, and the records satisfy the size-independent properties of the path."""
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    w, h, n_obj, cfg = shape
+    s = SyntheticStream(width=w, height=h, n_objects=n_obj, config=cfg, near_thresh=(cfg == 4))
+    ids = np.arange(30, 32)
+    recs, xyz, lab = _records_both_modes(engine, s, ids, 2)
+    K = len(s.total_unique_labels)
+    st = compare_records(recs["bounded"], recs["exact"], K, s.thresh, radius_exact=False)
+    assert st["filtered"] == 2 * (n_obj + 1)
+    for f, rec in enumerate(recs["bounded"]):
+        valid = ~np.isnan(xyz[f]).any(1)
+        W = K + 1
+        pt = rec[REC_HEADER + REC_ENTITY * K: REC_HEADER + REC_ENTITY * K + W * W].reshape(W, W)
+        assert (pt == pt.T).all()                                    # min distance is symmetric
+        for e in range(K):
+            a = rec[REC_HEADER + REC_ENTITY * e: REC_HEADER + REC_ENTITY * (e + 1)]
+            assert a[0] == np.count_nonzero(valid & (lab[f] == s.total_unique_labels[e]))     # segmentation counts
+            if a[2] >= 0:
+                assert 1 <= a[1] <= a[0] + 1                          # filter output is a subset (+ the doubled seed)
+                assert (a[7:10] <= a[13:16]).all() and (a[13:16] <= a[10:13]).all()      # mean inside the AABB
+                assert (a[7:10] <= a[4:7] + 1.0).all()
+
+
 # ---- the drop-in Python surface ---------------------------------------------------------------------
 def _write_sequence(tmp, frames, every=3):
     """Pushing_06 fixture frames as files named like the MANIAC recordings: <stem>_pc.pcd (binary PCD) and
