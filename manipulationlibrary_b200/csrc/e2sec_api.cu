@@ -3,11 +3,13 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
 #include "common.cuh"
 #include "seg.cuh"
+#include "seg_fused.cuh"
 #include "select.cuh"
 #include "radius.cuh"
 #include "filter.cuh"
@@ -42,12 +44,13 @@ struct e2sec_ctx {
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
-        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next;
+        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next, seg_list;
     int map_cfg[4] = {0, 0, 0, 0};
     int64_t launches = 0;
     cudaEvent_t ev[8];
     bool ev_valid = false;
     int sm_count = 148;
+    bool force_two_pass = false;   // E2SEC_SEG_TWO_PASS=1: always take the two-pass segmentation (tests compare both)
 };
 
 #define CU(call)                                                                         \
@@ -112,6 +115,9 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double)));
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
+    cudaFuncSetAttribute(seg_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
+    cudaFuncSetAttribute(seg_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
+    { const char *e = getenv("E2SEC_SEG_TWO_PASS"); ctx->force_two_pass = e && e[0] == '1'; }
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
     ctx->bufs = {&ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
@@ -120,7 +126,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
                  &ctx->gz, &ctx->pair_key, &ctx->records, &ctx->error, &ctx->plan_off, &ctx->plan_total,
                  &ctx->below_acc, &ctx->min_above, &ctx->single_count, &ctx->cross_key, &ctx->frame_used, &ctx->prev_slot,
-                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next};
+                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->seg_list};
     *out = ctx;
     return E2SEC_OK;
 }
@@ -219,6 +225,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     rc |= ensure(ctx, ctx->ct_cnt, (size_t)F * slots * sizeof(unsigned));
     rc |= ensure(ctx, ctx->ct_off, ((size_t)F * slots + 1) * sizeof(unsigned));
     rc |= ensure(ctx, ctx->ct_next, sizeof(unsigned));
+    rc |= ensure(ctx, ctx->seg_list, (size_t)F * N * sizeof(uint4));
     if (rc) return E2SEC_ERR_CUDA;
     CU(cudaMemset(ctx->error.p, 0, sizeof(int)));
     ctx->maxF = F;
@@ -263,6 +270,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     d.rad_lo = (double *)ctx->rad_lo.p;
     d.rad_hi = (double *)ctx->rad_hi.p;
     d.amb = (int *)ctx->amb.p;
+    d.seg_list = (uint4 *)ctx->seg_list.p;
     return E2SEC_OK;
 }
 
@@ -333,6 +341,9 @@ extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t ma
     d.thresh = p->thresh;
     memcpy(d.T, p->translation, sizeof(d.T));
     memcpy(d.R, p->roll, sizeof(d.R));
+    d.affine = 1;
+    for (int i = 12; i < 16; ++i)
+        if (d.T[i] != (i == 15 ? 1.0 : 0.0) || d.R[i] != (i == 15 ? 1.0 : 0.0)) d.affine = 0;
     d.gx = (const double *)ctx->gx.p;
     d.gy = (const double *)ctx->gy.p;
     d.gz = (const double *)ctx->gz.p;
@@ -473,10 +484,34 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const int32_t *l
     }
     CU(cudaMemcpyAsync(ctx->frame_ids.p, frame_ids, n_frames * sizeof(int), cudaMemcpyHostToDevice, st));
     CU(cudaMemsetAsync(ctx->flags.p, 0, n_frames * sizeof(int), st));      // the device error flag is sticky until checked
-    const dim3 sgrid((d.S + E2_SEG_WARPS - 1) / E2_SEG_WARPS, n_frames);
-    seg_count_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
-    seg_scan_kernel<<<n_frames, E2SEC_MAX_ENTITIES, 0, st>>>(d); LAUNCHED();
-    seg_scatter_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
+    // single-pass cluster kernel when the bulk copies can be issued (16-byte aligned frames), else the two-pass kernels
+    const bool fused = !ctx->force_two_pass && (N % 4 == 0) && ((uintptr_t)d.xyz % 16 == 0) && ((uintptr_t)d.labels % 16 == 0) &&
+                       (upscale || d.label_size % 4 == 0) && N <= (1 << 26);
+    if (fused) {
+        const int tpf = (N + E2_SF_TILE - 1) / E2_SF_TILE;
+        int C = E2_SF_CLUSTER;
+        while (C > 1 && C > tpf) C >>= 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)n_frames * C);
+        cfg.blockDim = dim3(E2_SF_THREADS);
+        cfg.dynamicSmemBytes = sizeof(SegFusedSmem);
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = C;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (upscale) CU(cudaLaunchKernelEx(&cfg, seg_fused_kernel<true>, d));
+        else CU(cudaLaunchKernelEx(&cfg, seg_fused_kernel<false>, d));
+        LAUNCHED();
+    } else {
+        const dim3 sgrid((d.S + E2_SEG_WARPS - 1) / E2_SEG_WARPS, n_frames);
+        seg_count_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
+        seg_scan_kernel<<<n_frames, E2SEC_MAX_ENTITIES, 0, st>>>(d); LAUNCHED();
+        seg_scatter_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
+    }
     if (stage_slot >= 0) { CU(cudaEventRecord(ctx->slot_free[stage_slot], st)); ctx->slot_used[stage_slot] = true; }   // inputs consumed
     cudaEventRecord(ctx->ev[1], st);
     int rc = run_entity_stages(ctx, d, true, true, true, true);

@@ -484,3 +484,43 @@ def test_dropin_region_filter_cython(engine):
         f.region_filter_cython(pts.mean(0), pts[:, ::-1], 0, center, center, radius)       # not C-contiguous
     assert f.distance_cython(pts[0].copy(), pts[1].copy()) == float(
         np.sqrt((pts[0, 0] - pts[1, 0]) ** 2 + (pts[0, 1] - pts[1, 1]) ** 2 + (pts[0, 2] - pts[1, 2]) ** 2))
+
+
+# ---- single-pass cluster segmentation (seg_fused.cuh) against the two-pass kernels (seg.cuh) -----------------------
+@pytest.mark.parametrize("shape", [(320, 240, False), (640, 480, True), (64, 48, False), (252, 1, False), (250, 1, False), (2048, 3, False)])
+def test_seg_fused_equals_two_pass(shape, monkeypatch):
+    """The bulk-copy / cluster kernel and the two-pass fallback must give bit-identical records: same per-entity counts,
+    same raster order inside an entity, same transformed coordinates (so every downstream field is equal)."""
+    from manipulationlibrary_b200 import _native as nat
+    from manipulationlibrary_b200.engine import Engine
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    w, h, upscale = shape
+    recs = []
+    for two_pass in ("0", "1"):
+        monkeypatch.setenv("E2SEC_SEG_TWO_PASS", two_pass)
+        eng = Engine(0)
+        try:
+            if h >= 48:
+                s = SyntheticStream(width=w, height=h, n_objects=4, config=7, cycle=24)
+                p, keep = nat.make_params(**s.params())
+                ids = np.arange(8, 13)
+                xyz, lab = s.fetch(ids)
+                eng.configure(p, len(ids), s.N, keep)
+                if upscale:          # labels arrive at half resolution and are upscaled like cv2.resize (:1433)
+                    small = lab.reshape(len(ids), h, w)[:, ::2, ::2]
+                    recs.append(eng.process_batch(xyz, small, ids, label_shape=(h // 2, w // 2), image_shape=(h, w)))
+                else:
+                    recs.append(eng.process_batch(xyz, lab, ids))
+            else:                    # ragged sizes: N not a multiple of the tile, fewer tiles than the cluster has CTAs
+                fx = load_golden("pushing06_fixture")
+                p, keep = nat.make_params(fx["total_unique_labels"], 11, 2, None, 0.07, fx["translation"], fx["roll"], fx["ground"])
+                N = w * h
+                rng = np.random.default_rng(N)
+                xyz = (rng.normal(size=(3, N, 3)) * 0.05 + [0, 0, 1.0]).astype(np.float32)
+                xyz[rng.random((3, N)) < 0.1] = np.nan
+                lab = rng.choice([0, 2, 4, 5, 6, 11], size=(3, N)).astype(np.int32)
+                eng.configure(p, 3, N, keep)
+                recs.append(eng.process_batch(xyz, lab, [0, 3, 6]))
+        finally:
+            eng.close()
+    np.testing.assert_array_equal(recs[0], recs[1])
