@@ -92,41 +92,48 @@ __device__ __forceinline__ int cell_bin(double d2, double scale)
     return t >= (double)(E2_CELL_BINS - 1) ? E2_CELL_BINS - 1 : (int)t;
 }
 
-// box-box squared distance bounds from float boxes, float64 arithmetic in pdist's operation order
+// box-box squared distance bounds from the float boxes, in float32 with directed rounding: every step rounds the lower
+// bound down and the upper bound up, so  lo <= (exact real d^2 of any point pair) <= hi;  the final factor (1 -+ 2^-23)
+// absorbs the rounding of the reference's own float64 evaluation (dx*dx + dy*dy) + dz*dz (relative error < 2^-50).
+// float32 halves the pipe time of these O(cells^2) loops against float64 and needs no conversions.
+__device__ __forceinline__ float cell_pair_lo32(const CellSmem &s, int a, int b)
+{
+    float acc = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float alo = __uint_as_float(s.box[k][a]), ahi = __uint_as_float(s.box[3 + k][a]);
+        const float blo = __uint_as_float(s.box[k][b]), bhi = __uint_as_float(s.box[3 + k][b]);
+        const float g = fmaxf(fmaxf(__fsub_rd(alo, bhi), __fsub_rd(blo, ahi)), 0.0f);
+        acc = __fadd_rd(acc, __fmul_rd(g, g));
+    }
+    return __fmul_rd(acc, 0.99999988f);
+}
+__device__ __forceinline__ float cell_pair_hi32(const CellSmem &s, int a, int b)
+{
+    float acc = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float alo = __uint_as_float(s.box[k][a]), ahi = __uint_as_float(s.box[3 + k][a]);
+        const float blo = __uint_as_float(s.box[k][b]), bhi = __uint_as_float(s.box[3 + k][b]);
+        const float f = fmaxf(__fsub_ru(ahi, blo), __fsub_ru(bhi, alo));
+        acc = __fadd_ru(acc, __fmul_ru(f, f));
+    }
+    return __fmul_ru(acc, 1.00000012f);
+}
 __device__ __forceinline__ void cell_pair_d2(const CellSmem &s, int a, int b, double &dmin2, double &dmax2)
 {
-    double g[3], f[3];
+    float lo = 0.0f, hi = 0.0f;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const double alo = (double)__uint_as_float(s.box[k][a]), ahi = (double)__uint_as_float(s.box[3 + k][a]);
-        const double blo = (double)__uint_as_float(s.box[k][b]), bhi = (double)__uint_as_float(s.box[3 + k][b]);
-        g[k] = fmax(fmax(alo - bhi, blo - ahi), 0.0);
-        f[k] = fmax(ahi - blo, bhi - alo);
+        const float alo = __uint_as_float(s.box[k][a]), ahi = __uint_as_float(s.box[3 + k][a]);
+        const float blo = __uint_as_float(s.box[k][b]), bhi = __uint_as_float(s.box[3 + k][b]);
+        const float g = fmaxf(fmaxf(__fsub_rd(alo, bhi), __fsub_rd(blo, ahi)), 0.0f);
+        const float f = fmaxf(__fsub_ru(ahi, blo), __fsub_ru(bhi, alo));
+        lo = __fadd_rd(lo, __fmul_rd(g, g));
+        hi = __fadd_ru(hi, __fmul_ru(f, f));
     }
-    dmin2 = (g[0] * g[0] + g[1] * g[1]) + g[2] * g[2];
-    dmax2 = (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
-}
-__device__ __forceinline__ double cell_pair_dmax2(const CellSmem &s, int a, int b)
-{
-    double f[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const double alo = (double)__uint_as_float(s.box[k][a]), ahi = (double)__uint_as_float(s.box[3 + k][a]);
-        const double blo = (double)__uint_as_float(s.box[k][b]), bhi = (double)__uint_as_float(s.box[3 + k][b]);
-        f[k] = fmax(ahi - blo, bhi - alo);
-    }
-    return (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
-}
-__device__ __forceinline__ double cell_pair_dmin2(const CellSmem &s, int a, int b)
-{
-    double g[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const double alo = (double)__uint_as_float(s.box[k][a]), ahi = (double)__uint_as_float(s.box[3 + k][a]);
-        const double blo = (double)__uint_as_float(s.box[k][b]), bhi = (double)__uint_as_float(s.box[3 + k][b]);
-        g[k] = fmax(fmax(alo - bhi, blo - ahi), 0.0);
-    }
-    return (g[0] * g[0] + g[1] * g[1]) + g[2] * g[2];
+    dmin2 = (double)__fmul_rd(lo, 0.99999988f);
+    dmax2 = (double)__fmul_ru(hi, 1.00000012f);
 }
 // the same between a point and a box
 __device__ __forceinline__ double cell_point_dmax2(const CellSmem &s, const double *p, int b)
@@ -528,6 +535,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
 
         // ---- E: cell closure at r_lo ---------------------------------------------------------------------------------
         const double t_lo = s.t_lo, t_hi = s.t_hi;
+        const float t_lo32 = __double2float_rd(t_lo), t_hi32 = __double2float_ru(t_hi);     // conservative float32 copies of the thresholds
         {
             const double sp[3] = {s.seedp[0], s.seedp[1], s.seedp[2]};
             for (int b = tid; b < m; b += E2_CELL_THREADS)
@@ -552,7 +560,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
                 const int b = s.rest[r];
                 if (s.member[b]) continue;
                 bool hit = false;
-                for (unsigned q = lane; q < nf && !hit; q += 32) hit = cell_pair_dmax2(s, (int)s.front[cur][q], b) <= t_lo;
+                for (unsigned q = lane; q < nf && !hit; q += 32) hit = cell_pair_hi32(s, (int)s.front[cur][q], b) <= t_lo32;
                 if (__any_sync(0xffffffffu, hit) && lane == 0) { s.member[b] = 1; s.front[cur ^ 1][atomicAdd(&s.n_new, 1u)] = (unsigned short)b; }
             }
             cur ^= 1;
@@ -572,7 +580,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
                 bool hit = false;
                 for (int a = lane; a < m && !hit; a += 32) {
                     if (!s.member[a] && !s.cand[a]) continue;
-                    hit = cell_pair_dmin2(s, a, b) <= t_hi;
+                    hit = cell_pair_lo32(s, a, b) <= t_hi32;
                 }
                 if (__any_sync(0xffffffffu, hit) && lane == 0) { s.cand[b] = 1; atomicAdd(&s.n_new, s.cnt[b]); atomicAdd(&s.n_cand, s.cnt[b]); }
             }

@@ -156,7 +156,34 @@ __device__ __forceinline__ unsigned contact_push(ContactSmem &s, bool take, doub
     return count + tot;
 }
 
-__global__ void __launch_bounds__(E2_CT_THREADS) contact_work_kernel(Dev d, ContactPlan plan)
+// Four candidates per thread at once: all loads of a 1024-point tile are in flight together and the tile costs one
+// pair of block barriers instead of four.  Order inside the tile is warp-major (irrelevant for a minimum).
+__device__ __forceinline__ unsigned contact_push4(ContactSmem &s, const bool take[4], const double x[4], const double y[4],
+                                                  const double z[4], bool with_f32, double ox, double oy, double oz)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned bal[4], wtot = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { bal[k] = __ballot_sync(0xffffffffu, take[k]); wtot += __popc(bal[k]); }
+    if (lane == 0) s.wcnt[warp] = wtot;
+    __syncthreads();
+    unsigned before = 0, tot = 0;
+    for (int w = 0; w < E2_CT_THREADS / 32; ++w) { const unsigned c = s.wcnt[w]; if (w < warp) before += c; tot += c; }
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (take[k]) {
+            const unsigned p = before + __popc(bal[k] & lt);
+            s.dx[p] = x[k]; s.dy[p] = y[k]; s.dz[p] = z[k];
+            if (with_f32) { s.fx[p] = (float)(x[k] - ox); s.fy[p] = (float)(y[k] - oy); s.fz[p] = (float)(z[k] - oz); }
+        }
+        before += __popc(bal[k]);
+    }
+    __syncthreads();
+    return tot;
+}
+
+__global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, ContactPlan plan)
 {
     __shared__ ContactSmem s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, K = d.K;
@@ -202,21 +229,27 @@ __global__ void __launch_bounds__(E2_CT_THREADS) contact_work_kernel(Dev d, Cont
         // ---- A chunk: points within thresh of B's box, and their own tight box ---------------------------------
         unsigned nA = 0;
         double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
-        for (int k = 0; k < E2_CT_CHUNK / E2_CT_THREADS; ++k) {
-            const int i = chunk * E2_CT_CHUNK + k * E2_CT_THREADS + tid;
-            bool take = false;
-            double x = 0, y = 0, z = 0;
-            if (i < na) {
-                const unsigned p = fla[i];
-                x = AX[p]; y = AY[p]; z = AZ[p];
-                take = point_box_d2(x, y, z, bb) <= lim2;
-                if (take) {
-                    mn[0] = fmin(mn[0], x); mx[0] = fmax(mx[0], x);
-                    mn[1] = fmin(mn[1], y); mx[1] = fmax(mx[1], y);
-                    mn[2] = fmin(mn[2], z); mx[2] = fmax(mx[2], z);
+        {
+            bool take[4];
+            double x[4], y[4], z[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = chunk * E2_CT_CHUNK + k * E2_CT_THREADS + tid;
+                take[k] = false;
+                x[k] = y[k] = z[k] = 0.0;
+                if (i < na) { const unsigned p = fla[i]; x[k] = AX[p]; y[k] = AY[p]; z[k] = AZ[p]; }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = chunk * E2_CT_CHUNK + k * E2_CT_THREADS + tid;
+                take[k] = (i < na) && point_box_d2(x[k], y[k], z[k], bb) <= lim2;
+                if (take[k]) {
+                    mn[0] = fmin(mn[0], x[k]); mx[0] = fmax(mx[0], x[k]);
+                    mn[1] = fmin(mn[1], y[k]); mx[1] = fmax(mx[1], y[k]);
+                    mn[2] = fmin(mn[2], z[k]); mx[2] = fmax(mx[2], z[k]);
                 }
             }
-            nA = contact_push(s, take, x, y, z, nA, false, 0, 0, 0);
+            nA = contact_push4(s, take, x, y, z, false, 0, 0, 0);
         }
         if (nA == 0) continue;
         for (int k = 0; k < 3; ++k) {
@@ -257,16 +290,21 @@ __global__ void __launch_bounds__(E2_CT_THREADS) contact_work_kernel(Dev d, Cont
         for (int base = 0; base < nb; base += E2_CT_TILE) {
             __syncthreads();                                     // the previous tile (or the A staging) is consumed
             unsigned mB = 0;
-            for (int k = 0; k < E2_CT_TILE / E2_CT_THREADS; ++k) {
-                const int j = base + k * E2_CT_THREADS + tid;
-                bool take = false;
-                double x = 0, y = 0, z = 0;
-                if (j < nb) {
-                    const unsigned q = flb ? flb[j] : (unsigned)j;
-                    x = BX[q]; y = BY[q]; z = BZ[q];
-                    take = point_box_d2(x, y, z, cb) <= best;   // nothing farther than the current minimum can improve it
+            {
+                bool take[4];
+                double x[4], y[4], z[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int j = base + k * E2_CT_THREADS + tid;
+                    x[k] = y[k] = z[k] = 0.0;
+                    if (j < nb) { const unsigned q = flb ? flb[j] : (unsigned)j; x[k] = BX[q]; y[k] = BY[q]; z[k] = BZ[q]; }
                 }
-                mB = contact_push(s, take, x, y, z, mB, true, ox, oy, oz);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int j = base + k * E2_CT_THREADS + tid;
+                    take[k] = (j < nb) && point_box_d2(x[k], y[k], z[k], cb) <= best;   // nothing farther than the current minimum can improve it
+                }
+                mB = contact_push4(s, take, x, y, z, true, ox, oy, oz);
             }
             for (unsigned j = 0; j < mB; ++j) {
                 const float bx = s.fx[j], by = s.fy[j], bz = s.fz[j];
