@@ -264,23 +264,33 @@ def run_b200(args):
         else:
             eng.process_batch_device_async(hx_t[s].data_ptr(), hl_t[s].data_ptr(), B, ids, N, records=out, on_device=False)
 
-    def finish(n_steps, first_step):
-        """one gather of the records (N > 1) + the sequential phase 2 on rank 0"""
+    def resolve_shards(full, per):
+        """phase 2 on rank 0: every shard is its own sequence in this benchmark, so the shards resolve side by side
+        (the feed is one C call per shard and releases the GIL)"""
+        def one(r):
+            res = Resolver(p, keep)
+            res.feed(full[r * per: (r + 1) * per])
+            n = res.n_columns
+            res.close()
+            return n
+        if world == 1:
+            return one(0)
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(world, os.cpu_count() or 1)) as ex:
+            return sum(ex.map(one, range(world)))
+
+    def finish(n_steps, first_step, res=None, fed=0):
+        """one gather of the records (N > 1) + the sequential phase 2 on rank 0.  With one GPU the resolver has been
+        following the batches while the GPU worked (`res` has seen `fed` batches); the rest is fed here."""
         eng.sync()                                     # all queued batches done, records on the host, errors raised
         local_rec = rec_np[first_step * B: (first_step + n_steps) * B]
-        if world > 1:
-            full = gather_records(local_rec, n_steps * B * world, world, device=dev)
-        else:
-            full = local_rec
-        cols = 0
-        if rank == 0:
-            per = n_steps * B
-            for r in range(world):                     # every shard is its own sequence in this benchmark
-                res = Resolver(p, keep)
-                res.feed(full[r * per: (r + 1) * per])
-                cols += res.n_columns
-                res.close()
-        return cols
+        if res is not None:
+            res.feed(local_rec[fed * B:])
+            cols = res.n_columns
+            res.close()
+            return cols
+        full = gather_records(local_rec, n_steps * B * world, world, device=dev)
+        return resolve_shards(full, n_steps * B) if rank == 0 else 0
 
     def barrier():
         if world > 1:
@@ -295,9 +305,21 @@ def run_b200(args):
         t0 = time.perf_counter()
         with torch.cuda.stream(est):
             ev0.record()
+        # one GPU: phase 2 (host, sequential) runs one batch behind the GPU instead of after it
+        res = Resolver(p, keep) if world == 1 else None
+        done, fed = [], 0
         for i in range(n_steps):
             step(first_step + i, on_device)
-        cols = finish(n_steps, first_step)
+            if res is not None:
+                with torch.cuda.stream(est):
+                    e = torch.cuda.Event()
+                    e.record()
+                done.append(e)
+                if i >= 1:
+                    done[i - 1].synchronize()          # batch i-1 is on the host; batch i keeps the GPU busy meanwhile
+                    res.feed(rec_np[(first_step + i - 1) * B: (first_step + i) * B])
+                    fed = i
+        cols = finish(n_steps, first_step, res, fed)
         with torch.cuda.stream(est):
             ev1.record()
         barrier()

@@ -34,6 +34,7 @@ def build(force=False, verbose=False):
            "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-fvisibility=default", "-shared", "-o", LIB]
     if verbose:
         cmd += ["-Xptxas", "-v"]
+    cmd += os.environ.get("E2SEC_NVCC_FLAGS", "").split()          # tuning experiments (-DE2_CELL_THREADS=256 ...)
     cmd += [os.path.join(CSRC, s) for s in SOURCES]
     cmd += ["-lcudart"]
     subprocess.check_call(cmd)

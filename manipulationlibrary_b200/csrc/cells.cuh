@@ -24,7 +24,12 @@
 #include "common.cuh"
 #include "filter.cuh"
 
+#ifndef E2_CELL_THREADS
 #define E2_CELL_THREADS 512
+#endif
+#ifndef E2_CELL_CTAS
+#define E2_CELL_CTAS 2              // resident CTAs per SM the register budget is cut for
+#endif
 #define E2_CELL_WARPS (E2_CELL_THREADS / 32)
 #define E2_CELL_MAX 1024          // occupied cells per entity
 #define E2_CELL_HASH 4096         // hash slots (power of two)
@@ -308,10 +313,10 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
             if (m2[a] != E2_M_COLLECT) continue;
             const unsigned c = s.m_ccnt[a];
             const unsigned r1 = k1 - s.m_below[a] - s.m_before[a], r2 = k2 - s.m_below[a] - s.m_before[a];
-            if ((unsigned)tid < c) {
-                const double v = s.mcand[a][tid];
+            for (unsigned t = tid; t < c; t += E2_CELL_THREADS) {
+                const double v = s.mcand[a][t];
                 unsigned rank = 0;
-                for (unsigned j = 0; j < c; ++j) { const double w = s.mcand[a][j]; rank += (w < v) || (w == v && j < (unsigned)tid); }
+                for (unsigned j = 0; j < c; ++j) { const double w = s.mcand[a][j]; rank += (w < v) || (w == v && j < t); }
                 if (rank == r1) s.m_a[a] = v;
                 if (rank == r2) s.m_b[a] = v;
             }
@@ -328,7 +333,7 @@ extern __shared__ __align__(16) unsigned char cell_smem_raw[];
 // grid F*K CTAs of E2_CELL_THREADS. Needs d.med (axis_median_kernel). Writes, for every filtered entity that it can
 // decide: seed_pos, flist, n_list, aabb, mean, rad_lo / rad_hi, amb = 0; for the others amb = 1 (exact path follows).
 // Entities that are not stored or have <= 3 points are finished here too (raw cloud, :1543-1546).
-__global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
+__global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_kernel(Dev d)
 {
     CellSmem &s = *reinterpret_cast<CellSmem *>(cell_smem_raw);
     const int fe = blockIdx.x, f = fe / d.K;
@@ -595,7 +600,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
         else if (nU > 0 && !s.amb) {
             for (int i = tid; i < n; i += E2_CELL_THREADS)
                 if (s.cand[pcell[i]]) s.ulist[atomicAdd(&s.n_front, 1u)] = (unsigned)i;
-            if (tid < E2_CELL_UMAX) s.joined[tid] = 0;
+            for (int u = tid; u < E2_CELL_UMAX; u += E2_CELL_THREADS) s.joined[u] = 0;
             if (tid == 0) s.member[E2_CELL_JOIN] = 1;            // virtual cell of the points that join here
             __syncthreads();
             for (;;) {
@@ -620,7 +625,8 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, 2) cell_filter_kernel(Dev d)
                 if (!grew) break;
             }
             // the last round changed nothing: udist is measured against the final member set
-            if (tid < nU && !s.joined[tid] && s.udist[tid] <= t_hi) s.amb = 1;      // reachable at r_hi but not at r_lo
+            for (unsigned u = tid; u < nU; u += E2_CELL_THREADS)
+                if (!s.joined[u] && s.udist[u] <= t_hi) s.amb = 1;      // reachable at r_hi but not at r_lo
         }
         __syncthreads();
         decided = !s.amb;

@@ -22,6 +22,7 @@
 //            entity (stable) and writes the transformed float64 SoA points + raster indices.
 #pragma once
 #include <cooperative_groups.h>
+#include <limits.h>
 
 #include "common.cuh"
 #include "seg.cuh"
@@ -32,14 +33,14 @@
 #define E2_SF_TILE 128             // points per warp tile = 4 per lane
 #define E2_SF_STAGES 3
 #define E2_SF_CLUSTER 8
-#define E2_SF_UNTRACKED 0x80u      // byte LUT: bit 7 = label not in total_unique_labels, bit 6 = raw label is hand_label
-#define E2_SF_HAND 0x40u
+#define E2_SF_ZERO 0x40u           // class byte: bits 0-5 = stored entity (0: none), bit 6 = index 0 of total_unique_labels,
+#define E2_SF_GROUND 0x80u         //             bit 7 = the ground entity (both are counted, never stored, :1520)
 
 struct SegFusedSmem {
     float4 xs[E2_SF_WARPS][E2_SF_STAGES][E2_SF_TILE * 3 / 4];     // 1536 B per stage: xyz of one warp tile
     int4 ls[E2_SF_WARPS][E2_SF_STAGES][E2_SF_TILE / 4];           //  512 B per stage: its labels
     uint64_t full[E2_SF_WARPS][E2_SF_STAGES];
-    unsigned char lut8[E2SEC_LABEL_LUT];
+    unsigned char lut8[E2SEC_LABEL_LUT + 16];          // + the empty entry that out-of-range labels clamp to
     unsigned cnt[E2SEC_MAX_ENTITIES];                  // valid points per entity in this CTA's tiles
     unsigned tot[E2SEC_MAX_ENTITIES], bef[E2SEC_MAX_ENTITIES], base[E2SEC_MAX_ENTITIES];
     unsigned wc[E2_SF_WARPS][E2SEC_MAX_ENTITIES];
@@ -95,25 +96,28 @@ __global__ void __launch_bounds__(E2_SF_THREADS, 4) seg_fused_kernel(Dev d)
     }
     for (int e = tid; e < E2SEC_MAX_ENTITIES; e += E2_SF_THREADS) s.cnt[e] = 0;
     for (int e = tid; e < E2_SF_WARPS * E2SEC_MAX_ENTITIES; e += E2_SF_THREADS) (&s.wc[0][0])[e] = 0;
-    for (int raw = tid; raw < E2SEC_LABEL_LUT; raw += E2_SF_THREADS) {
-        const int e = __ldg(d.lut + raw);
-        s.lut8[raw] = (unsigned char)((e < 0 ? E2_SF_UNTRACKED : (unsigned)e) | (raw == d.hand_label ? E2_SF_HAND : 0u));
+    for (int raw = tid; raw <= E2SEC_LABEL_LUT; raw += E2_SF_THREADS) {
+        const int e = raw < E2SEC_LABEL_LUT ? __ldg(d.lut + raw) : -1;
+        s.lut8[raw] = (unsigned char)(e < 0 ? 0u : e == 0 ? E2_SF_ZERO : e == gi ? E2_SF_GROUND : (unsigned)e);
     }
     __syncthreads();
 
     // ---- phase 1 ---------------------------------------------------------------------------------------------------
-    unsigned run = 0, c_zero = 0, c_ground = 0, hand_seen = 0;
+    unsigned run = 0, c_zero = 0, c_ground = 0;
+    bool hand_seen = false;
+    const int hand_label = d.hand_label;
     for (int i = 0; i < nt; ++i) {
         const int st = i % E2_SF_STAGES;
         mbar_wait(&full[st], (unsigned)(i / E2_SF_STAGES) & 1u);
         const float4 a = s.xs[warp][st][3 * lane], b = s.xs[warp][st][3 * lane + 1], c = s.xs[warp][st][3 * lane + 2];
-        int4 l = make_int4(-1, -1, -1, -1);
+        int4 l = make_int4(INT_MIN, INT_MIN, INT_MIN, INT_MIN);
         if (!UPSCALE) l = s.ls[warp][st][lane];
         __syncwarp();                                          // every lane has read the stage
         if (lane == 0 && i + E2_SF_STAGES < nt) issue(i + E2_SF_STAGES);
         const float px[4] = {a.x, a.w, b.z, c.y}, py[4] = {a.y, b.x, b.w, c.z}, pz[4] = {a.z, b.y, c.x, c.w};
         const int p0 = (t0 + i) * E2_SF_TILE + 4 * lane;
         const bool in = p0 < N;                                // N % 4 == 0: a lane's four points are inside together
+        if (!UPSCALE && !in) l = make_int4(INT_MIN, INT_MIN, INT_MIN, INT_MIN);     // stale shared memory past the frame's end
         int raw[4] = {l.x, l.y, l.z, l.w};
         if (UPSCALE && in) {
 #pragma unroll
@@ -123,36 +127,37 @@ __global__ void __launch_bounds__(E2_SF_THREADS, 4) seg_fused_kernel(Dev d)
                 raw[j] = __ldg(lab + __ldg(d.rowmap + rr) * d.label_w + __ldg(d.colmap + cc));
             }
         }
-        int ent[4];
-        unsigned mine = 0;
+        // one class byte per point, packed: bits 0-5 stored entity (0 = none), 0x40 = index 0, 0x80 = ground
+        unsigned w4 = 0;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int rw = raw[j];
-            unsigned code = ((unsigned)rw < (unsigned)E2SEC_LABEL_LUT) ? (unsigned)s.lut8[rw]
-                                                                         : (E2_SF_UNTRACKED | (rw == d.hand_label ? E2_SF_HAND : 0u));
-            if (!in) code = E2_SF_UNTRACKED;
-            hand_seen |= code & E2_SF_HAND;                    // :1429 looks at the raw label image, valid point or not
-            const bool valid = coord_valid(px[j]) && coord_valid(py[j]) && coord_valid(pz[j]);
-            const int e = ((code & E2_SF_UNTRACKED) || !valid) ? -1 : (int)(code & 63u);
-            c_zero += (e == 0);
-            c_ground += (e == gi);
-            const bool stored = e > 0 && e != gi;
-            ent[j] = stored ? e : -1;
-            mine += stored;
+            hand_seen |= (rw == hand_label);                   // :1429 looks at the raw label image, valid point or not
+            unsigned code = s.lut8[min((unsigned)rw, (unsigned)E2SEC_LABEL_LUT)];      // out of range -> the empty entry
+            if (!(coord_valid(px[j]) && coord_valid(py[j]) && coord_valid(pz[j]))) code = 0;
+            w4 |= code << (8 * j);
         }
-        if (__any_sync(0xffffffffu, mine != 0)) {
+        c_zero += __popc(w4 & 0x40404040u);
+        c_ground += __popc(w4 & 0x80808080u);
+        const unsigned e4 = w4 & 0x3f3f3f3fu;
+        if (__any_sync(0xffffffffu, e4 != 0)) {                // ground / border / NaN tiles never get here
+            unsigned mine = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mine += ((e4 >> (8 * j)) & 63u) != 0;
             unsigned incl = mine;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
             unsigned pos = run + incl - mine;
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (ent[j] >= 0) {
+            for (int j = 0; j < 4; ++j) {
+                const unsigned e = (e4 >> (8 * j)) & 63u;
+                if (e) {
                     uint4 rec;
                     rec.x = __float_as_uint(px[j]); rec.y = __float_as_uint(py[j]); rec.z = __float_as_uint(pz[j]);
-                    rec.w = ((unsigned)(p0 + j) << 6) | (unsigned)ent[j];
+                    rec.w = ((unsigned)(p0 + j) << 6) | e;
                     list[pos++] = rec;
                 }
+            }
             run += __shfl_sync(0xffffffffu, incl, 31);
         }
     }
@@ -162,7 +167,7 @@ __global__ void __launch_bounds__(E2_SF_THREADS, 4) seg_fused_kernel(Dev d)
         if (c_zero) atomicAdd(&s.cnt[0], c_zero);
         if (c_ground) atomicAdd(&s.cnt[gi], c_ground);
     }
-    if (__any_sync(0xffffffffu, hand_seen != 0) && lane == 0) atomicOr(d.flags + f, E2SEC_FLAG_HAND_LABEL);
+    if (__any_sync(0xffffffffu, hand_seen) && lane == 0) atomicOr(d.flags + f, E2SEC_FLAG_HAND_LABEL);
     __syncwarp();                                              // the warp's list entries are visible to all its lanes
 
     // ---- phase 2: entity counts of the warp lists, then the frame's totals through distributed shared memory ------
