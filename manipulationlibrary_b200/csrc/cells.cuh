@@ -335,6 +335,7 @@ extern __shared__ __align__(16) unsigned char cell_smem_raw[];
 // Entities that are not stored or have <= 3 points are finished here too (raw cloud, :1543-1546).
 __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_kernel(Dev d)
 {
+    pdl_enter();
     CellSmem &s = *reinterpret_cast<CellSmem *>(cell_smem_raw);
     const int fe = blockIdx.x, f = fe / d.K;
     const int off = d.ent_off[fe], n = d.ent_raw[fe];

@@ -94,6 +94,15 @@ struct Dev {
     int *error;                       // device error flag
 };
 
+// Programmatic dependent launch (e2sec_api.cu: launch_pdl): wait until the grids this one depends on have completed and
+// their writes are visible, then let the NEXT grid of the stream start its own launch; it parks at the same wait.
+// A no-op for a kernel launched without the attribute.  Must run before the first global-memory access.
+__device__ __forceinline__ void pdl_enter()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 __device__ __forceinline__ u64 d2key(double v) { return (u64)__double_as_longlong(v); }
 __device__ __forceinline__ double key2d(u64 k) { return __longlong_as_double((long long)k); }
 

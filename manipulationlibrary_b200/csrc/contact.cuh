@@ -64,6 +64,7 @@ __device__ __forceinline__ ContactSlot contact_decode(const Dev &d, int f, int s
 
 __global__ void contact_plan_kernel(Dev d, ContactPlan plan)
 {
+    pdl_enter();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx == 0) *plan.next = 0;
     if (idx >= d.F * plan.slots) return;
@@ -94,6 +95,7 @@ __global__ void contact_plan_kernel(Dev d, ContactPlan plan)
 // single CTA of 1024 threads: exclusive scan of plan.cnt -> plan.off
 __global__ void __launch_bounds__(1024) contact_scan_kernel(ContactPlan plan, int n)
 {
+    pdl_enter();
     __shared__ unsigned warp_tot[32];
     __shared__ unsigned carry;
     if (threadIdx.x == 0) carry = 0;
@@ -185,6 +187,7 @@ __device__ __forceinline__ unsigned contact_push4(ContactSmem &s, const bool tak
 
 __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, ContactPlan plan)
 {
+    pdl_enter();
     __shared__ ContactSmem s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, K = d.K;
     const int n_idx = d.F * plan.slots;

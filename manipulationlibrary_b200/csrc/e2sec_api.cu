@@ -50,6 +50,8 @@ struct e2sec_ctx {
     cudaEvent_t ev[8];
     bool ev_valid = false;
     int sm_count = 148;
+    int sf_cluster = 8;
+    bool pdl = true;
     bool force_two_pass = false;   // E2SEC_SEG_TWO_PASS=1: always take the two-pass segmentation (tests compare both)
 };
 
@@ -118,6 +120,8 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     cudaFuncSetAttribute(seg_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
     cudaFuncSetAttribute(seg_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
     { const char *e = getenv("E2SEC_SEG_TWO_PASS"); ctx->force_two_pass = e && e[0] == '1'; }
+    { const char *e = getenv("E2SEC_PDL"); ctx->pdl = !(e && e[0] == '0'); }
+    { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
     ctx->bufs = {&ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
@@ -371,6 +375,26 @@ static int upload_maps(e2sec_ctx *ctx, int lw, int lh, int width, int height)
 
 #define LAUNCHED() do { ++ctx->launches; } while (0)
 
+// Kernels of the per-batch pipeline are launched with programmatic stream serialization: every one of them starts with
+// griddepcontrol.wait (common.cuh: pdl_enter), so the next grid's launch latency and prologue hide behind the tail of the
+// previous one instead of adding a gap per launch (33 launches per batch).  E2SEC_PDL=0 falls back to plain ordering.
+template <class... P, class... A>
+static inline void launch_pdl(e2sec_ctx *ctx, void (*k)(P...), dim3 g, dim3 b, size_t smem, cudaStream_t st, A... a)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = g;
+    cfg.blockDim = b;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = ctx->pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, k, P(a)...);
+    ++ctx->launches;
+}
+
 // Everything after segmentation: medians, radius, filter, stats, pairs, records. `d` already describes the batch.
 static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, bool need_radius, bool do_pairs, bool do_records)
 {
@@ -379,44 +403,44 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
     PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p};
     u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
     // BOUNDED mode selects the medians inside cell_filter_kernel
-    if (need_median && d.radius_mode != E2SEC_RADIUS_BOUNDED) { axis_median_kernel<<<dim3(3, FK), E2_SEL_THREADS, 0, st>>>(d); LAUNCHED(); }
+    if (need_median && d.radius_mode != E2SEC_RADIUS_BOUNDED) { launch_pdl(ctx, axis_median_kernel, dim3(dim3(3, FK)), dim3(E2_SEL_THREADS), 0, st, d); }
     cudaEventRecord(ctx->ev[2], st);
     if (d.radius_mode == E2SEC_RADIUS_BOUNDED) {
-        cell_filter_kernel<<<FK, E2_CELL_THREADS, sizeof(CellSmem), st>>>(d); LAUNCHED();
+        launch_pdl(ctx, cell_filter_kernel, dim3(FK), dim3(E2_CELL_THREADS), sizeof(CellSmem), st, d);
     }
     if (need_radius) {
         CU(cudaMemsetAsync(below_acc, 0, sizeof(u64) * FK, st));
         CU(cudaMemsetAsync(single, 0, sizeof(u64) * FK, st));
-        radius_init_kernel<<<FK, 256, 0, st>>>(d, min_above); LAUNCHED();
+        launch_pdl(ctx, radius_init_kernel, dim3(FK), dim3(256), 0, st, d, min_above);
         const int grid = ctx->sm_count * 3;
         const size_t smem = sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double);
         for (int round = 0; round < E2_MAX_REFINE; ++round) {
-            radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 0); LAUNCHED();
-            pair_pass_kernel<false><<<grid, E2_PAIR_THREADS, smem, st>>>(d, plan, below_acc, min_above); LAUNCHED();
-            radius_select_kernel<<<(FK + 127) / 128, 128, 0, st>>>(d, below_acc, single); LAUNCHED();
+            launch_pdl(ctx, radius_plan_kernel, dim3(1), dim3(1024), 0, st, d, plan, 0);
+            launch_pdl(ctx, pair_pass_kernel<false>, dim3(grid), dim3(E2_PAIR_THREADS), smem, st, d, plan, below_acc, min_above);
+            launch_pdl(ctx, radius_select_kernel, dim3((FK + 127) / 128), dim3(128), 0, st, d, below_acc, single);
         }
-        radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 1); LAUNCHED();
-        pair_pass_kernel<true><<<ctx->sm_count * 8, E2_PAIR_THREADS, 3 * E2_TILE * sizeof(double), st>>>(d, plan, below_acc, min_above); LAUNCHED();
-        radius_final_kernel<<<FK, E2_SEL_THREADS, 0, st>>>(d, min_above, single); LAUNCHED();
+        launch_pdl(ctx, radius_plan_kernel, dim3(1), dim3(1024), 0, st, d, plan, 1);
+        launch_pdl(ctx, pair_pass_kernel<true>, dim3(ctx->sm_count * 8), dim3(E2_PAIR_THREADS), 3 * E2_TILE * sizeof(double), st, d, plan, below_acc, min_above);
+        launch_pdl(ctx, radius_final_kernel, dim3(FK), dim3(E2_SEL_THREADS), 0, st, d, min_above, single);
     }
     cudaEventRecord(ctx->ev[3], st);
-    region_filter_kernel<<<FK, E2_FILTER_THREADS, 0, st>>>(d); LAUNCHED();
+    launch_pdl(ctx, region_filter_kernel, dim3(FK), dim3(E2_FILTER_THREADS), 0, st, d);
     cudaEventRecord(ctx->ev[4], st);
-    entity_stats_kernel<<<FK, E2_STATS_THREADS, 0, st>>>(d); LAUNCHED();
+    launch_pdl(ctx, entity_stats_kernel, dim3(FK), dim3(E2_STATS_THREADS), 0, st, d);
     cudaEventRecord(ctx->ev[5], st);
     if (do_pairs) {
-        prev_kept_kernel<<<1, 1024, 0, st>>>(d); LAUNCHED();
+        launch_pdl(ctx, prev_kept_kernel, dim3(1), dim3(1024), 0, st, d);
         ContactPlan cp{(unsigned *)ctx->ct_cnt.p, (unsigned *)ctx->ct_off.p, (unsigned *)ctx->ct_next.p,
                        d.K * (d.K - 1) / 2 + d.K + d.K * d.K};
         const int n_idx = d.F * cp.slots;
-        contact_plan_kernel<<<(n_idx + 255) / 256, 256, 0, st>>>(d, cp); LAUNCHED();
-        contact_scan_kernel<<<1, 1024, 0, st>>>(cp, n_idx); LAUNCHED();
-        contact_work_kernel<<<ctx->sm_count * 4, E2_CT_THREADS, 0, st>>>(d, cp); LAUNCHED();
-        halo_save_kernel<<<64, 256, 0, st>>>(d); LAUNCHED();
-        halo_commit_kernel<<<1, 1, 0, st>>>(d); LAUNCHED();
+        launch_pdl(ctx, contact_plan_kernel, dim3((n_idx + 255) / 256), dim3(256), 0, st, d, cp);
+        launch_pdl(ctx, contact_scan_kernel, dim3(1), dim3(1024), 0, st, cp, n_idx);
+        launch_pdl(ctx, contact_work_kernel, dim3(ctx->sm_count * 4), dim3(E2_CT_THREADS), 0, st, d, cp);
+        launch_pdl(ctx, halo_save_kernel, dim3(64), dim3(256), 0, st, d);
+        launch_pdl(ctx, halo_commit_kernel, dim3(1), dim3(1), 0, st, d);
     }
     cudaEventRecord(ctx->ev[6], st);
-    if (do_records) { assemble_kernel<<<d.F, 128, 0, st>>>(d); LAUNCHED(); }
+    if (do_records) { launch_pdl(ctx, assemble_kernel, dim3(d.F), dim3(128), 0, st, d); }
     cudaEventRecord(ctx->ev[7], st);
     CU(cudaGetLastError());
     return E2SEC_OK;
@@ -489,28 +513,30 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const int32_t *l
                        (upscale || d.label_size % 4 == 0) && N <= (1 << 26);
     if (fused) {
         const int tpf = (N + E2_SF_TILE - 1) / E2_SF_TILE;
-        int C = E2_SF_CLUSTER;
+        int C = ctx->sf_cluster;
         while (C > 1 && C > tpf) C >>= 1;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)n_frames * C);
         cfg.blockDim = dim3(E2_SF_THREADS);
         cfg.dynamicSmemBytes = sizeof(SegFusedSmem);
         cfg.stream = st;
-        cudaLaunchAttribute attr[1];
+        cudaLaunchAttribute attr[2];
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[1].val.programmaticStreamSerializationAllowed = 1;
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = C;
         attr[0].val.clusterDim.y = 1;
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = ctx->pdl ? 2 : 1;
         if (upscale) CU(cudaLaunchKernelEx(&cfg, seg_fused_kernel<true>, d));
         else CU(cudaLaunchKernelEx(&cfg, seg_fused_kernel<false>, d));
         LAUNCHED();
     } else {
         const dim3 sgrid((d.S + E2_SEG_WARPS - 1) / E2_SEG_WARPS, n_frames);
-        seg_count_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
-        seg_scan_kernel<<<n_frames, E2SEC_MAX_ENTITIES, 0, st>>>(d); LAUNCHED();
-        seg_scatter_kernel<<<sgrid, 32 * E2_SEG_WARPS, 0, st>>>(d); LAUNCHED();
+        launch_pdl(ctx, seg_count_kernel, dim3(sgrid), dim3(32 * E2_SEG_WARPS), 0, st, d);
+        launch_pdl(ctx, seg_scan_kernel, dim3(n_frames), dim3(E2SEC_MAX_ENTITIES), 0, st, d);
+        launch_pdl(ctx, seg_scatter_kernel, dim3(sgrid), dim3(32 * E2_SEG_WARPS), 0, st, d);
     }
     if (stage_slot >= 0) { CU(cudaEventRecord(ctx->slot_free[stage_slot], st)); ctx->slot_used[stage_slot] = true; }   // inputs consumed
     cudaEventRecord(ctx->ev[1], st);

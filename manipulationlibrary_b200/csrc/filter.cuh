@@ -103,6 +103,7 @@ struct FilterSmem {
 // grid F*K CTAs. flist / front_a / front_b / member are indexed like the stored points (f*cap + off + i).
 __global__ void __launch_bounds__(E2_FILTER_THREADS) region_filter_kernel(Dev d)
 {
+    pdl_enter();
     __shared__ FilterSmem sm;
     __shared__ Mt19937 rng;
     const int fe = blockIdx.x, f = fe / d.K, e = fe - f * d.K;

@@ -15,6 +15,7 @@
 
 __global__ void __launch_bounds__(E2_STATS_THREADS) entity_stats_kernel(Dev d)
 {
+    pdl_enter();
     __shared__ double red[6][E2_STATS_THREADS / 32];
     const int fe = blockIdx.x, f = fe / d.K;
     const int off = d.ent_off[fe];
@@ -84,6 +85,7 @@ __device__ __forceinline__ double box_box_d2(const double *a, const double *b)
 // the previous batches.
 __global__ void __launch_bounds__(1024) prev_kept_kernel(Dev d)
 {
+    pdl_enter();
     __shared__ unsigned char kept[1024];
     __shared__ int slot_s, id_s, last_s;
     if (threadIdx.x == 0) {
@@ -115,6 +117,7 @@ __global__ void __launch_bounds__(1024) prev_kept_kernel(Dev d)
 // Copies the last kept frame of the batch into the halo slot (grid-stride over its stored points).
 __global__ void halo_save_kernel(Dev d)
 {
+    pdl_enter();
     const int src = d.halo_info[2];
     if (src < 0) return;
     const int K = d.K, H = d.maxF;
@@ -137,6 +140,7 @@ __global__ void halo_save_kernel(Dev d)
 }
 __global__ void halo_commit_kernel(Dev d)     // after halo_save_kernel: publish the new halo
 {
+    pdl_enter();
     const int src = d.halo_info[2];
     if (src < 0) return;
     d.halo_info[0] = 1;
@@ -147,6 +151,7 @@ __global__ void halo_commit_kernel(Dev d)     // after halo_save_kernel: publish
 // cross pairs (entity a of the previous kept frame, entity b of this frame).
 __global__ void __launch_bounds__(E2_PD_THREADS) pair_distance_kernel(Dev d)
 {
+    pdl_enter();
     __shared__ double sx[E2_PD_TILE], sy[E2_PD_TILE], sz[E2_PD_TILE];
     __shared__ unsigned s_n;
     __shared__ double red[E2_PD_THREADS / 32];
@@ -240,6 +245,7 @@ __global__ void __launch_bounds__(E2_PD_THREADS) pair_distance_kernel(Dev d)
 // one CTA per frame
 __global__ void assemble_kernel(Dev d)
 {
+    pdl_enter();
     const int f = blockIdx.x, K = d.K;
     double *rec = d.records + (size_t)f * d.rec_doubles;
     const double NaN = __longlong_as_double(0x7ff8000000000000ll);

@@ -36,6 +36,7 @@ __device__ __forceinline__ int shift_for_width(u64 width)
 // grid F*K CTAs of 256 threads
 __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, u64 *min_above)
 {
+    pdl_enter();
     __shared__ double red[6][8];
     const int fe = blockIdx.x, f = fe / d.K;
     const int off = d.ent_off[fe], n = d.ent_raw[fe];
@@ -93,6 +94,7 @@ __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, u64 *min_above)
 // single CTA: items per entity for the wanted phase, exclusive scan
 __global__ void __launch_bounds__(1024) radius_plan_kernel(Dev d, PairPlan plan, int want_phase)
 {
+    pdl_enter();
     __shared__ unsigned warp_tot[32];
     __shared__ unsigned carry;
     const int n_fe = d.F * d.K;
@@ -152,6 +154,7 @@ extern __shared__ __align__(16) unsigned char pair_smem[];
 template <bool COLLECT>
 __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *min_above)
 {
+    pdl_enter();
     unsigned short *cnt = reinterpret_cast<unsigned short *>(pair_smem);
     double *sx = reinterpret_cast<double *>(pair_smem + (COLLECT ? 0 : sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS));
     double *sy = sx + E2_TILE, *sz = sy + E2_TILE;
@@ -266,6 +269,7 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
 // one thread per entity
 __global__ void radius_select_kernel(Dev d, u64 *below_acc, u64 *single_count)
 {
+    pdl_enter();
     const int fe = blockIdx.x * blockDim.x + threadIdx.x;
     if (fe >= d.F * d.K) return;
     RadiusState &rs = d.rs[fe];
@@ -313,6 +317,7 @@ __global__ void radius_select_kernel(Dev d, u64 *below_acc, u64 *single_count)
 // grid F*K CTAs of E2_SEL_THREADS
 __global__ void __launch_bounds__(E2_SEL_THREADS) radius_final_kernel(Dev d, const u64 *min_above, const u64 *single_count)
 {
+    pdl_enter();
     __shared__ SelectSmem sm;
     const int fe = blockIdx.x;
     RadiusState &rs = d.rs[fe];

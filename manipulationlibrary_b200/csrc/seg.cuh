@@ -60,6 +60,7 @@ __device__ __forceinline__ void transform_point(const double *M, double &x, doub
 
 __global__ void __launch_bounds__(32 * E2_SEG_WARPS) seg_count_kernel(Dev d)
 {
+    pdl_enter();
     __shared__ unsigned wcnt[E2_SEG_WARPS][E2SEC_MAX_ENTITIES];
     const int f = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int s = blockIdx.x * E2_SEG_WARPS + warp;
@@ -97,6 +98,7 @@ __global__ void __launch_bounds__(32 * E2_SEG_WARPS) seg_count_kernel(Dev d)
 // one CTA per frame, thread e scans entity e over the S segments
 __global__ void seg_scan_kernel(Dev d)
 {
+    pdl_enter();
     __shared__ int tot[E2SEC_MAX_ENTITIES];
     const int f = blockIdx.x, e = threadIdx.x;
     if (e < d.K) {
@@ -125,6 +127,7 @@ __global__ void seg_scan_kernel(Dev d)
 
 __global__ void __launch_bounds__(32 * E2_SEG_WARPS) seg_scatter_kernel(Dev d)
 {
+    pdl_enter();
     __shared__ unsigned wcnt[E2_SEG_WARPS][E2SEC_MAX_ENTITIES];
     const int f = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int s = blockIdx.x * E2_SEG_WARPS + warp;

@@ -62,6 +62,7 @@ extern __shared__ __align__(128) unsigned char seg_fused_smem_raw[];
 template <bool UPSCALE>
 __global__ void __launch_bounds__(E2_SF_THREADS, 4) seg_fused_kernel(Dev d)
 {
+    pdl_enter();
     namespace cg = cooperative_groups;
     cg::cluster_group cl = cg::this_cluster();
     SegFusedSmem &s = *reinterpret_cast<SegFusedSmem *>(seg_fused_smem_raw);

@@ -83,6 +83,7 @@ __device__ void block_select2(Get get, int n, u64 k1, u64 k2, u64 &v1, u64 &v2, 
 // np.median(objects[i], axis=0) for every filtered entity: grid (3, F*K), E2_SEL_THREADS threads.
 __global__ void __launch_bounds__(E2_SEL_THREADS) axis_median_kernel(Dev d)
 {
+    pdl_enter();
     __shared__ SelectSmem sm;
     const int fe = blockIdx.y, axis = blockIdx.x;
     const int f = fe / d.K, e = fe - f * d.K;
