@@ -45,6 +45,8 @@ def parse():
                     help="bounded: cell-table bounds of np.median(pdist) with exact fallback; exact: always the O(n^2) selection")
     ap.add_argument("--cpu-frames", type=int, default=4, help="frames of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-labels", default="u8", choices=["u8", "i32"],
+                    help="host label images of the e2e leg: uint8 (e2sec_process_batch_labels8, 13 B/point over PCIe) or int32")
     return ap.parse_args()
 
 
@@ -239,6 +241,8 @@ def run_b200(args):
     hx, hl = generate_pool(stream, rank_first, pool)
     hx_t = torch.from_numpy(hx).pin_memory()
     hl_t = torch.from_numpy(hl).pin_memory()
+    lab8 = args.e2e_labels == "u8" and not args.no_e2e and int(hl.max()) < 256 and int(hl.min()) >= 0
+    hl8_t = torch.from_numpy(hl.astype(np.uint8)).pin_memory() if lab8 else None     # what a uint8 label reader hands over
     dx = hx_t.to(dev, non_blocking=True)
     dl = hl_t.to(dev, non_blocking=True)
     torch.cuda.synchronize()
@@ -262,7 +266,8 @@ def run_b200(args):
         if on_device:
             eng.process_batch_device_async(dx[s].data_ptr(), dl[s].data_ptr(), B, ids, N, records=out)
         else:
-            eng.process_batch_device_async(hx_t[s].data_ptr(), hl_t[s].data_ptr(), B, ids, N, records=out, on_device=False)
+            eng.process_batch_device_async(hx_t[s].data_ptr(), (hl8_t if lab8 else hl_t)[s].data_ptr(), B, ids, N, records=out,
+                                           on_device=False, labels8=lab8)
 
     def resolve_shards(full, per):
         """phase 2 on rank 0: every shard is its own sequence in this benchmark, so the shards resolve side by side
@@ -356,8 +361,9 @@ def run_b200(args):
         step(0, False)
         eng.sync()
         ems, ewall, _, _, _ = timed(False, W, K)
-        e2e = {"value": frames / (ewall * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * N * BYTES_PER_POINT,
-               "d2h_bytes_per_step": B * rec_w * 8, "timing": "wall clock around the C-ABI calls, pinned host buffers"}
+        e2e = {"value": frames / (ewall * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * N * (13 if lab8 else BYTES_PER_POINT),
+               "d2h_bytes_per_step": B * rec_w * 8, "host_labels": "uint8" if lab8 else "int32",
+               "timing": "wall clock around the C-ABI calls, pinned host buffers"}
 
     if rank == 0:
         peaks = {}

@@ -41,6 +41,7 @@ struct e2sec_ctx {
     size_t cap_total = 0;          // stored-point capacity over the whole batch (maxF * N)
     Dev d;
     std::vector<DevBuf *> bufs;
+    DevBuf lab8_stage;
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
@@ -124,7 +125,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
-    ctx->bufs = {&ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
+    ctx->bufs = {&ctx->lab8_stage, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
                  &ctx->radius, &ctx->rs, &ctx->hist, &ctx->cand, &ctx->cand_n, &ctx->seed_pos, &ctx->member,
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
@@ -458,7 +459,16 @@ static int check_device_error(e2sec_ctx *ctx)
     return E2SEC_OK;
 }
 
-static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
+// uint8 label images (e2sec_process_batch_labels8): widened to int32 on the device, 4 labels per thread
+__global__ void labels_widen_kernel(const uchar4 *src, int4 *dst, size_t n4, const unsigned char *src1, int *dst1, size_t n)
+{
+    pdl_enter();
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n4) { const uchar4 v = src[i]; dst[i] = make_int4(v.x, v.y, v.z, v.w); }
+    if (i < n - 4 * n4) dst1[4 * n4 + i] = src1[4 * n4 + i];
+}
+
+static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labels, int label_bytes, int32_t n_frames,
                               int32_t label_w, int32_t label_h, int32_t width, int32_t height,
                               const int32_t *frame_ids, int on_device, double *records, bool wait)
 {
@@ -489,21 +499,35 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const int32_t *l
     d.label_w = label_w;
     int stage_slot = -1;
     cudaEventRecord(ctx->ev[0], st);
-    if (on_device) {
+    const size_t n_lab = (size_t)n_frames * (size_t)lsz;
+    if (label_bytes == 1 && ensure(ctx, ctx->lab8_stage, (size_t)2 * ctx->maxF * N)) return E2SEC_ERR_CUDA;
+    if (on_device && label_bytes == 4) {
         d.xyz = xyz;
-        d.labels = labels;
+        d.labels = (const int *)labels;
     } else {
         // slot s is refilled on the copy stream as soon as the kernels that read it two batches ago are done, so the
         // upload of this batch overlaps the kernels of the previous one when batches are queued asynchronously
         stage_slot = (int)(ctx->stage_idx++ & 1u);
         float *xs = (float *)ctx->xyz_stage.p + (size_t)stage_slot * ctx->maxF * N * 3;
         int *ls = (int *)ctx->lab_stage.p + (size_t)stage_slot * ctx->maxF * N;
-        if (ctx->slot_used[stage_slot]) CU(cudaStreamWaitEvent(ctx->copy_stream, ctx->slot_free[stage_slot], 0));
-        CU(cudaMemcpyAsync(xs, xyz, (size_t)n_frames * N * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->copy_stream));
-        CU(cudaMemcpyAsync(ls, labels, (size_t)n_frames * lsz * sizeof(int), cudaMemcpyHostToDevice, ctx->copy_stream));
-        CU(cudaEventRecord(ctx->copy_done[stage_slot], ctx->copy_stream));
-        CU(cudaStreamWaitEvent(st, ctx->copy_done[stage_slot], 0));
-        d.xyz = xs;
+        unsigned char *l8 = label_bytes == 1 ? (unsigned char *)ctx->lab8_stage.p + (size_t)stage_slot * ctx->maxF * N : nullptr;
+        const unsigned char *src8 = (const unsigned char *)labels;
+        d.xyz = xyz;
+        if (!on_device) {
+            if (ctx->slot_used[stage_slot]) CU(cudaStreamWaitEvent(ctx->copy_stream, ctx->slot_free[stage_slot], 0));
+            CU(cudaMemcpyAsync(xs, xyz, (size_t)n_frames * N * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->copy_stream));
+            if (label_bytes == 1) CU(cudaMemcpyAsync(l8, labels, n_lab, cudaMemcpyHostToDevice, ctx->copy_stream));
+            else CU(cudaMemcpyAsync(ls, labels, n_lab * sizeof(int), cudaMemcpyHostToDevice, ctx->copy_stream));
+            CU(cudaEventRecord(ctx->copy_done[stage_slot], ctx->copy_stream));
+            CU(cudaStreamWaitEvent(st, ctx->copy_done[stage_slot], 0));
+            d.xyz = xs;
+            src8 = l8;
+        }
+        if (label_bytes == 1) {
+            const size_t n4 = ((uintptr_t)src8 % 4 == 0 && (uintptr_t)ls % 16 == 0) ? n_lab / 4 : 0, work = n4 > n_lab - 4 * n4 ? n4 : n_lab - 4 * n4;
+            launch_pdl(ctx, labels_widen_kernel, dim3((unsigned)((work + 255) / 256)), dim3(256), 0, st, (const uchar4 *)src8,
+                       (int4 *)ls, n4, src8, ls, n_lab);
+        }
         d.labels = ls;
     }
     CU(cudaMemcpyAsync(ctx->frame_ids.p, frame_ids, n_frames * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -551,14 +575,28 @@ extern "C" int e2sec_process_batch(e2sec_ctx *ctx, const float *xyz, const int32
                                    int32_t label_w, int32_t label_h, int32_t width, int32_t height,
                                    const int32_t *frame_ids, int on_device, double *records)
 {
-    return process_batch_impl(ctx, xyz, labels, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, true);
+    return process_batch_impl(ctx, xyz, labels, 4, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, true);
 }
 
 extern "C" int e2sec_process_batch_async(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
                                          int32_t label_w, int32_t label_h, int32_t width, int32_t height,
                                          const int32_t *frame_ids, int on_device, double *records)
 {
-    return process_batch_impl(ctx, xyz, labels, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, false);
+    return process_batch_impl(ctx, xyz, labels, 4, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, false);
+}
+
+extern "C" int e2sec_process_batch_labels8(e2sec_ctx *ctx, const float *xyz, const uint8_t *labels, int32_t n_frames,
+                                           int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                                           const int32_t *frame_ids, int on_device, double *records)
+{
+    return process_batch_impl(ctx, xyz, labels, 1, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, true);
+}
+
+extern "C" int e2sec_process_batch_labels8_async(e2sec_ctx *ctx, const float *xyz, const uint8_t *labels, int32_t n_frames,
+                                                 int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                                                 const int32_t *frame_ids, int on_device, double *records)
+{
+    return process_batch_impl(ctx, xyz, labels, 1, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, false);
 }
 
 extern "C" int e2sec_stage_ms(e2sec_ctx *ctx, float out[8])

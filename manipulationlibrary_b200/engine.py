@@ -51,10 +51,17 @@ class Engine:
         """xyz (F, N, 3) float32, labels (F, N) or (F, h, w) int32 (host numpy). -> records (F, rec) float64."""
         xyz = np.ascontiguousarray(xyz, np.float32)
         F = xyz.shape[0]
-        labels = np.ascontiguousarray(labels, np.int32).reshape(F, -1)
+        labels = np.asarray(labels)
         fid = np.ascontiguousarray(frame_ids, np.int32)
-        lw, lh, w, h = self._shapes(labels.shape[1], label_shape, image_shape)
         rec = np.empty((F, nat.record_doubles(self.K)), np.float64)
+        if labels.dtype == np.uint8:                   # uint8 label images travel as they are (13 B/point over PCIe)
+            labels = np.ascontiguousarray(labels).reshape(F, -1)
+            lw, lh, w, h = self._shapes(labels.shape[1], label_shape, image_shape)
+            self._check(lib.e2sec_process_batch_labels8(self._h, ptr(xyz), ptr(labels), F, lw, lh, w, h, ptr(fid), 0,
+                                                        ptr(rec)), "e2sec_process_batch_labels8")
+            return rec
+        labels = np.ascontiguousarray(labels, np.int32).reshape(F, -1)
+        lw, lh, w, h = self._shapes(labels.shape[1], label_shape, image_shape)
         self._check(lib.e2sec_process_batch(self._h, ptr(xyz), ptr(labels), F, lw, lh, w, h, ptr(fid), 0, ptr(rec)),
                     "e2sec_process_batch")
         return rec
@@ -70,15 +77,14 @@ class Engine:
         return records
 
     def process_batch_device_async(self, xyz_ptr, labels_ptr, n_frames, frame_ids, label_size, records=None,
-                                   label_shape=None, image_shape=None, on_device=True):
+                                   label_shape=None, image_shape=None, on_device=True, labels8=False):
         """Queues a batch without waiting (e2sec_process_batch_async): `records` must be pinned host memory that stays
         alive, inputs must stay untouched until sync(); device-side errors surface at the next sync()."""
         fid = np.ascontiguousarray(frame_ids, np.int32)
         lw, lh, w, h = self._shapes(label_size, label_shape, image_shape)
-        self._check(lib.e2sec_process_batch_async(self._h, C.c_void_p(xyz_ptr), C.c_void_p(labels_ptr), int(n_frames), lw,
-                                                  lh, w, h, ptr(fid), 1 if on_device else 0,
-                                                  ptr(records) if records is not None else None),
-                    "e2sec_process_batch_async")
+        fn = lib.e2sec_process_batch_labels8_async if labels8 else lib.e2sec_process_batch_async
+        self._check(fn(self._h, C.c_void_p(xyz_ptr), C.c_void_p(labels_ptr), int(n_frames), lw, lh, w, h, ptr(fid),
+                       1 if on_device else 0, ptr(records) if records is not None else None), "e2sec_process_batch_async")
         return records
 
     def _shapes(self, label_size, label_shape, image_shape):

@@ -524,3 +524,43 @@ def test_seg_fused_equals_two_pass(shape, monkeypatch):
         finally:
             eng.close()
     np.testing.assert_array_equal(recs[0], recs[1])
+
+
+# ---- uint8 label images (e2sec_process_batch_labels8) ----------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(320, 240, False), (640, 480, True), (250, 1, False), (253, 1, False)])
+def test_labels8_equals_int32(shape):
+    """Label images sent as uint8 (13 B/point over PCIe) give bit-identical records to the int32 entry point, for full-size
+    images, for images that are upscaled on the device, and for sizes the 4-wide widening kernel has to finish one by one."""
+    from manipulationlibrary_b200 import _native as nat
+    from manipulationlibrary_b200.engine import Engine
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    w, h, upscale = shape
+    eng = Engine(0)
+    try:
+        if h >= 48:
+            s = SyntheticStream(width=w, height=h, n_objects=4, config=7, cycle=24)
+            p, keep = nat.make_params(**s.params())
+            ids = np.arange(8, 13)
+            xyz, lab = s.fetch(ids)
+            eng.configure(p, len(ids), s.N, keep)
+            kw = {}
+            if upscale:
+                lab = np.ascontiguousarray(lab.reshape(len(ids), h, w)[:, ::2, ::2])
+                kw = dict(label_shape=(h // 2, w // 2), image_shape=(h, w))
+        else:
+            fx = load_golden("pushing06_fixture")
+            p, keep = nat.make_params(fx["total_unique_labels"], 11, 2, None, 0.07, fx["translation"], fx["roll"], fx["ground"])
+            N = w * h
+            rng = np.random.default_rng(N)
+            xyz = (rng.normal(size=(3, N, 3)) * 0.05 + [0, 0, 1.0]).astype(np.float32)
+            xyz[rng.random((3, N)) < 0.1] = np.nan
+            lab = rng.choice([0, 2, 4, 5, 6, 11, 200, 255], size=(3, N)).astype(np.int32)
+            ids, kw = [0, 3, 6], {}
+            eng.configure(p, 3, N, keep)
+        eng.reset_sequence()
+        a = eng.process_batch(xyz, lab.astype(np.int32), ids, **kw)
+        eng.reset_sequence()
+        b = eng.process_batch(xyz, lab.astype(np.uint8), ids, **kw)
+    finally:
+        eng.close()
+    np.testing.assert_array_equal(a, b)
