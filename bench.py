@@ -29,6 +29,10 @@ if ROOT not in sys.path:
 METRIC = "e2sec_frames_per_sec"
 UNIT = "frames/s"
 WIDTH, HEIGHT, N_OBJECTS, STREAM_CONFIG = 640, 480, 10, 2
+# dram__bytes_read.sum + dram__bytes_write.sum per frame of the dominant kernel of each stage, from the ncu --set full capture
+# of this workload (profiles/r1_v8_ncu_full_summary.csv: 100-frame launches): seg_fused_kernel, cell_filter_kernel,
+# contact_work_kernel
+NCU_TRAFFIC_PER_FRAME = {"segment": 8.292e6, "radius": 1.857e6, "pairs": 0.793e6}
 BYTES_PER_POINT = 16                     # 12 B xyz float32 + 4 B int32 label, read once
 
 
@@ -210,7 +214,6 @@ def run_b200(args):
     import torch.distributed as dist
     from manipulationlibrary_b200 import _native as nat
     from manipulationlibrary_b200.engine import Engine, Resolver
-    from manipulationlibrary_b200.sharding import gather_records
     from manipulationlibrary_b200.synthetic import SyntheticStream
 
     rank = int(os.environ.get("RANK", "0"))
@@ -269,38 +272,65 @@ def run_b200(args):
             eng.process_batch_device_async(hx_t[s].data_ptr(), (hl8_t if lab8 else hl_t)[s].data_ptr(), B, ids, N, records=out,
                                            on_device=False, labels8=lab8)
 
-    def resolve_shards(full, per):
-        """phase 2 on rank 0: every shard is its own sequence in this benchmark, so the shards resolve side by side
-        (the feed is one C call per shard and releases the GIL)"""
-        def one(r):
-            res = Resolver(p, keep)
-            res.feed(full[r * per: (r + 1) * per])
-            n = res.n_columns
-            res.close()
-            return n
-        if world == 1:
-            return one(0)
-        from concurrent.futures import ThreadPoolExecutor
-        with ThreadPoolExecutor(max_workers=min(world, os.cpu_count() or 1)) as ex:
-            return sum(ex.map(one, range(world)))
-
-    def finish(n_steps, first_step, res=None, fed=0):
-        """one gather of the records (N > 1) + the sequential phase 2 on rank 0.  With one GPU the resolver has been
-        following the batches while the GPU worked (`res` has seen `fed` batches); the rest is fed here."""
-        eng.sync()                                     # all queued batches done, records on the host, errors raised
-        local_rec = rec_np[first_step * B: (first_step + n_steps) * B]
-        if res is not None:
-            res.feed(local_rec[fed * B:])
-            cols = res.n_columns
-            res.close()
-            return cols
-        full = gather_records(local_rec, n_steps * B * world, world, device=dev)
-        return resolve_shards(full, n_steps * B) if rank == 0 else 0
+    def finish(n_steps, first_step, res, fed):
+        """one GPU: the resolver has been following the batches while the GPU worked (`res` has seen `fed` batches); the
+        rest is fed here, after every queued batch is done and device-side errors have been raised"""
+        eng.sync()
+        res.feed(rec_np[(first_step + fed) * B: (first_step + n_steps) * B])
+        cols = res.n_columns
+        res.close()
+        return cols
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    # N > 1: the records of batch i are all-gathered (NCCL, its own stream) while the GPUs work on batch i+1, and rank 0
+    # resolves the gathered batch one step behind -- every shard is its own sequence here, so the shards' resolvers run
+    # side by side (one C call each, the GIL is released).  No collective on the data path itself.
+    if world > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        gst = torch.cuda.Stream(device=dev)
+        gbuf = [torch.empty((B, rec_w), dtype=torch.float64, device=dev) for _ in range(2)]
+        gfull = [torch.empty((world * B, rec_w), dtype=torch.float64, device=dev) for _ in range(2)]
+        ghost = torch.empty((max(K, W, 1), world * B, rec_w), dtype=torch.float64).pin_memory()
+        ghost_np = ghost.numpy()
+        tpool = ThreadPoolExecutor(max_workers=min(world, os.cpu_count() or 1)) if rank == 0 else None
+
+    def pipelined_gather(on_device, first_step, n_steps):
+        resolvers = [Resolver(p, keep) for _ in range(world)] if rank == 0 else None
+        gdone = []
+
+        def feed(j):
+            if rank == 0:
+                list(tpool.map(lambda r: resolvers[r].feed(ghost_np[j, r * B: (r + 1) * B]), range(world)))
+
+        for i in range(n_steps):
+            step(first_step + i, on_device)
+            with torch.cuda.stream(est):
+                e = torch.cuda.Event()
+                e.record()
+            with torch.cuda.stream(gst):
+                gst.wait_event(e)                      # the batch's records are in the pinned host buffer
+                gbuf[i & 1].copy_(rec_host[(first_step + i) * B: (first_step + i + 1) * B], non_blocking=True)
+                dist.all_gather_into_tensor(gfull[i & 1], gbuf[i & 1])
+                ghost[i].copy_(gfull[i & 1], non_blocking=True)
+                ge = torch.cuda.Event()
+                ge.record()
+            gdone.append(ge)
+            if i >= 1:
+                gdone[i - 1].synchronize()
+                feed(i - 1)
+        eng.sync()
+        gdone[-1].synchronize()
+        feed(n_steps - 1)
+        cols = 0
+        if rank == 0:
+            cols = sum(r.n_columns for r in resolvers)
+            for r in resolvers:
+                r.close()
+        return cols
 
     def timed(on_device, first_step, n_steps):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -310,12 +340,12 @@ def run_b200(args):
         t0 = time.perf_counter()
         with torch.cuda.stream(est):
             ev0.record()
-        # one GPU: phase 2 (host, sequential) runs one batch behind the GPU instead of after it
-        res = Resolver(p, keep) if world == 1 else None
-        done, fed = [], 0
-        for i in range(n_steps):
-            step(first_step + i, on_device)
-            if res is not None:
+        if world == 1:
+            # one GPU: phase 2 (host, sequential) runs one batch behind the GPU instead of after it
+            res = Resolver(p, keep)
+            done, fed = [], 0
+            for i in range(n_steps):
+                step(first_step + i, on_device)
                 with torch.cuda.stream(est):
                     e = torch.cuda.Event()
                     e.record()
@@ -324,7 +354,9 @@ def run_b200(args):
                     done[i - 1].synchronize()          # batch i-1 is on the host; batch i keeps the GPU busy meanwhile
                     res.feed(rec_np[(first_step + i - 1) * B: (first_step + i) * B])
                     fed = i
-        cols = finish(n_steps, first_step, res, fed)
+            cols = finish(n_steps, first_step, res, fed)
+        else:
+            cols = pipelined_gather(on_device, first_step, n_steps)
         with torch.cuda.stream(est):
             ev1.record()
         barrier()
@@ -337,8 +369,11 @@ def run_b200(args):
         return float(t[0]), float(t[1]), eng.launch_count - l0, cols, (t0, t1)
 
     eng.reset_sequence()
-    for i in range(W):
-        step(i, True)
+    if world > 1:
+        pipelined_gather(True, 0, W)        # also brings up the NCCL communicator outside the timed region
+    else:
+        for i in range(W):
+            step(i, True)
     eng.sync()
     uuid = str(torch.cuda.get_device_properties(dev).uuid)
     sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if rank == 0 else None
@@ -386,12 +421,20 @@ def run_b200(args):
                        "pool_frames_per_gpu": pool, "filter_mode": args.filter_mode, "radius_mode": args.radius_mode,
                        "filtered_entities": n_filtered, "exact_path_entities": n_exact,
                        "l2": "inputs larger than L2 (one step reads %d MB)" % (alg // 2 ** 20),
-                       "parallelism": "frame-sharded x%d, one record all-gather" % world},
+                       "parallelism": ("frame-sharded x%d, records all-gathered per batch behind the GPU work" % world) if world > 1
+                       else "one GPU, host resolver one batch behind"},
             "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": wall_ms / K, "esec_columns": cols,
             "stages_ms_last_step": stages,
             "roofline": {"bound": "hbm", "kernel": dom + " stage of one step", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
-                         "peak_source": which, "whole_step_gbs_per_gpu": step_gbs, "whole_step_frac": step_gbs / peak},
+                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
+                         "traffic": (NCU_TRAFFIC_PER_FRAME[dom] * B) if (dom in NCU_TRAFFIC_PER_FRAME and N == 307200) else None,
+                         "peak_source": which, "whole_step_gbs_per_gpu": step_gbs, "whole_step_frac": step_gbs / peak,
+                         # the streaming kernel (label filter + compaction) is the HBM-bound one; the other two stages are
+                         # bound by O(cells^2) / O(n_a n_b) arithmetic on L2-resident data
+                         "stages": {k: {"ms": stages[k], "algorithmic_gbs": alg / (stages[k] * 1e-3) / 1e9,
+                                        "frac": alg / (stages[k] * 1e-3) / 1e9 / peak,
+                                        "dram_gbs": (NCU_TRAFFIC_PER_FRAME[k] * B / (stages[k] * 1e-3) / 1e9) if N == 307200 else None}
+                                    for k in ("segment", "radius", "pairs") if stages.get(k, 0) > 0}},
         }
         if e2e:
             out["e2e"] = e2e
