@@ -300,7 +300,7 @@ def run_b200(args):
 
     def pipelined_gather(on_device, first_step, n_steps):
         resolvers = [Resolver(p, keep) for _ in range(world)] if rank == 0 else None
-        gdone = []
+        gdone, LAG = [], 2
 
         def feed(j):
             if rank == 0:
@@ -315,16 +315,18 @@ def run_b200(args):
                 gst.wait_event(e)                      # the batch's records are in the pinned host buffer
                 gbuf[i & 1].copy_(rec_host[(first_step + i) * B: (first_step + i + 1) * B], non_blocking=True)
                 dist.all_gather_into_tensor(gfull[i & 1], gbuf[i & 1])
-                ghost[i].copy_(gfull[i & 1], non_blocking=True)
+                if rank == 0:
+                    ghost[i].copy_(gfull[i & 1], non_blocking=True)
                 ge = torch.cuda.Event()
                 ge.record()
             gdone.append(ge)
-            if i >= 1:
-                gdone[i - 1].synchronize()
-                feed(i - 1)
+            if i >= LAG:                               # two batches of slack: a rank that runs late does not stall the others
+                gdone[i - LAG].synchronize()
+                feed(i - LAG)
         eng.sync()
-        gdone[-1].synchronize()
-        feed(n_steps - 1)
+        for j in range(max(n_steps - LAG, 0), n_steps):
+            gdone[j].synchronize()
+            feed(j)
         cols = 0
         if rank == 0:
             cols = sum(r.n_columns for r in resolvers)
