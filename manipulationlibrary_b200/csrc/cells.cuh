@@ -33,7 +33,9 @@
 #define E2_CELL_WARPS (E2_CELL_THREADS / 32)
 #define E2_CELL_MAX 1024          // occupied cells per entity
 #define E2_CELL_HASH 4096         // hash slots (power of two)
+#ifndef E2_CELL_G
 #define E2_CELL_G 24              // cells along the largest robust extent; ids use 5 bits per axis
+#endif
 #define E2_CELL_BINS 1024         // histogram bins over d^2
 #define E2_CELL_EMPTY 0xffffffffu
 #define E2_CELL_JOIN (E2_CELL_MAX - 1)   // virtual cell of candidate points that were settled as members one by one
@@ -152,33 +154,35 @@ __device__ __forceinline__ double cell_point_dmax2(const CellSmem &s, const doub
     return (f[0] * f[0] + f[1] * f[1]) + f[2] * f[2];
 }
 
-// block-wide reductions over E2_CELL_THREADS threads; `slot` picks a row of s.red
+// block-wide reductions over E2_CELL_THREADS threads; `slot` picks a row of s.red.  Every thread reads the
+// E2_CELL_WARPS partials with one shuffle tree instead of a serial loop.
 __device__ __forceinline__ double cell_block_sum(CellSmem &s, int slot, double v)
 {
     for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if ((threadIdx.x & 31) == 0) s.red[slot][threadIdx.x >> 5] = v;
     __syncthreads();
-    double t = 0.0;
-    for (int w = 0; w < E2_CELL_WARPS; ++w) t += s.red[slot][w];
-    return t;
+    const int l = threadIdx.x & 31;
+    double t = (l < E2_CELL_WARPS) ? s.red[slot][l] : 0.0;
+    // fixed summation order (warp 0, 1, 2, ...) regardless of the lane: the mean must not depend on the thread that asks
+    double acc = 0.0;
+    for (int w = 0; w < E2_CELL_WARPS; ++w) acc += __shfl_sync(0xffffffffu, t, w);
+    return acc;
 }
 __device__ __forceinline__ double cell_block_min(CellSmem &s, int slot, double v)
 {
     v = warp_min_d(v);
     if ((threadIdx.x & 31) == 0) s.red[slot][threadIdx.x >> 5] = v;
     __syncthreads();
-    double t = s.red[slot][0];
-    for (int w = 1; w < E2_CELL_WARPS; ++w) t = fmin(t, s.red[slot][w]);
-    return t;
+    const int l = threadIdx.x & 31;
+    return warp_min_d(s.red[slot][l < E2_CELL_WARPS ? l : 0]);
 }
 __device__ __forceinline__ double cell_block_max(CellSmem &s, int slot, double v)
 {
     v = warp_max_d(v);
     if ((threadIdx.x & 31) == 0) s.red[slot][threadIdx.x >> 5] = v;
     __syncthreads();
-    double t = s.red[slot][0];
-    for (int w = 1; w < E2_CELL_WARPS; ++w) t = fmax(t, s.red[slot][w]);
-    return t;
+    const int l = threadIdx.x & 31;
+    return warp_max_d(s.red[slot][l < E2_CELL_WARPS ? l : 0]);
 }
 
 // One warp finds the bin holding 0-based rank k of a weighted histogram (cumulative weight > k). Returns
@@ -256,14 +260,18 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
         if (tid < 3) s.m_ccnt[tid] = 0;
         __syncthreads();
         // ---- pass H: histograms (one shared atomic per distinct bin of a warp) ----------------------------------
-        for (int base = 0; base < n; base += E2_CELL_THREADS) {
-            const int i = base + tid;
+        // (values spread over 1024 bins: plain shared atomics beat a match_any aggregation; the three loads of a point are
+        // issued together, two points per thread in flight)
+        for (int base = 0; base < n; base += 2 * E2_CELL_THREADS) {
+            const int i0 = base + tid, i1 = i0 + E2_CELL_THREADS;
+            double v0[3], v1[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { v0[a] = (i0 < n) ? A[a][i0] : 0.0; v1[a] = (i1 < n) ? A[a][i1] : 0.0; }
+#pragma unroll
             for (int a = 0; a < 3; ++a) {
                 if (mode[a] != E2_M_HIST) continue;
-                int bin = -1;
-                if (i < n) { const double v = A[a][i]; if (v >= lo[a] && v <= hi[a]) bin = median_bin(v, lo[a], sc[a]); }
-                const unsigned peers = __match_any_sync(0xffffffffu, bin);
-                if (bin >= 0 && lane == __ffs(peers) - 1) atomicAdd(&s.mhist[a][bin], (unsigned)__popc(peers));
+                if (i0 < n && v0[a] >= lo[a] && v0[a] <= hi[a]) atomicAdd(&s.mhist[a][median_bin(v0[a], lo[a], sc[a])], 1u);
+                if (i1 < n && v1[a] >= lo[a] && v1[a] <= hi[a]) atomicAdd(&s.mhist[a][median_bin(v1[a], lo[a], sc[a])], 1u);
             }
         }
         __syncthreads();
@@ -285,9 +293,13 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
         int m2[3], b1[3], b2[3];
         for (int a = 0; a < 3; ++a) { m2[a] = (mode[a] == E2_M_HIST) ? s.m_mode[a] : E2_M_DONE; b1[a] = s.m_b1[a]; b2[a] = s.m_b2[a]; }
         for (int i = tid; i < n; i += E2_CELL_THREADS) {
+            double vv[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) vv[a] = A[a][i];
+#pragma unroll
             for (int a = 0; a < 3; ++a) {
                 if (m2[a] == E2_M_DONE) continue;
-                const double v = A[a][i];
+                const double v = vv[a];
                 if (!(v >= lo[a] && v <= hi[a])) continue;
                 const int bin = median_bin(v, lo[a], sc[a]);
                 if (m2[a] == E2_M_COLLECT) { if (bin == b1[a]) s.mcand[a][atomicAdd(&s.m_ccnt[a], 1u)] = v; }
