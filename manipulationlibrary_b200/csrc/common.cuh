@@ -14,6 +14,7 @@
 #define E2_SEG_WARPS 8       // warps per CTA there
 #define E2_TILE 256          // points per tile in the pair-distance kernels
 #define E2_NBINS 256         // bins per refinement pass of the radius selection
+#define E2_CT_SUB 256        // ground points per pruning box (contact.cuh)
 #define E2_CAND_CAP 4096     // candidate keys kept for the final exact selection
 
 typedef unsigned long long u64;
@@ -85,7 +86,8 @@ struct Dev {
     // stats + pairs
     double *aabb;                     // F x K x 6
     double *mean;                     // F x K x 3
-    const double *gx, *gy, *gz;       // ground cloud
+    const double *gx, *gy, *gz;       // ground cloud (Morton order)
+    const double *gsub;               // ceil(n_ground / E2_CT_SUB) x 6   tight box of every run of E2_CT_SUB ground points
     double gaabb[6];
     u64 *pair_key;                    // F x (K+1) x (K+1)   min d^2 key per in-frame pair
     u64 *cross_key;                   // F x K x K           min d^2 key, entity a of the previous kept frame vs b of this one

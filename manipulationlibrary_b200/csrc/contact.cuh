@@ -25,6 +25,8 @@
 #define E2_CT_THREADS 256
 #define E2_CT_CHUNK 1024          // A points per work item (4 per thread)
 #define E2_CT_TILE 1024           // B entries staged per tile
+#define E2_CT_RUNS 1024           // ground runs listed per item; a larger ground cloud is scanned tile by tile
+static_assert(E2_CT_SUB == E2_CT_THREADS, "a thread slice of a B tile must be exactly one ground pruning run");
 
 struct ContactPlan {
     unsigned *cnt;        // F * slots      items of the slot (0 = decided by the plan kernel)
@@ -129,6 +131,8 @@ struct ContactSmem {
     unsigned wcnt[E2_CT_THREADS / 32];
     unsigned item, skip;
     double box[6];
+    unsigned n_run;                                            // ground runs within thresh of the item's box ...
+    unsigned short run[E2_CT_RUNS];                            // ... and their indices (contact_work_kernel)
 };
 
 // float32 acceptance bound for a float64 minimum `best` <= lim2: every pair whose float64 d^2 is < best has a float32 d^2
@@ -156,6 +160,31 @@ __device__ __forceinline__ unsigned contact_push(ContactSmem &s, bool take, doub
     }
     __syncthreads();
     return count + tot;
+}
+
+// The O(n_a * m_b) sweep of one staged B tile: NK compacted A points per thread in float32, entries jstart, jstart + jstep,
+// ... of the tile; a pair is re-evaluated in float64 only inside the guard band of the thread's current minimum.
+template <int NK>
+__device__ __forceinline__ void contact_sweep(const ContactSmem &s, unsigned mB, unsigned jstart, unsigned jstep, const float *rx,
+                                              const float *ry, const float *rz, const double *ax, const double *ay,
+                                              const double *az, double &best, float &guard, double c0)
+{
+    for (unsigned j = jstart; j < mB; j += jstep) {
+        const float bx = s.fx[j], by = s.fy[j], bz = s.fz[j];
+        float d32[NK], lo = 3.0e38f;
+#pragma unroll
+        for (int k = 0; k < NK; ++k) {
+            const float ux = rx[k] - bx, uy = ry[k] - by, uz = rz[k] - bz;
+            d32[k] = fmaf(uz, uz, fmaf(uy, uy, ux * ux));
+            lo = fminf(lo, d32[k]);
+        }
+        if (lo <= guard) {
+#pragma unroll
+            for (int k = 0; k < NK; ++k)
+                if (d32[k] <= guard) best = fmin(best, dist2(ax[k], ay[k], az[k], s.dx[j], s.dy[j], s.dz[j]));
+            guard = contact_guard(best, c0);
+        }
+    }
 }
 
 // Four candidates per thread at once: all loads of a 1024-point tile are in flight together and the tile costs one
@@ -216,10 +245,12 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
         const unsigned *fla = d.flist + pa;
         const double *BX, *BY, *BZ;
         const unsigned *flb = nullptr;
+        const double *gsub = nullptr;
         int nb;
         double bb[6];
         if (cs.b == K) {
             BX = d.gx; BY = d.gy; BZ = d.gz; nb = d.n_ground;
+            gsub = d.gsub;
             for (int k = 0; k < 6; ++k) bb[k] = d.gaabb[k];
         } else {
             const int offb = d.ent_off[f * K + cs.b];
@@ -272,12 +303,18 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
         const double hx = cb[3] - cb[0], hy = cb[4] - cb[1], hz = cb[5] - cb[2];
         const double M = 0.5 * sqrt(hx * hx + hy * hy + hz * hz) + sqrt(lim2);       // |relative coordinate| bound
         const double e = M * 2.4e-7;
-        // this thread's A points: float64 for the recheck, float32 relative for the sweep
+        // this thread's A points: float64 for the recheck, float32 relative for the sweep.  Most items keep few A points
+        // (only the part of a chunk that lies within thresh of B's box): with n_a <= 256 every thread holds at most one
+        // point, P = the power of two >= n_a (>= 32) threads share the points and the 256 / P thread groups split the B tile.
+        const int nk = (int)((nA + E2_CT_THREADS - 1) / E2_CT_THREADS);
+        unsigned P = E2_CT_THREADS;
+        if (nk == 1) { P = 32; while (P < nA) P <<= 1; }
+        const unsigned jstart = (nk == 1) ? (unsigned)tid / P : 0u, jstep = (nk == 1) ? E2_CT_THREADS / P : 1u;
         double ax[4], ay[4], az[4];
         float rx[4], ry[4], rz[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const unsigned j = (unsigned)(tid + k * E2_CT_THREADS);
+            const unsigned j = (nk == 1) ? ((unsigned)tid & (P - 1)) + (k ? nA : 0u) : (unsigned)(tid + k * E2_CT_THREADS);
             if (j < nA) {
                 ax[k] = s.dx[j]; ay[k] = s.dy[j]; az[k] = s.dz[j];
                 rx[k] = (float)(ax[k] - ox); ry[k] = (float)(ay[k] - oy); rz[k] = (float)(az[k] - oz);
@@ -290,39 +327,54 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
         double best = lim2;                                      // block-uniform at every tile boundary
         float guard = contact_guard(best, c0);
         // ---- B tiles -----------------------------------------------------------------------------------------------
-        for (int base = 0; base < nb; base += E2_CT_TILE) {
+        // Ground (Morton order, one tight box per run of E2_CT_SUB points): warp 0 lists the runs that lie within thresh
+        // of the item's box once; the tiles below are made of listed runs only, the others are never loaded.
+        const int n_sub = (nb + E2_CT_SUB - 1) / E2_CT_SUB;
+        const bool listed = gsub && n_sub <= E2_CT_RUNS;
+        if (listed) {
+            __syncthreads();                                     // s.box readers are done, s.n_run of the last item is dead
+            if (warp == 0) {
+                unsigned n = 0;
+                for (int b0 = 0; b0 < n_sub; b0 += 32) {
+                    const int sub = b0 + lane;
+                    const bool ok = sub < n_sub && box_box_d2(gsub + (size_t)6 * sub, cb) <= lim2;
+                    const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                    if (ok) s.run[n + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)sub;
+                    n += __popc(bal);
+                }
+                if (lane == 0) s.n_run = n;
+            }
+            __syncthreads();
+        }
+        const int n_tiles = listed ? (int)((s.n_run + 3u) / 4u) : (nb + E2_CT_TILE - 1) / E2_CT_TILE;
+        for (int it = 0; it < n_tiles; ++it) {
             __syncthreads();                                     // the previous tile (or the A staging) is consumed
             unsigned mB = 0;
             {
+                int jb[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (listed) jb[k] = (4u * it + k < s.n_run) ? (int)s.run[4 * it + k] * E2_CT_SUB + tid : nb;
+                    else jb[k] = it * E2_CT_TILE + k * E2_CT_THREADS + tid;
+                }
                 bool take[4];
                 double x[4], y[4], z[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const int j = base + k * E2_CT_THREADS + tid;
+                    const int j = jb[k];
                     x[k] = y[k] = z[k] = 0.0;
                     if (j < nb) { const unsigned q = flb ? flb[j] : (unsigned)j; x[k] = BX[q]; y[k] = BY[q]; z[k] = BZ[q]; }
                 }
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int j = base + k * E2_CT_THREADS + tid;
-                    take[k] = (j < nb) && point_box_d2(x[k], y[k], z[k], cb) <= best;   // nothing farther than the current minimum can improve it
-                }
+                for (int k = 0; k < 4; ++k)
+                    take[k] = (jb[k] < nb) && point_box_d2(x[k], y[k], z[k], cb) <= best;   // nothing farther than the current minimum can improve it
                 mB = contact_push4(s, take, x, y, z, true, ox, oy, oz);
             }
-            for (unsigned j = 0; j < mB; ++j) {
-                const float bx = s.fx[j], by = s.fy[j], bz = s.fz[j];
-                float d32[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float ux = rx[k] - bx, uy = ry[k] - by, uz = rz[k] - bz;
-                    d32[k] = fmaf(uz, uz, fmaf(uy, uy, ux * ux));
-                }
-                if (fminf(fminf(d32[0], d32[1]), fminf(d32[2], d32[3])) <= guard) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (d32[k] <= guard) best = fmin(best, dist2(ax[k], ay[k], az[k], s.dx[j], s.dy[j], s.dz[j]));
-                    guard = contact_guard(best, c0);
-                }
+            switch (nk) {                                        // block-uniform
+            case 1: contact_sweep<1>(s, mB, jstart, jstep, rx, ry, rz, ax, ay, az, best, guard, c0); break;
+            case 2: contact_sweep<2>(s, mB, 0u, 1u, rx, ry, rz, ax, ay, az, best, guard, c0); break;
+            case 3: contact_sweep<3>(s, mB, 0u, 1u, rx, ry, rz, ax, ay, az, best, guard, c0); break;
+            default: contact_sweep<4>(s, mB, 0u, 1u, rx, ry, rz, ax, ay, az, best, guard, c0); break;
             }
             // share the minimum: every thread continues with the block's best, which tightens guard and the B filter
             const double wb = warp_min_d(best);

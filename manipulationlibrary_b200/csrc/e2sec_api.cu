@@ -4,6 +4,8 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <algorithm>
+#include <cmath>
 #include <string>
 #include <vector>
 
@@ -41,7 +43,7 @@ struct e2sec_ctx {
     size_t cap_total = 0;          // stored-point capacity over the whole batch (maxF * N)
     Dev d;
     std::vector<DevBuf *> bufs;
-    DevBuf lab8_stage;
+    DevBuf lab8_stage, gsub;
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
@@ -125,7 +127,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
-    ctx->bufs = {&ctx->lab8_stage, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
+    ctx->bufs = {&ctx->lab8_stage, &ctx->gsub, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
                  &ctx->radius, &ctx->rs, &ctx->hist, &ctx->cand, &ctx->cand_n, &ctx->seed_pos, &ctx->member,
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
@@ -312,17 +314,58 @@ extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t ma
         lut[raw] = idx;
     }
     CU(cudaMemcpyAsync(ctx->lut.p, lut.data(), lut.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-    // ground cloud as SoA + its AABB
+    // ground cloud as SoA + its AABB.  The cloud only ever enters minimum distances, so its order is free: the points
+    // are sorted along a Morton curve and every run of E2_CT_SUB points gets a tight box -- contact_work_kernel skips the
+    // runs that lie farther from a work item than its current minimum without loading them.
     const int G = p->n_ground;
     std::vector<double> soa((size_t)3 * (G ? G : 1));
     double box[6] = {0, 0, 0, 0, 0, 0};
     for (int i = 0; i < G; ++i)
         for (int a = 0; a < 3; ++a) {
             double v = p->ground_xyz[3 * (size_t)i + a];
-            soa[(size_t)a * G + i] = v;
             if (i == 0 || v < box[a]) box[a] = v;
             if (i == 0 || v > box[3 + a]) box[3 + a] = v;
         }
+    std::vector<int> order(G);
+    {
+        std::vector<unsigned long long> code(G);
+        auto spread = [](unsigned long long v) {            // 21 bits -> every third bit
+            v &= 0x1fffffull;
+            v = (v | v << 32) & 0x1f00000000ffffull;
+            v = (v | v << 16) & 0x1f0000ff0000ffull;
+            v = (v | v << 8) & 0x100f00f00f00f00full;
+            v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+            v = (v | v << 2) & 0x1249249249249249ull;
+            return v;
+        };
+        double ext = 0.0;
+        for (int a = 0; a < 3; ++a) ext = std::max(ext, box[3 + a] - box[a]);
+        const double q = (ext > 0.0 && std::isfinite(ext)) ? 2097151.0 / ext : 0.0;
+        for (int i = 0; i < G; ++i) {
+            unsigned long long c = 0;
+            for (int a = 0; a < 3; ++a) {
+                double t = (p->ground_xyz[3 * (size_t)i + a] - box[a]) * q;
+                if (!(t >= 0.0)) t = 0.0;
+                if (t > 2097151.0) t = 2097151.0;
+                c |= spread((unsigned long long)t) << a;
+            }
+            code[i] = c;
+            order[i] = i;
+        }
+        std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return code[x] < code[y]; });
+    }
+    const int n_sub = (G + E2_CT_SUB - 1) / E2_CT_SUB;
+    std::vector<double> sub((size_t)6 * (n_sub ? n_sub : 1), 0.0);
+    for (int i = 0; i < G; ++i)
+        for (int a = 0; a < 3; ++a) {
+            const double v = p->ground_xyz[3 * (size_t)order[i] + a];
+            soa[(size_t)a * G + i] = v;
+            double *b = &sub[(size_t)6 * (i / E2_CT_SUB)];
+            if (i % E2_CT_SUB == 0 || v < b[a]) b[a] = v;
+            if (i % E2_CT_SUB == 0 || v > b[3 + a]) b[3 + a] = v;
+        }
+    if (ensure(ctx, ctx->gsub, sizeof(double) * 6 * (n_sub ? n_sub : 1))) return E2SEC_ERR_CUDA;
+    CU(cudaMemcpyAsync(ctx->gsub.p, sub.data(), sizeof(double) * 6 * (n_sub ? n_sub : 1), cudaMemcpyHostToDevice, ctx->stream));
     if (ensure(ctx, ctx->gx, sizeof(double) * (G ? G : 1)) || ensure(ctx, ctx->gy, sizeof(double) * (G ? G : 1)) ||
         ensure(ctx, ctx->gz, sizeof(double) * (G ? G : 1)))
         return E2SEC_ERR_CUDA;
@@ -349,6 +392,7 @@ extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t ma
     d.affine = 1;
     for (int i = 12; i < 16; ++i)
         if (d.T[i] != (i == 15 ? 1.0 : 0.0) || d.R[i] != (i == 15 ? 1.0 : 0.0)) d.affine = 0;
+    d.gsub = (const double *)ctx->gsub.p;
     d.gx = (const double *)ctx->gx.p;
     d.gy = (const double *)ctx->gy.p;
     d.gz = (const double *)ctx->gz.p;
