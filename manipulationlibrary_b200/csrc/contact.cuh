@@ -33,6 +33,8 @@ struct ContactPlan {
     unsigned *off;        // F * slots + 1  exclusive prefix
     unsigned *next;       // work counter
     int slots;            // pair slots per frame: K(K-1)/2 + K + K*K
+    unsigned *map;        // item -> index of its (frame, slot), filled by the scan kernel while the items fit map_cap
+    unsigned map_cap;
 };
 
 struct ContactSlot { int a, b, fa; bool cross; u64 *out; };
@@ -94,34 +96,37 @@ __global__ void contact_plan_kernel(Dev d, ContactPlan plan)
     plan.cnt[idx] = items;
 }
 
-// single CTA of 1024 threads: exclusive scan of plan.cnt -> plan.off
+// single CTA of 1024 threads: exclusive scan of plan.cnt -> plan.off (every thread owns a run of consecutive entries: one
+// block scan in all), then the item -> entry map the work kernel reads instead of searching plan.off
 __global__ void __launch_bounds__(1024) contact_scan_kernel(ContactPlan plan, int n)
 {
     pdl_enter();
     __shared__ unsigned warp_tot[32];
-    __shared__ unsigned carry;
-    if (threadIdx.x == 0) carry = 0;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (n + 1023) / 1024, first = tid * per, last = min(n, first + per);
+    unsigned mine = 0;
+    for (int i = first; i < last; ++i) mine += plan.cnt[i];
+    unsigned v = mine;
+    for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+    if (lane == 31) warp_tot[warp] = v;
     __syncthreads();
-    for (int base = 0; base < n; base += 1024) {
-        const int i = base + threadIdx.x;
-        const unsigned items = (i < n) ? plan.cnt[i] : 0u;
-        unsigned v = items;
-        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, v, o); if ((threadIdx.x & 31) >= o) v += t; }
-        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = v;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            unsigned w = warp_tot[threadIdx.x];
-            for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, w, o); if (threadIdx.x >= o) w += t; }
-            warp_tot[threadIdx.x] = w;
-        }
-        __syncthreads();
-        const unsigned excl = carry + v - items + ((threadIdx.x >> 5) ? warp_tot[(threadIdx.x >> 5) - 1] : 0u);
-        if (i < n) plan.off[i] = excl;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + items;
-        __syncthreads();
+    if (warp == 0) {
+        unsigned w = warp_tot[lane];
+        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += t; }
+        warp_tot[lane] = w;
     }
-    if (threadIdx.x == 0) plan.off[n] = carry;
+    __syncthreads();
+    const unsigned total = warp_tot[31];
+    unsigned off = v - mine + (warp ? warp_tot[warp - 1] : 0u);
+    const bool mapped = total <= plan.map_cap;
+    for (int i = first; i < last; ++i) {
+        const unsigned items = plan.cnt[i];
+        plan.off[i] = off;
+        if (mapped)
+            for (unsigned c = 0; c < items; ++c) plan.map[off + c] = (unsigned)i;
+        off += items;
+    }
+    if (tid == 0) plan.off[n] = total;
 }
 
 struct ContactSmem {
@@ -229,10 +234,12 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
         const unsigned item = s.item;
         if (item >= total) break;
         int lo = 0, hi = n_idx;                               // last idx with off[idx] <= item
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (plan.off[mid] <= item) lo = mid; else hi = mid;
-        }
+        if (total <= plan.map_cap) lo = (int)plan.map[item];
+        else
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (plan.off[mid] <= item) lo = mid; else hi = mid;
+            }
         const int f = lo / plan.slots;
         const ContactSlot cs = contact_decode(d, f, lo - f * plan.slots);
         const int chunk = (int)(item - plan.off[lo]);

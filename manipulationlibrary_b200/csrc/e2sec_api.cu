@@ -47,7 +47,7 @@ struct e2sec_ctx {
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
-        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next, seg_list;
+        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next, ct_map, seg_list;
     int map_cfg[4] = {0, 0, 0, 0};
     int64_t launches = 0;
     cudaEvent_t ev[8];
@@ -133,7 +133,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
                  &ctx->gz, &ctx->pair_key, &ctx->records, &ctx->error, &ctx->plan_off, &ctx->plan_total,
                  &ctx->below_acc, &ctx->min_above, &ctx->single_count, &ctx->cross_key, &ctx->frame_used, &ctx->prev_slot,
-                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->seg_list};
+                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->ct_map, &ctx->seg_list};
     *out = ctx;
     return E2SEC_OK;
 }
@@ -232,6 +232,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     rc |= ensure(ctx, ctx->ct_cnt, (size_t)F * slots * sizeof(unsigned));
     rc |= ensure(ctx, ctx->ct_off, ((size_t)F * slots + 1) * sizeof(unsigned));
     rc |= ensure(ctx, ctx->ct_next, sizeof(unsigned));
+    rc |= ensure(ctx, ctx->ct_map, std::max((size_t)F * slots * 4, (size_t)65536) * sizeof(unsigned));
     rc |= ensure(ctx, ctx->seg_list, (size_t)F * N * sizeof(uint4));
     if (rc) return E2SEC_ERR_CUDA;
     CU(cudaMemset(ctx->error.p, 0, sizeof(int)));
@@ -476,7 +477,8 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
     if (do_pairs) {
         launch_pdl(ctx, prev_kept_kernel, dim3(1), dim3(1024), 0, st, d);
         ContactPlan cp{(unsigned *)ctx->ct_cnt.p, (unsigned *)ctx->ct_off.p, (unsigned *)ctx->ct_next.p,
-                       d.K * (d.K - 1) / 2 + d.K + d.K * d.K};
+                       d.K * (d.K - 1) / 2 + d.K + d.K * d.K, (unsigned *)ctx->ct_map.p,
+                       (unsigned)(ctx->ct_map.bytes / sizeof(unsigned))};
         const int n_idx = d.F * cp.slots;
         launch_pdl(ctx, contact_plan_kernel, dim3((n_idx + 255) / 256), dim3(256), 0, st, d, cp);
         launch_pdl(ctx, contact_scan_kernel, dim3(1), dim3(1024), 0, st, cp, n_idx);
