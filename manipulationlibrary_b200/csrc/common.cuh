@@ -62,6 +62,7 @@ struct Dev {
     int *prev_slot;                   // F           frame slot of the previous kept frame (maxF = halo, -1 = none)
     int *prev_id;                     // F           its frame id (-1 = none)
     int *halo_info;                   // [0] valid, [1] frame id, [2] slot of the last kept frame of this batch (-1 none)
+    unsigned *seg_len;                // F x units   entries of every unit's scratch list (seg_stream.cuh)
     uint4 *seg_list;                  // F x N       scratch of seg_fused_kernel: compacted (x, y, z, raster index << 6 | entity)
     int affine;                       // translation and roll both end in the row (0, 0, 0, 1): the perspective divide is by exactly 1.0
     double *px, *py, *pz;             // F x cap     transformed points, grouped by entity, raster order inside

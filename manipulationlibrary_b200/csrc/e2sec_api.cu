@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "seg.cuh"
 #include "seg_fused.cuh"
+#include "seg_stream.cuh"
 #include "select.cuh"
 #include "radius.cuh"
 #include "filter.cuh"
@@ -47,13 +48,14 @@ struct e2sec_ctx {
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
-        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next, ct_map, seg_list;
+        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next, ct_map, seg_list, seg_len, seg_next;
     int map_cfg[4] = {0, 0, 0, 0};
     int64_t launches = 0;
     cudaEvent_t ev[8];
     bool ev_valid = false;
     int sm_count = 148;
     int sf_cluster = 8;
+    bool seg_cluster = false;      // E2SEC_SEG_MODE=cluster: the one-kernel cluster segmentation instead of the unit stream
     bool pdl = true;
     bool force_two_pass = false;   // E2SEC_SEG_TWO_PASS=1: always take the two-pass segmentation (tests compare both)
 };
@@ -122,7 +124,10 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
     cudaFuncSetAttribute(seg_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
     cudaFuncSetAttribute(seg_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
+    cudaFuncSetAttribute(seg_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegStreamSmem));
+    cudaFuncSetAttribute(seg_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegStreamSmem));
     { const char *e = getenv("E2SEC_SEG_TWO_PASS"); ctx->force_two_pass = e && e[0] == '1'; }
+    { const char *e = getenv("E2SEC_SEG_MODE"); ctx->seg_cluster = e && !strcmp(e, "cluster"); }
     { const char *e = getenv("E2SEC_PDL"); ctx->pdl = !(e && e[0] == '0'); }
     { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -133,7 +138,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
                  &ctx->gz, &ctx->pair_key, &ctx->records, &ctx->error, &ctx->plan_off, &ctx->plan_total,
                  &ctx->below_acc, &ctx->min_above, &ctx->single_count, &ctx->cross_key, &ctx->frame_used, &ctx->prev_slot,
-                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->ct_map, &ctx->seg_list};
+                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->ct_map, &ctx->seg_list, &ctx->seg_len, &ctx->seg_next};
     *out = ctx;
     return E2SEC_OK;
 }
@@ -234,8 +239,11 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     rc |= ensure(ctx, ctx->ct_next, sizeof(unsigned));
     rc |= ensure(ctx, ctx->ct_map, std::max((size_t)F * slots * 4, (size_t)65536) * sizeof(unsigned));
     rc |= ensure(ctx, ctx->seg_list, (size_t)F * N * sizeof(uint4));
+    rc |= ensure(ctx, ctx->seg_len, (size_t)F * ((N + E2_SS_UNIT - 1) / E2_SS_UNIT) * sizeof(unsigned));
+    rc |= ensure(ctx, ctx->seg_next, sizeof(unsigned));
     if (rc) return E2SEC_ERR_CUDA;
     CU(cudaMemset(ctx->error.p, 0, sizeof(int)));
+    CU(cudaMemset(ctx->seg_next.p, 0, sizeof(unsigned)));
     ctx->maxF = F;
     ctx->N = N;
     ctx->K = K;
@@ -279,6 +287,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     d.rad_hi = (double *)ctx->rad_hi.p;
     d.amb = (int *)ctx->amb.p;
     d.seg_list = (uint4 *)ctx->seg_list.p;
+    d.seg_len = (unsigned *)ctx->seg_len.p;
     return E2SEC_OK;
 }
 
@@ -581,7 +590,18 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labe
     // single-pass cluster kernel when the bulk copies can be issued (16-byte aligned frames), else the two-pass kernels
     const bool fused = !ctx->force_two_pass && (N % 4 == 0) && ((uintptr_t)d.xyz % 16 == 0) && ((uintptr_t)d.labels % 16 == 0) &&
                        (upscale || d.label_size % 4 == 0) && N <= (1 << 26);
-    if (fused) {
+    if (fused && !ctx->seg_cluster) {
+        // unit stream: persistent warps pull 2048-point units, then a per-frame scan and one warp per unit to emit
+        Dev du = d;
+        du.S = (N + E2_SS_UNIT - 1) / E2_SS_UNIT;
+        unsigned *next = (unsigned *)ctx->seg_next.p;
+        const long long units = (long long)n_frames * du.S;
+        const int ctas = (int)std::min<long long>((units + E2_SS_WARPS - 1) / E2_SS_WARPS, (long long)ctx->sm_count * 7);
+        if (upscale) launch_pdl(ctx, seg_stream_kernel<true>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);
+        else launch_pdl(ctx, seg_stream_kernel<false>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);
+        launch_pdl(ctx, seg_unit_scan_kernel, dim3(n_frames), dim3(E2SEC_MAX_ENTITIES), 0, st, du);
+        launch_pdl(ctx, seg_emit_kernel, dim3((du.S + E2_SS_WARPS - 1) / E2_SS_WARPS, n_frames), dim3(E2_SS_THREADS), 0, st, du, next);
+    } else if (fused) {
         const int tpf = (N + E2_SF_TILE - 1) / E2_SF_TILE;
         int C = ctx->sf_cluster;
         while (C > 1 && C > tpf) C >>= 1;

@@ -496,8 +496,9 @@ def test_seg_fused_equals_two_pass(shape, monkeypatch):
     from manipulationlibrary_b200.synthetic import SyntheticStream
     w, h, upscale = shape
     recs = []
-    for two_pass in ("0", "1"):
+    for two_pass, mode in (("0", "stream"), ("1", "stream"), ("0", "cluster")):     # unit stream, two-pass, cluster kernel
         monkeypatch.setenv("E2SEC_SEG_TWO_PASS", two_pass)
+        monkeypatch.setenv("E2SEC_SEG_MODE", mode)
         eng = Engine(0)
         try:
             if h >= 48:
@@ -524,6 +525,7 @@ def test_seg_fused_equals_two_pass(shape, monkeypatch):
         finally:
             eng.close()
     np.testing.assert_array_equal(recs[0], recs[1])
+    np.testing.assert_array_equal(recs[0], recs[2])
 
 
 # ---- uint8 label images (e2sec_process_batch_labels8) ----------------------------------------------------------------
