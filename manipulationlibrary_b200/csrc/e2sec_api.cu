@@ -599,7 +599,6 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labe
         const int ctas = (int)std::min<long long>((units + E2_SS_WARPS - 1) / E2_SS_WARPS, (long long)ctx->sm_count * 7);
         if (upscale) launch_pdl(ctx, seg_stream_kernel<true>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);
         else launch_pdl(ctx, seg_stream_kernel<false>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);
-        launch_pdl(ctx, seg_unit_scan_kernel, dim3(n_frames), dim3(E2SEC_MAX_ENTITIES), 0, st, du);
         launch_pdl(ctx, seg_emit_kernel, dim3((du.S + E2_SS_WARPS - 1) / E2_SS_WARPS, n_frames), dim3(E2_SS_THREADS), 0, st, du, next);
     } else if (fused) {
         const int tpf = (N + E2_SF_TILE - 1) / E2_SF_TILE;

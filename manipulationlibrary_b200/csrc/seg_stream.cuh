@@ -1,4 +1,4 @@
-// seg_stream.cuh -- label filter + segment compaction (manipulation_analyser.py:1433-1504) as three stream-ordered
+// seg_stream.cuh -- label filter + segment compaction (manipulation_analyser.py:1433-1504) as two stream-ordered
 // kernels that read the input exactly once and never make a warp wait for another one:
 //
 //   seg_stream_kernel   persistent warps pull UNITS (E2_SS_UNIT_TILES tiles of 128 points = 2048 consecutive points of one
@@ -9,9 +9,8 @@
 //                       / entity; stays in L2) and leaves the unit's per-entity counts in seg_cnt[frame][unit][entity].
 //                       Units are small and handed out dynamically, so object-heavy image rows do not stall anybody
 //                       (the cluster kernel of seg_fused.cuh spends 38 % of its stall samples at barriers).
-//   seg_unit_scan_kernel  one CTA per frame: exclusive prefix of the counts over the frame's units, entity totals and
-//                       offsets (:1456-1472; index 0 and the ground are counted, never stored, :1520).
-//   seg_emit_kernel     one warp per unit: re-reads the unit's list (13 % of the input on the 640x480 stream), ranks the
+//   seg_emit_kernel     one warp per unit (the CTA first sums the frame's small count table: entity totals, offsets
+//                       :1456-1472, and the prefix of its own units): re-reads the unit's list (13 % of the input on the 640x480 stream), ranks the
 //                       points per entity (stable) from the unit's prefix and writes `translation` then `roll` applied in
 //                       float64 (:1482-1485) as SoA + raster indices.
 // Same results as seg_fused.cuh and as the two-pass kernels of seg.cuh (tests compare all three bit for bit).
@@ -53,6 +52,7 @@ __global__ void __launch_bounds__(E2_SS_THREADS, 7) seg_stream_kernel(Dev d, uns
     const int hand_label = d.hand_label;
     const unsigned total_units = (unsigned)d.F * (unsigned)S;
     uint64_t *full = s.full[warp];
+    const uint64_t stream_once = l2_evict_first_policy();      // the input is read once: keep the scratch lists in L2 instead
     if (lane == 0) {
         for (int i = 0; i < E2_SS_STAGES; ++i) mbar_init(&full[i], 1);
         mbar_fence_init();
@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(E2_SS_THREADS, 7) seg_stream_kernel(Dev d, uns
             const int npts = min(E2_SS_TILE, N - start);
             const unsigned xb = (unsigned)npts * 12u, lb = UPSCALE ? 0u : (unsigned)npts * 4u;
             mbar_arrive_expect_tx(&full[st], xb + lb);
-            bulk_g2s(&s.xs[warp][st][0], xyz + (size_t)start * 3, xb, &full[st]);
-            if (!UPSCALE) bulk_g2s(&s.ls[warp][st][0], lab + start, lb, &full[st]);
+            bulk_g2s_hint(&s.xs[warp][st][0], xyz + (size_t)start * 3, xb, &full[st], stream_once);
+            if (!UPSCALE) bulk_g2s_hint(&s.ls[warp][st][0], lab + start, lb, &full[st], stream_once);
         };
         if (lane == 0)
             for (int i = 0; i < min(E2_SS_STAGES, nt); ++i) issue(i);
@@ -172,55 +172,64 @@ __global__ void __launch_bounds__(E2_SS_THREADS, 7) seg_stream_kernel(Dev d, uns
     }
 }
 
-// grid F, block E2SEC_MAX_ENTITIES: exclusive prefix over the frame's units per entity (8 independent loads in flight),
-// entity totals and offsets
-__global__ void __launch_bounds__(E2SEC_MAX_ENTITIES) seg_unit_scan_kernel(Dev d)
-{
-    pdl_enter();
-    __shared__ int tot[E2SEC_MAX_ENTITIES];
-    const int f = blockIdx.x, e = threadIdx.x, S = d.S, K = d.K;
-    if (e < K) {
-        unsigned *c = d.seg_cnt + (size_t)f * S * K + e;
-        unsigned run = 0;
-        for (int s0 = 0; s0 < S; s0 += 8) {
-            unsigned v[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = (s0 + j < S) ? c[(size_t)(s0 + j) * K] : 0u;
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-                if (s0 + j < S) { c[(size_t)(s0 + j) * K] = run; run += v[j]; }
-        }
-        tot[e] = (int)run;
-        d.ent_raw[f * K + e] = (int)run;
-    }
-    __syncthreads();
-    if (e == 0) {
-        int off = 0;
-        for (int k = 0; k < K; ++k) {
-            const bool stored = (k != 0 && k != d.ground_idx);   // :1520 -- index 0 and the ground label are never filtered nor related
-            d.ent_off[f * K + k] = stored ? off : -1;
-            if (stored) off += tot[k];
-        }
-        d.frame_used[f] = off < d.cap ? off : d.cap;
-        if (off > d.cap) atomicExch(d.error, E2SEC_ERR_CAPACITY);
-    }
-}
-
-// grid (ceil(S / E2_SS_WARPS), F): one warp per unit
+// grid (ceil(S / E2_SS_WARPS), F): one warp per unit.  Every CTA first sums the frame's count table itself (S x K counters,
+// a few kB out of L2: thread (g, e) walks the units g, g + 2, ... of entity e with 8 loads in flight) -- entity totals,
+// offsets (:1456-1472; index 0 and the ground are counted, never stored, :1520) and the prefix of its own four units --
+// which is cheaper than a separate scan kernel between the two.
 __global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned *next)
 {
     pdl_enter();
     __shared__ unsigned wc[E2_SS_WARPS][E2SEC_MAX_ENTITIES];
+    __shared__ unsigned part[2][E2_SS_WARPS + 1][E2SEC_MAX_ENTITIES];
+    __shared__ int ent_off[E2SEC_MAX_ENTITIES];
+    static_assert(E2_SS_THREADS == 2 * E2SEC_MAX_ENTITIES, "two thread groups of one thread per entity");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int f = blockIdx.y, u = blockIdx.x * E2_SS_WARPS + warp, S = d.S, K = d.K;
+    const int f = blockIdx.y, u0 = blockIdx.x * E2_SS_WARPS, u = u0 + warp, S = d.S, K = d.K;
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *next = 0;      // the counter of the next batch's stream kernel
+    {
+        const int e = threadIdx.x % E2SEC_MAX_ENTITIES, g = threadIdx.x / E2SEC_MAX_ENTITIES;
+        unsigned tot = 0, pre[E2_SS_WARPS] = {0, 0, 0, 0};
+        if (e < K) {
+            const unsigned *c = d.seg_cnt + (size_t)f * S * K + e;
+            for (int s0 = g; s0 < S; s0 += 16) {
+                unsigned v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = (s0 + 2 * j < S) ? c[(size_t)(s0 + 2 * j) * K] : 0u;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int su = s0 + 2 * j;
+                    tot += v[j];
+#pragma unroll
+                    for (int w = 0; w < E2_SS_WARPS; ++w) pre[w] += (su < u0 + w) ? v[j] : 0u;
+                }
+            }
+        }
+#pragma unroll
+        for (int w = 0; w < E2_SS_WARPS; ++w) part[g][w][e] = pre[w];
+        part[g][E2_SS_WARPS][e] = tot;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int off = 0;
+        for (int k = 0; k < K; ++k) {
+            const bool stored = (k != 0 && k != d.ground_idx);
+            const int tk = (int)(part[0][E2_SS_WARPS][k] + part[1][E2_SS_WARPS][k]);
+            ent_off[k] = stored ? off : -1;
+            if (blockIdx.x == 0) { d.ent_raw[f * K + k] = tk; d.ent_off[f * K + k] = stored ? off : -1; }
+            if (stored) off += tk;
+        }
+        if (blockIdx.x == 0) {
+            d.frame_used[f] = off < d.cap ? off : d.cap;
+            if (off > d.cap) atomicExch(d.error, E2SEC_ERR_CAPACITY);
+        }
+    }
+    __syncthreads();
     if (u >= S) return;
     const unsigned M = d.seg_len[(size_t)f * S + u];
     if (M == 0) return;
-    const unsigned *pre = d.seg_cnt + ((size_t)f * S + u) * K;
     for (int e = lane; e < K; e += 32) {
-        const int off = d.ent_off[f * K + e];
-        wc[warp][e] = off < 0 ? 0xffffffffu : (unsigned)off + pre[e];            // first output position of the unit, per entity
+        const int off = ent_off[e];
+        wc[warp][e] = off < 0 ? 0xffffffffu : (unsigned)off + part[0][warp][e] + part[1][warp][e];   // first output position of the unit, per entity
     }
     __syncwarp();
     const uint4 *list = d.seg_list + (size_t)f * d.N + (size_t)u * E2_SS_UNIT;
