@@ -186,9 +186,13 @@ __global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int f = blockIdx.y, u0 = blockIdx.x * E2_SS_WARPS, u = u0 + warp, S = d.S, K = d.K;
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *next = 0;      // the counter of the next batch's stream kernel
+    // a CTA whose units hold no stored point has nothing to place (the first CTA of a frame still publishes the totals)
+    unsigned mlen = 0;
+    if (u < S) mlen = d.seg_len[(size_t)f * S + u];
+    if (!__syncthreads_or(mlen != 0) && blockIdx.x != 0) return;
     {
         const int e = threadIdx.x % E2SEC_MAX_ENTITIES, g = threadIdx.x / E2SEC_MAX_ENTITIES;
-        unsigned tot = 0, pre[E2_SS_WARPS] = {0, 0, 0, 0};
+        unsigned tot = 0, pre = 0;
         if (e < K) {
             const unsigned *c = d.seg_cnt + (size_t)f * S * K + e;
             for (int s0 = g; s0 < S; s0 += 16) {
@@ -197,15 +201,12 @@ __global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned
                 for (int j = 0; j < 8; ++j) v[j] = (s0 + 2 * j < S) ? c[(size_t)(s0 + 2 * j) * K] : 0u;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    const int su = s0 + 2 * j;
                     tot += v[j];
-#pragma unroll
-                    for (int w = 0; w < E2_SS_WARPS; ++w) pre[w] += (su < u0 + w) ? v[j] : 0u;
+                    pre += (s0 + 2 * j < u0) ? v[j] : 0u;
                 }
             }
         }
-#pragma unroll
-        for (int w = 0; w < E2_SS_WARPS; ++w) part[g][w][e] = pre[w];
+        part[g][0][e] = pre;                                   // stored points of entity e in the units before this CTA's
         part[g][E2_SS_WARPS][e] = tot;
     }
     __syncthreads();
@@ -224,23 +225,29 @@ __global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned
         }
     }
     __syncthreads();
-    if (u >= S) return;
-    const unsigned M = d.seg_len[(size_t)f * S + u];
+    const unsigned M = mlen;
     if (M == 0) return;
     for (int e = lane; e < K; e += 32) {
         const int off = ent_off[e];
-        wc[warp][e] = off < 0 ? 0xffffffffu : (unsigned)off + part[0][warp][e] + part[1][warp][e];   // first output position of the unit, per entity
+        unsigned first = (unsigned)off + part[0][0][e] + part[1][0][e];
+        for (int w = 0; w < warp; ++w) first += d.seg_cnt[((size_t)f * S + u0 + w) * K + e];    // the CTA's earlier units
+        wc[warp][e] = off < 0 ? 0xffffffffu : first;              // first output position of the unit, per entity
     }
     __syncwarp();
     const uint4 *list = d.seg_list + (size_t)f * d.N + (size_t)u * E2_SS_UNIT;
     const unsigned lt = (1u << lane) - 1u;
     const size_t fb = (size_t)f * d.cap;
-    uint4 nxt = make_uint4(0, 0, 0, 0);
-    if ((unsigned)lane < M) nxt = __ldcg(&list[lane]);
+    // three rows of the list in flight while one is ranked
+    uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0, r2 = r0;
+    if ((unsigned)lane < M) r0 = __ldcg(&list[lane]);
+    if ((unsigned)lane + 32 < M) r1 = __ldcg(&list[lane + 32]);
+    if ((unsigned)lane + 64 < M) r2 = __ldcg(&list[lane + 64]);
     for (unsigned q = 0; q < M; q += 32) {
         const unsigned i = q + lane;
-        const uint4 rec = nxt;
-        if (i + 32 < M) nxt = __ldcg(&list[i + 32]);           // the next row is in flight while this one is ranked
+        const uint4 rec = r0;
+        r0 = r1;
+        r1 = r2;
+        if (i + 96 < M) r2 = __ldcg(&list[i + 96]);
         const int e = (i < M) ? (int)(rec.w & 63u) : -1;
         const unsigned peers = __match_any_sync(0xffffffffu, e);
         unsigned pos = 0;
@@ -249,7 +256,10 @@ __global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned
         if (e >= 0 && lane == __ffs(peers) - 1) wc[warp][e] += __popc(peers);
         __syncwarp();
         if (e >= 0 && pos < (unsigned)d.cap) {
-            double X = widen(__uint_as_float(rec.x)), Y = widen(__uint_as_float(rec.y)), Z = widen(__uint_as_float(rec.z));
+            double X = (double)__uint_as_float(rec.x), Y = (double)__uint_as_float(rec.y), Z = (double)__uint_as_float(rec.z);
+            if (((rec.x & 0x7fffffffu) == 0x7f800000u) | ((rec.y & 0x7fffffffu) == 0x7f800000u) | ((rec.z & 0x7fffffffu) == 0x7f800000u)) {
+                X = widen(__uint_as_float(rec.x)); Y = widen(__uint_as_float(rec.y)); Z = widen(__uint_as_float(rec.z));   // +-inf -> +-DBL_MAX (:1445), rare
+            }
             if (d.affine) {
                 transform_point_affine(d.T, X, Y, Z);
                 transform_point_affine(d.R, X, Y, Z);
