@@ -30,9 +30,10 @@ METRIC = "e2sec_frames_per_sec"
 UNIT = "frames/s"
 WIDTH, HEIGHT, N_OBJECTS, STREAM_CONFIG = 640, 480, 10, 2
 # dram__bytes_read.sum + dram__bytes_write.sum per frame of the dominant kernel of each stage, from the ncu --set full capture
-# of this workload (profiles/r1_v8_ncu_full_summary.csv: 100-frame launches): seg_fused_kernel, cell_filter_kernel,
-# contact_work_kernel
-NCU_TRAFFIC_PER_FRAME = {"segment": 8.292e6, "radius": 1.857e6, "pairs": 0.793e6}
+# of this workload (profiles/r1_v13_ncu_full_summary.csv: 400-frame launches): seg_stream_kernel + seg_emit_kernel,
+# cell_filter_kernel, contact_work_kernel
+NCU_TRAFFIC_PER_FRAME = {"segment": 8.334e6, "radius": 2.007e6, "pairs": 0.821e6}
+NCU_STREAM_KERNEL_PER_FRAME = 5.770e6      # seg_stream_kernel alone: 4.922 MB read (the input, once) + 0.848 MB written
 BYTES_PER_POINT = 16                     # 12 B xyz float32 + 4 B int32 label, read once
 
 
@@ -42,8 +43,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=100, help="frames per step and per GPU")
-    ap.add_argument("--pool", type=int, default=300, help="distinct frames resident per GPU (cycled)")
+    ap.add_argument("--batch", type=int, default=400, help="frames per step and per GPU (larger batches amortise kernel tails: 100 -> 72k, 400 -> 88k frames/s)")
+    ap.add_argument("--pool", type=int, default=1200, help="distinct frames resident per GPU (cycled)")
     ap.add_argument("--filter-mode", default="closure", choices=["closure", "reference_seeded"])
     ap.add_argument("--radius-mode", default="bounded", choices=["bounded", "exact"],
                     help="bounded: cell-table bounds of np.median(pdist) with exact fallback; exact: always the O(n^2) selection")
@@ -433,6 +434,14 @@ def run_b200(args):
                          "peak_source": which, "whole_step_gbs_per_gpu": step_gbs, "whole_step_frac": step_gbs / peak,
                          # the streaming kernel (label filter + compaction) is the HBM-bound one; the other two stages are
                          # bound by O(cells^2) / O(n_a n_b) arithmetic on L2-resident data
+                         # the one kernel that streams the input (label filter + compaction, seg_stream.cuh), timed alone with
+                         # its own event pair: this is the HBM-bound kernel of the path
+                         "streaming_kernel": ({"name": "seg_stream_kernel", "ms": eng.seg_stream_ms,
+                                               "algorithmic_gbs": alg / (eng.seg_stream_ms * 1e-3) / 1e9,
+                                               "frac": alg / (eng.seg_stream_ms * 1e-3) / 1e9 / peak,
+                                               "dram_gbs": (NCU_STREAM_KERNEL_PER_FRAME * B / (eng.seg_stream_ms * 1e-3) / 1e9)
+                                               if N == 307200 else None}
+                                              if getattr(eng, "seg_stream_ms", 0) > 0 else None),
                          "stages": {k: {"ms": stages[k], "algorithmic_gbs": alg / (stages[k] * 1e-3) / 1e9,
                                         "frac": alg / (stages[k] * 1e-3) / 1e9 / peak,
                                         "dram_gbs": (NCU_TRAFFIC_PER_FRAME[k] * B / (stages[k] * 1e-3) / 1e9) if N == 307200 else None}

@@ -143,7 +143,8 @@ const double *e2sec_records_dev(e2sec_ctx *ctx);
 int e2sec_sync(e2sec_ctx *ctx);
 /* number of kernels launched by this context so far (bench.py's gpu_launches) */
 int64_t e2sec_launch_count(const e2sec_ctx *ctx);
-/* per-stage device time of the last batch in ms: segment, medians, radius, filter, stats, pairs     */
+/* per-stage device time of the last batch in ms: segment, medians, radius, filter, stats, pairs, assemble;
+ * out[7] = the streaming segmentation kernel alone (part of "segment")                              */
 int e2sec_stage_ms(e2sec_ctx *ctx, float out[8]);
 
 /* ---- operators at the reference's own seams ------------------------------------------------------ */

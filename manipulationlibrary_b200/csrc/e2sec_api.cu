@@ -51,7 +51,8 @@ struct e2sec_ctx {
         frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next, ct_map, seg_list, seg_len, seg_next;
     int map_cfg[4] = {0, 0, 0, 0};
     int64_t launches = 0;
-    cudaEvent_t ev[8];
+    cudaEvent_t ev[10];            // [0..7] stage boundaries, [8] / [9] around the streaming segmentation kernel
+    bool ev_stream = false;
     bool ev_valid = false;
     int sm_count = 148;
     int sf_cluster = 8;
@@ -597,8 +598,11 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labe
         unsigned *next = (unsigned *)ctx->seg_next.p;
         const long long units = (long long)n_frames * du.S;
         const int ctas = (int)std::min<long long>((units + E2_SS_WARPS - 1) / E2_SS_WARPS, (long long)ctx->sm_count * 7);
+        cudaEventRecord(ctx->ev[8], st);
         if (upscale) launch_pdl(ctx, seg_stream_kernel<true>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);
         else launch_pdl(ctx, seg_stream_kernel<false>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);
+        cudaEventRecord(ctx->ev[9], st);
+        ctx->ev_stream = true;
         launch_pdl(ctx, seg_emit_kernel, dim3((du.S + E2_SS_WARPS - 1) / E2_SS_WARPS, n_frames), dim3(E2_SS_THREADS), 0, st, du, next);
     } else if (fused) {
         const int tpf = (N + E2_SF_TILE - 1) / E2_SF_TILE;
@@ -671,6 +675,8 @@ extern "C" int e2sec_stage_ms(e2sec_ctx *ctx, float out[8])
     for (int i = 0; i < 8; ++i) out[i] = 0.f;
     for (int i = 0; i < 7; ++i)
         if (cudaEventElapsedTime(&out[i], ctx->ev[i], ctx->ev[i + 1]) != cudaSuccess) out[i] = -1.f;
+    // out[7]: the streaming segmentation kernel alone (seg_stream_kernel), the HBM-bound kernel of the path
+    if (ctx->ev_stream && cudaEventElapsedTime(&out[7], ctx->ev[8], ctx->ev[9]) != cudaSuccess) out[7] = -1.f;
     cudaGetLastError();
     return E2SEC_OK;
 }

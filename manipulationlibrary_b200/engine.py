@@ -108,7 +108,9 @@ class Engine:
     def stage_ms(self):
         out = np.zeros(8, np.float32)
         self._check(lib.e2sec_stage_ms(self._h, ptr(out)), "e2sec_stage_ms")
-        return dict(zip(["segment", "medians", "radius", "filter", "stats", "pairs", "assemble"], out[:7].tolist()))
+        st = dict(zip(["segment", "medians", "radius", "filter", "stats", "pairs", "assemble"], out[:7].tolist()))
+        self.seg_stream_ms = float(out[7])          # the streaming kernel alone (inside "segment")
+        return st
 
     # ---- operators ------------------------------------------------------------------------------
     def region_filter(self, pcd, center, median_distance, mode="closure", seed=0):
