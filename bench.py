@@ -240,7 +240,12 @@ def run_b200(args):
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    saved_stdout = None
     if world > 1:
+        # NCCL prints its version banner on stdout when the communicator comes up: keep stdout for the one JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     hx, hl = generate_pool(stream, rank_first, pool)
     hx_t = torch.from_numpy(hx).pin_memory()
@@ -378,6 +383,10 @@ def run_b200(args):
         for i in range(W):
             step(i, True)
     eng.sync()
+    if saved_stdout is not None:            # the warm-up has run the first collectives: the banner is out
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     uuid = str(torch.cuda.get_device_properties(dev).uuid)
     sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if rank == 0 else None
     time.sleep(0.3 if sampler else 0.0)
