@@ -587,7 +587,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         // ---- F: can anything else be reached at r_hi? --------------------------------------------------------------
         // Candidate cells: non-members within r_hi of a member or of another candidate (transitively).  Cells that are
         // not candidates cannot be reached at any radius <= r_hi, whatever happens to the candidates.
-        if (tid == 0 && !s.member[pcell[s.seed]]) s.amb = 1;      // the seed's own cell must be certain
+        if (tid == 0 && !s.member[pcell[s.seed]]) s.amb = 2;      // the seed's own cell must be certain
         for (int b = tid; b < E2_CELL_MAX; b += E2_CELL_THREADS) s.cand[b] = 0;
         __syncthreads();
         for (;;) {
@@ -609,7 +609,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         }
         // ---- F2: settle the candidate points one by one against the member POINTS (exact float64 distances) ------
         const unsigned nU = s.n_cand;
-        if (nU > E2_CELL_UMAX) { if (tid == 0) s.amb = 1; }
+        if (nU > E2_CELL_UMAX) { if (tid == 0) s.amb = 3; }
         else if (nU > 0 && !s.amb) {
             for (int i = tid; i < n; i += E2_CELL_THREADS)
                 if (s.cand[pcell[i]]) s.ulist[atomicAdd(&s.n_front, 1u)] = (unsigned)i;
@@ -639,7 +639,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             }
             // the last round changed nothing: udist is measured against the final member set
             for (unsigned u = tid; u < nU; u += E2_CELL_THREADS)
-                if (!s.joined[u] && s.udist[u] <= t_hi) s.amb = 1;      // reachable at r_hi but not at r_lo
+                if (!s.joined[u] && s.udist[u] <= t_hi) s.amb = 4;      // reachable at r_hi but not at r_lo
         }
         __syncthreads();
         decided = !s.amb;
@@ -647,7 +647,14 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         decided = false;                                           // too many cells for the table
     }
     if (!decided) {
-        if (tid == 0) d.amb[fe] = 1;
+        if (tid == 0) {
+            d.amb[fe] = 1;
+            atomicAdd(d.amb_count, 1);
+#ifdef E2_CELL_DEBUG
+            printf("amb fe=%d n=%d reason=%d (1 table overflow, 2 seed cell, 3 candidates > %d, 4 point in the band) m=%u n_cand=%u r_lo=%g r_hi=%g\n", fe, n,
+                   filtered && s.overflow ? 1 : (int)s.amb, E2_CELL_UMAX, s.m, s.n_cand, s.r_lo, s.r_hi);
+#endif
+        }
         return;
     }
 

@@ -84,6 +84,7 @@ struct Dev {
     unsigned short *pcell;            // F x cap     cell of each stored point (hash slot, then compact index)
     double *rad_lo, *rad_hi;          // F x K       float32-rounded bounds of the median pair distance
     int *amb;                         // F x K       1 = the cell table could not decide: the exact path runs
+    int *amb_count;                   // number of such entities in the batch (reset by halo_commit_kernel)
     // stats + pairs
     double *aabb;                     // F x K x 6
     double *mean;                     // F x K x 3
@@ -104,6 +105,13 @@ __device__ __forceinline__ void pdl_enter()
 {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+// BOUNDED radius mode and the cell table decided every entity of the batch: the kernels of the exact O(n^2) radius have
+// nothing to do (they are launched unconditionally -- the host never waits for the device inside a batch)
+__device__ __forceinline__ bool exact_path_idle(const Dev &d)
+{
+    return d.radius_mode == E2SEC_RADIUS_BOUNDED && *((volatile int *)d.amb_count) == 0;
 }
 
 __device__ __forceinline__ u64 d2key(double v) { return (u64)__double_as_longlong(v); }

@@ -96,37 +96,47 @@ __global__ void contact_plan_kernel(Dev d, ContactPlan plan)
     plan.cnt[idx] = items;
 }
 
-// single CTA of 1024 threads: exclusive scan of plan.cnt -> plan.off (every thread owns a run of consecutive entries: one
-// block scan in all), then the item -> entry map the work kernel reads instead of searching plan.off
+// single CTA of 1024 threads: exclusive scan of plan.cnt -> plan.off, 4096 entries per round (one coalesced uint4 per
+// thread), then the item -> entry map the work kernel reads instead of searching plan.off
 __global__ void __launch_bounds__(1024) contact_scan_kernel(ContactPlan plan, int n)
 {
     pdl_enter();
     __shared__ unsigned warp_tot[32];
+    __shared__ unsigned carry_s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int per = (n + 1023) / 1024, first = tid * per, last = min(n, first + per);
-    unsigned mine = 0;
-    for (int i = first; i < last; ++i) mine += plan.cnt[i];
-    unsigned v = mine;
-    for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
-    if (lane == 31) warp_tot[warp] = v;
+    if (tid == 0) carry_s = 0;
     __syncthreads();
-    if (warp == 0) {
-        unsigned w = warp_tot[lane];
-        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += t; }
-        warp_tot[lane] = w;
+    for (int base = 0; base < n; base += 4096) {
+        const int i0 = base + 4 * tid;
+        unsigned c[4] = {0, 0, 0, 0};
+        if (i0 + 3 < n) { const uint4 q = *reinterpret_cast<const uint4 *>(plan.cnt + i0); c[0] = q.x; c[1] = q.y; c[2] = q.z; c[3] = q.w; }
+        else for (int k = 0; k < 4; ++k) if (i0 + k < n) c[k] = plan.cnt[i0 + k];
+        const unsigned mine = c[0] + c[1] + c[2] + c[3];
+        unsigned v = mine;
+        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+        if (lane == 31) warp_tot[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned w = warp_tot[lane];
+            for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += t; }
+            warp_tot[lane] = w;
+        }
+        __syncthreads();
+        const unsigned carry = carry_s;
+        unsigned off = carry + v - mine + (warp ? warp_tot[warp - 1] : 0u);
+        for (int k = 0; k < 4; ++k)
+            if (i0 + k < n) {
+                plan.off[i0 + k] = off;
+                for (unsigned j = 0; j < c[k]; ++j)
+                    if (off + j < plan.map_cap) plan.map[off + j] = (unsigned)(i0 + k);
+                off += c[k];
+            }
+        const unsigned block_total = warp_tot[31];
+        __syncthreads();
+        if (tid == 0) carry_s = carry + block_total;
+        __syncthreads();
     }
-    __syncthreads();
-    const unsigned total = warp_tot[31];
-    unsigned off = v - mine + (warp ? warp_tot[warp - 1] : 0u);
-    const bool mapped = total <= plan.map_cap;
-    for (int i = first; i < last; ++i) {
-        const unsigned items = plan.cnt[i];
-        plan.off[i] = off;
-        if (mapped)
-            for (unsigned c = 0; c < items; ++c) plan.map[off + c] = (unsigned)i;
-        off += items;
-    }
-    if (tid == 0) plan.off[n] = total;
+    if (tid == 0) plan.off[n] = carry_s;
 }
 
 struct ContactSmem {

@@ -44,7 +44,7 @@ struct e2sec_ctx {
     size_t cap_total = 0;          // stored-point capacity over the whole batch (maxF * N)
     Dev d;
     std::vector<DevBuf *> bufs;
-    DevBuf lab8_stage, gsub;
+    DevBuf lab8_stage, gsub, amb_count;
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
@@ -133,7 +133,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
     cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
-    ctx->bufs = {&ctx->lab8_stage, &ctx->gsub, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
+    ctx->bufs = {&ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
                  &ctx->radius, &ctx->rs, &ctx->hist, &ctx->cand, &ctx->cand_n, &ctx->seed_pos, &ctx->member,
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
@@ -234,6 +234,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     rc |= ensure(ctx, ctx->rad_lo, FK * sizeof(double));
     rc |= ensure(ctx, ctx->rad_hi, FK * sizeof(double));
     rc |= ensure(ctx, ctx->amb, FK * sizeof(int));
+    rc |= ensure(ctx, ctx->amb_count, sizeof(int));
     const size_t slots = (size_t)K * (K - 1) / 2 + K + (size_t)K * K;
     rc |= ensure(ctx, ctx->ct_cnt, (size_t)F * slots * sizeof(unsigned));
     rc |= ensure(ctx, ctx->ct_off, ((size_t)F * slots + 1) * sizeof(unsigned));
@@ -245,6 +246,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     if (rc) return E2SEC_ERR_CUDA;
     CU(cudaMemset(ctx->error.p, 0, sizeof(int)));
     CU(cudaMemset(ctx->seg_next.p, 0, sizeof(unsigned)));
+    CU(cudaMemset(ctx->amb_count.p, 0, sizeof(int)));
     ctx->maxF = F;
     ctx->N = N;
     ctx->K = K;
@@ -287,6 +289,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     d.rad_lo = (double *)ctx->rad_lo.p;
     d.rad_hi = (double *)ctx->rad_hi.p;
     d.amb = (int *)ctx->amb.p;
+    d.amb_count = (int *)ctx->amb_count.p;
     d.seg_list = (uint4 *)ctx->seg_list.p;
     d.seg_len = (unsigned *)ctx->seg_len.p;
     return E2SEC_OK;

@@ -86,32 +86,42 @@ __device__ __forceinline__ double box_box_d2(const double *a, const double *b)
 __global__ void __launch_bounds__(1024) prev_kept_kernel(Dev d)
 {
     pdl_enter();
-    __shared__ unsigned char kept[1024];
+    __shared__ int warp_max[32];
     __shared__ int slot_s, id_s, last_s;
-    if (threadIdx.x == 0) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
         slot_s = d.halo_info[0] ? d.maxF : -1;
         id_s = d.halo_info[0] ? d.halo_info[1] : -1;
         last_s = -1;
     }
-    for (int base = 0; base < d.F; base += 1024) {           // flags in parallel, the running "previous" by one thread
-        const int f = base + threadIdx.x;
-        if (f < d.F)
-            kept[threadIdx.x] = (d.flags[f] & E2SEC_FLAG_HAND_LABEL) && d.ent_off[f * d.K + d.hand_idx] >= 0 &&
-                                d.n_list[f * d.K + d.hand_idx] > 0;
+    __syncthreads();
+    for (int base = 0; base < d.F; base += 1024) {           // running maximum of the kept frame indices (a block scan)
+        const int f = base + tid;
+        const bool kept = f < d.F && (d.flags[f] & E2SEC_FLAG_HAND_LABEL) && d.ent_off[f * d.K + d.hand_idx] >= 0 &&
+                          d.n_list[f * d.K + d.hand_idx] > 0;
+        int incl = kept ? f : -1;
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl = max(incl, t); }
+        if (lane == 31) warp_max[warp] = incl;
         __syncthreads();
-        if (threadIdx.x == 0) {
-            int slot = slot_s, id = id_s, last = last_s;
-            const int m = min(1024, d.F - base);
-            for (int i = 0; i < m; ++i) {
-                d.prev_slot[base + i] = slot;
-                d.prev_id[base + i] = id;
-                if (kept[i]) { slot = base + i; id = d.frame_ids[base + i]; last = base + i; }
-            }
-            slot_s = slot; id_s = id; last_s = last;
+        if (warp == 0) {
+            int w = warp_max[lane];
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w = max(w, t); }
+            warp_max[lane] = w;
         }
         __syncthreads();
+        int excl = __shfl_up_sync(0xffffffffu, incl, 1);      // last kept frame strictly before f inside this block
+        if (lane == 0) excl = -1;
+        if (warp) excl = max(excl, warp_max[warp - 1]);
+        if (f < d.F) {
+            d.prev_slot[f] = excl >= 0 ? excl : slot_s;
+            d.prev_id[f] = excl >= 0 ? d.frame_ids[excl] : id_s;
+        }
+        const int block_last = warp_max[31];
+        __syncthreads();
+        if (tid == 0 && block_last >= 0) { slot_s = block_last; id_s = d.frame_ids[block_last]; last_s = block_last; }
+        __syncthreads();
     }
-    if (threadIdx.x == 0) d.halo_info[2] = last_s;
+    if (tid == 0) d.halo_info[2] = last_s;
 }
 
 // Copies the last kept frame of the batch into the halo slot (grid-stride over its stored points).
@@ -141,6 +151,7 @@ __global__ void halo_save_kernel(Dev d)
 __global__ void halo_commit_kernel(Dev d)     // after halo_save_kernel: publish the new halo
 {
     pdl_enter();
+    *d.amb_count = 0;                        // next batch
     const int src = d.halo_info[2];
     if (src < 0) return;
     d.halo_info[0] = 1;

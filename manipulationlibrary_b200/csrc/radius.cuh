@@ -37,6 +37,7 @@ __device__ __forceinline__ int shift_for_width(u64 width)
 __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, u64 *min_above)
 {
     pdl_enter();
+    if (exact_path_idle(d)) return;
     __shared__ double red[6][8];
     const int fe = blockIdx.x, f = fe / d.K;
     const int off = d.ent_off[fe], n = d.ent_raw[fe];
@@ -95,6 +96,7 @@ __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, u64 *min_above)
 __global__ void __launch_bounds__(1024) radius_plan_kernel(Dev d, PairPlan plan, int want_phase)
 {
     pdl_enter();
+    if (exact_path_idle(d)) return;
     __shared__ unsigned warp_tot[32];
     __shared__ unsigned carry;
     const int n_fe = d.F * d.K;
@@ -155,6 +157,7 @@ template <bool COLLECT>
 __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *min_above)
 {
     pdl_enter();
+    if (exact_path_idle(d)) return;
     unsigned short *cnt = reinterpret_cast<unsigned short *>(pair_smem);
     double *sx = reinterpret_cast<double *>(pair_smem + (COLLECT ? 0 : sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS));
     double *sy = sx + E2_TILE, *sz = sy + E2_TILE;
@@ -270,6 +273,7 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
 __global__ void radius_select_kernel(Dev d, u64 *below_acc, u64 *single_count)
 {
     pdl_enter();
+    if (exact_path_idle(d)) return;
     const int fe = blockIdx.x * blockDim.x + threadIdx.x;
     if (fe >= d.F * d.K) return;
     RadiusState &rs = d.rs[fe];
@@ -318,6 +322,7 @@ __global__ void radius_select_kernel(Dev d, u64 *below_acc, u64 *single_count)
 __global__ void __launch_bounds__(E2_SEL_THREADS) radius_final_kernel(Dev d, const u64 *min_above, const u64 *single_count)
 {
     pdl_enter();
+    if (exact_path_idle(d)) return;
     __shared__ SelectSmem sm;
     const int fe = blockIdx.x;
     RadiusState &rs = d.rs[fe];
