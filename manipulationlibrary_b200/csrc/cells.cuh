@@ -340,22 +340,64 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
     return false;
 }
 
+// What an entity with a candidate point inside the band (r_lo, r_hi] leaves behind for cell_filter_kernel<true>: once the
+// exact radius is known, the same point-level settlement finishes it -- no flood fill over the whole cloud.
+struct CellState {
+    unsigned char member[E2_CELL_MAX];
+    unsigned ulist[E2_CELL_UMAX];
+    unsigned n_u;
+    int seed;
+};
+
+// Point-level settlement of the nU candidate points against the member POINTS (exact float64 distances): a candidate whose
+// distance to a member is <= t_join becomes a member itself (virtual cell E2_CELL_JOIN); repeated until nothing changes,
+// so s.udist ends up measured against the final member set.
+__device__ __forceinline__ void cell_settle(CellSmem &s, const double *X, const double *Y, const double *Z, unsigned short *pcell,
+                                            int n, unsigned nU, double t_join)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (;;) {
+        if (tid == 0) s.n_new = 0;
+        __syncthreads();
+        for (unsigned u = warp; u < nU; u += E2_CELL_WARPS) {
+            if (s.joined[u]) continue;
+            const unsigned p = s.ulist[u];
+            const double x = X[p], y = Y[p], z = Z[p];
+            double best = 1e300;
+            for (int q = lane; q < n; q += 32)
+                if (s.member[pcell[q]]) best = fmin(best, dist2(x, y, z, X[q], Y[q], Z[q]));
+            best = warp_min_d(best);
+            if (lane == 0) {
+                s.udist[u] = best;
+                if (best <= t_join) { s.joined[u] = 1; pcell[p] = (unsigned short)E2_CELL_JOIN; s.n_new = 1; }
+            }
+        }
+        __syncthreads();
+        const unsigned grew = s.n_new;
+        __syncthreads();
+        if (!grew) break;
+    }
+}
+
 extern __shared__ __align__(16) unsigned char cell_smem_raw[];
 
 // grid F*K CTAs of E2_CELL_THREADS. Needs d.med (axis_median_kernel). Writes, for every filtered entity that it can
 // decide: seed_pos, flist, n_list, aabb, mean, rad_lo / rad_hi, amb = 0; for the others amb = 1 (exact path follows).
 // Entities that are not stored or have <= 3 points are finished here too (raw cloud, :1543-1546).
+// FINISH = true is the second visit (after the exact radius selection): only the entities that left a CellState (amb == 2).
+template <bool FINISH>
 __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_kernel(Dev d)
 {
     pdl_enter();
     CellSmem &s = *reinterpret_cast<CellSmem *>(cell_smem_raw);
     const int fe = blockIdx.x, f = fe / d.K;
+    if (FINISH && (exact_path_idle(d) || d.amb[fe] != 2)) return;
     const int off = d.ent_off[fe], n = d.ent_raw[fe];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double NaN = __longlong_as_double(0x7ff8000000000000ll);
-    if (tid == 0) { d.amb[fe] = 0; d.rad_lo[fe] = NaN; d.rad_hi[fe] = NaN; d.radius[fe] = NaN; }
+    if (!FINISH && tid == 0) { d.amb[fe] = 0; d.rad_lo[fe] = NaN; d.rad_hi[fe] = NaN; d.radius[fe] = NaN; }
     double *aabb = d.aabb + (size_t)fe * 6, *mean = d.mean + (size_t)fe * 3;
-    if (off < 0 || n == 0) {
+    if (!FINISH && (off < 0 || n == 0)) {
         if (tid == 0) { d.n_list[fe] = 0; d.seed_pos[fe] = -1; }
         if (tid < 6) aabb[tid] = 0.0;          // Open3D: an empty cloud has a zero box and a zero centre
         if (tid < 3) mean[tid] = 0.0;
@@ -367,7 +409,17 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
     unsigned short *pcell = d.pcell + pb;
     const bool filtered = n > 3;               // :1520
 
-    if (filtered) {
+    if (FINISH) {
+        // the cell closure of the first visit + the candidate points, settled at the exact float32 radius (pyx:35)
+        const CellState &cs = d.cell_state[fe];
+        for (int i = tid; i < E2_CELL_MAX; i += E2_CELL_THREADS) s.member[i] = cs.member[i];
+        const unsigned nU = cs.n_u;
+        for (unsigned u = tid; u < nU; u += E2_CELL_THREADS) { const unsigned p = cs.ulist[u]; s.ulist[u] = p; s.joined[u] = pcell[p] == E2_CELL_JOIN; }
+        if (tid == 0) { s.seed = cs.seed; s.overflow = 0; s.amb = 0; s.t_lo = sq_threshold((double)(float)d.radius[fe]); }
+        __syncthreads();
+        cell_settle(s, X, Y, Z, pcell, n, nU, s.t_lo);
+    }
+    if (!FINISH && filtered) {
         // ---- A: seed, mean absolute deviation, AABB ------------------------------------------------------------
         // ---- M: per-axis medians = the seed target (:1523) -----------------------------------------------------------
         double med[3];
@@ -459,7 +511,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
     }
 
     bool decided = true;
-    if (filtered && !s.overflow) {
+    if (!FINISH && filtered && !s.overflow) {
         // ---- B3: per-cell count and outward-rounded float box (warp-aggregated shared atomics) -----------------
         for (int i = tid; i < 2 * E2_CELL_BINS; i += E2_CELL_THREADS) (&s.hist[0][0])[i] = 0;      // keys are dead now
         for (int base = 0; base < n; base += E2_CELL_THREADS) {
@@ -616,39 +668,28 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             for (int u = tid; u < E2_CELL_UMAX; u += E2_CELL_THREADS) s.joined[u] = 0;
             if (tid == 0) s.member[E2_CELL_JOIN] = 1;            // virtual cell of the points that join here
             __syncthreads();
-            for (;;) {
-                if (tid == 0) s.n_new = 0;
-                __syncthreads();
-                for (unsigned u = warp; u < nU; u += E2_CELL_WARPS) {
-                    if (s.joined[u]) continue;
-                    const unsigned p = s.ulist[u];
-                    const double x = X[p], y = Y[p], z = Z[p];
-                    double best = 1e300;
-                    for (int q = lane; q < n; q += 32)
-                        if (s.member[pcell[q]]) best = fmin(best, dist2(x, y, z, X[q], Y[q], Z[q]));
-                    best = warp_min_d(best);
-                    if (lane == 0) {
-                        s.udist[u] = best;
-                        if (best <= t_lo) { s.joined[u] = 1; pcell[p] = (unsigned short)E2_CELL_JOIN; s.n_new = 1; }   // reachable at every radius >= r_lo
-                    }
-                }
-                __syncthreads();
-                const unsigned grew = s.n_new;
-                __syncthreads();
-                if (!grew) break;
-            }
+            cell_settle(s, X, Y, Z, pcell, n, nU, t_lo);           // reachable at every radius >= r_lo
             // the last round changed nothing: udist is measured against the final member set
             for (unsigned u = tid; u < nU; u += E2_CELL_THREADS)
                 if (!s.joined[u] && s.udist[u] <= t_hi) s.amb = 4;      // reachable at r_hi but not at r_lo
         }
         __syncthreads();
         decided = !s.amb;
-    } else if (filtered) {
+    } else if (!FINISH && filtered) {
         decided = false;                                           // too many cells for the table
     }
     if (!decided) {
+        // a point inside the band is the only thing in the way: leave the closure so far for the second visit (amb = 2);
+        // everything else (table overflow, too many candidates) goes to the point-level flood fill of filter.cuh (amb = 1)
+        const bool resume = filtered && !s.overflow && s.amb == 4;
+        if (resume) {
+            CellState &cs = d.cell_state[fe];
+            for (int i = tid; i < E2_CELL_MAX; i += E2_CELL_THREADS) cs.member[i] = s.member[i];
+            for (unsigned u = tid; u < s.n_cand; u += E2_CELL_THREADS) cs.ulist[u] = s.ulist[u];
+            if (tid == 0) { cs.n_u = s.n_cand; cs.seed = s.seed; }
+        }
         if (tid == 0) {
-            d.amb[fe] = 1;
+            d.amb[fe] = resume ? 2 : 1;
             atomicAdd(d.amb_count, 1);
 #ifdef E2_CELL_DEBUG
             printf("amb fe=%d n=%d reason=%d (1 table overflow, 2 seed cell, 3 candidates > %d, 4 point in the band) m=%u n_cand=%u r_lo=%g r_hi=%g\n", fe, n,
@@ -693,8 +734,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         if (filtered) {                                            // dicti[0] = first_point (pyx:48): the seed counts twice
             tot[0] += X[s.seed]; tot[1] += Y[s.seed]; tot[2] += Z[s.seed];
             cntp += 1.0;
-            d.rad_lo[fe] = s.r_lo;
-            d.rad_hi[fe] = s.r_hi;
+            if (!FINISH) { d.rad_lo[fe] = s.r_lo; d.rad_hi[fe] = s.r_hi; }
         }
         for (int k = 0; k < 3; ++k) {
             aabb[k] = run ? l[k] : 0.0;

@@ -31,6 +31,8 @@ struct RadiusState {
     int pad;
 };
 
+struct CellState;
+
 // Device view of one context. Entity-level arrays are indexed fe = frame * K + e.
 struct Dev {
     int F, N, K, cap;                 // frames in this batch, points per frame, entities, stored-point capacity
@@ -83,7 +85,10 @@ struct Dev {
     // bounded-radius route (cells.cuh)
     unsigned short *pcell;            // F x cap     cell of each stored point (hash slot, then compact index)
     double *rad_lo, *rad_hi;          // F x K       float32-rounded bounds of the median pair distance
-    int *amb;                         // F x K       1 = the cell table could not decide: the exact path runs
+    int *amb;                         // F x K       1 = the cell table could not decide: exact radius + point-level flood fill;
+                                      //             2 = only a point inside the radius band is open: exact radius, then the cell
+                                      //                 closure is finished by cell_filter_kernel<true>
+    struct CellState *cell_state;     // F x K       closure state of the entities with amb == 2 (cells.cuh)
     int *amb_count;                   // number of such entities in the batch (reset by halo_commit_kernel)
     // stats + pairs
     double *aabb;                     // F x K x 6

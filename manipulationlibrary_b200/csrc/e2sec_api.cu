@@ -44,7 +44,7 @@ struct e2sec_ctx {
     size_t cap_total = 0;          // stored-point capacity over the whole batch (maxF * N)
     Dev d;
     std::vector<DevBuf *> bufs;
-    DevBuf lab8_stage, gsub, amb_count;
+    DevBuf lab8_stage, gsub, amb_count, cell_state;
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
@@ -122,7 +122,8 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     ctx->ev_valid = true;
     cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)(sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double)));
-    cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
+    cudaFuncSetAttribute(cell_filter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
+    cudaFuncSetAttribute(cell_filter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
     cudaFuncSetAttribute(seg_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
     cudaFuncSetAttribute(seg_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
     cudaFuncSetAttribute(seg_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegStreamSmem));
@@ -131,9 +132,9 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     { const char *e = getenv("E2SEC_SEG_MODE"); ctx->seg_cluster = e && !strcmp(e, "cluster"); }
     { const char *e = getenv("E2SEC_PDL"); ctx->pdl = !(e && e[0] == '0'); }
     { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
-    cudaFuncSetAttribute(cell_filter_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(cell_filter_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
-    ctx->bufs = {&ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
+    ctx->bufs = {&ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->cell_state, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
                  &ctx->radius, &ctx->rs, &ctx->hist, &ctx->cand, &ctx->cand_n, &ctx->seed_pos, &ctx->member,
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
@@ -235,6 +236,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     rc |= ensure(ctx, ctx->rad_hi, FK * sizeof(double));
     rc |= ensure(ctx, ctx->amb, FK * sizeof(int));
     rc |= ensure(ctx, ctx->amb_count, sizeof(int));
+    rc |= ensure(ctx, ctx->cell_state, FK * sizeof(CellState));
     const size_t slots = (size_t)K * (K - 1) / 2 + K + (size_t)K * K;
     rc |= ensure(ctx, ctx->ct_cnt, (size_t)F * slots * sizeof(unsigned));
     rc |= ensure(ctx, ctx->ct_off, ((size_t)F * slots + 1) * sizeof(unsigned));
@@ -290,6 +292,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     d.rad_hi = (double *)ctx->rad_hi.p;
     d.amb = (int *)ctx->amb.p;
     d.amb_count = (int *)ctx->amb_count.p;
+    d.cell_state = (CellState *)ctx->cell_state.p;
     d.seg_list = (uint4 *)ctx->seg_list.p;
     d.seg_len = (unsigned *)ctx->seg_len.p;
     return E2SEC_OK;
@@ -465,7 +468,7 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
     if (need_median && d.radius_mode != E2SEC_RADIUS_BOUNDED) { launch_pdl(ctx, axis_median_kernel, dim3(dim3(3, FK)), dim3(E2_SEL_THREADS), 0, st, d); }
     cudaEventRecord(ctx->ev[2], st);
     if (d.radius_mode == E2SEC_RADIUS_BOUNDED) {
-        launch_pdl(ctx, cell_filter_kernel, dim3(FK), dim3(E2_CELL_THREADS), sizeof(CellSmem), st, d);
+        launch_pdl(ctx, cell_filter_kernel<false>, dim3(FK), dim3(E2_CELL_THREADS), sizeof(CellSmem), st, d);
     }
     if (need_radius) {
         CU(cudaMemsetAsync(below_acc, 0, sizeof(u64) * FK, st));
@@ -481,6 +484,9 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
         launch_pdl(ctx, radius_plan_kernel, dim3(1), dim3(1024), 0, st, d, plan, 1);
         launch_pdl(ctx, pair_pass_kernel<true>, dim3(ctx->sm_count * 8), dim3(E2_PAIR_THREADS), 3 * E2_TILE * sizeof(double), st, d, plan, below_acc, min_above);
         launch_pdl(ctx, radius_final_kernel, dim3(FK), dim3(E2_SEL_THREADS), 0, st, d, min_above, single);
+        // entities that only had a point inside the radius band: the cell closure is finished at the exact radius
+        if (d.radius_mode == E2SEC_RADIUS_BOUNDED)
+            launch_pdl(ctx, cell_filter_kernel<true>, dim3(FK), dim3(E2_CELL_THREADS), sizeof(CellSmem), st, d);
     }
     cudaEventRecord(ctx->ev[3], st);
     launch_pdl(ctx, region_filter_kernel, dim3(FK), dim3(E2_FILTER_THREADS), 0, st, d);

@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(E2_FILTER_THREADS) region_filter_kernel(Dev d)
     const int fe = blockIdx.x, f = fe / d.K, e = fe - f * d.K;
     const int off = d.ent_off[fe], n = d.ent_raw[fe];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (d.radius_mode == E2SEC_RADIUS_BOUNDED && !d.amb[fe]) return;      // decided by cell_filter_kernel
+    if (d.radius_mode == E2SEC_RADIUS_BOUNDED && d.amb[fe] != 1) return;  // decided by cell_filter_kernel (first or second visit)
     if (off < 0) {
         if (tid == 0) { d.n_list[fe] = 0; d.seed_pos[fe] = -1; }
         return;

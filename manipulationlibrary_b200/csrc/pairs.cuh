@@ -20,7 +20,7 @@ __global__ void __launch_bounds__(E2_STATS_THREADS) entity_stats_kernel(Dev d)
     const int fe = blockIdx.x, f = fe / d.K;
     const int off = d.ent_off[fe];
     const int tid = threadIdx.x;
-    if (d.radius_mode == E2SEC_RADIUS_BOUNDED && !d.amb[fe]) return;      // cell_filter_kernel wrote the stats
+    if (d.radius_mode == E2SEC_RADIUS_BOUNDED && d.amb[fe] != 1) return;  // cell_filter_kernel wrote the stats
     double *aabb = d.aabb + (size_t)fe * 6, *mean = d.mean + (size_t)fe * 3;
     const int m = (off < 0) ? 0 : d.n_list[fe];
     if (m == 0) {
