@@ -17,8 +17,11 @@
 //   F  if no non-member cell has dmin <= r_hi to a member cell, no further point can be reached at any radius in
 //      [r_lo, r_hi]: the closure of the TRUE radius is exactly the union of the member cells.  Otherwise the
 //      points of the cells that could still be reached (few) are settled one by one with exact float64 distances
-//      to the member points: <= r_lo joins, > r_hi stays out; a point in between makes the entity ambiguous and
-//      the exact path (radius.cuh + filter.cuh) redoes it.
+//      to the member points: <= r_lo joins, > r_hi stays out; a point in between makes the entity ambiguous: the
+//      exact radius is selected (radius.cuh) and a SECOND VISIT of this kernel (cell_filter_kernel<true>) settles the
+//      same candidate points at that radius from the saved closure (CellState) -- exact by the argument of E / F, and
+//      no flood fill over the whole cloud.  Only a cell table that overflows or more than E2_CELL_UMAX candidate points
+//      send the entity to the point-level flood fill of filter.cuh.
 //   G  stable compaction of the member points (raster order, like the exact path) + AABB / mean / count
 #pragma once
 #include "common.cuh"
