@@ -28,10 +28,10 @@
 #include "filter.cuh"
 
 #ifndef E2_CELL_THREADS
-#define E2_CELL_THREADS 512
+#define E2_CELL_THREADS 384        // 384 x 3 CTAs/SM beat 512 x 2 by 9 % (tools/exp_cell_threads.sh): more, smaller CTAs hide the barriers
 #endif
 #ifndef E2_CELL_CTAS
-#define E2_CELL_CTAS 2              // resident CTAs per SM the register budget is cut for
+#define E2_CELL_CTAS 3              // resident CTAs per SM the register budget is cut for
 #endif
 #define E2_CELL_WARPS (E2_CELL_THREADS / 32)
 #define E2_CELL_MAX 1024          // occupied cells per entity
@@ -492,17 +492,18 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         __syncthreads();
         // ---- B2: compact indices in slot order ------------------------------------------------------------------
         {
-            const int per = E2_CELL_HASH / E2_CELL_THREADS;       // 8 consecutive slots per thread
+            const int per = (E2_CELL_HASH + E2_CELL_THREADS - 1) / E2_CELL_THREADS;      // consecutive slots per thread
+            const int j0 = tid * per, j1 = min(E2_CELL_HASH, j0 + per);
             unsigned occ = 0;
-            for (int j = 0; j < per; ++j) occ += (s.keys[tid * per + j] != E2_CELL_EMPTY);
+            for (int j = j0; j < j1; ++j) occ += (s.keys[j] != E2_CELL_EMPTY);
             unsigned incl = occ;
             for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
             if (lane == 31) s.wcnt[warp] = incl;
             __syncthreads();
             unsigned base = incl - occ;
             for (int w = 0; w < warp; ++w) base += s.wcnt[w];
-            for (int j = 0; j < per; ++j)
-                if (s.keys[tid * per + j] != E2_CELL_EMPTY) { s.cidx[tid * per + j] = (unsigned short)(base < E2_CELL_MAX ? base : 0); ++base; }
+            for (int j = j0; j < j1; ++j)
+                if (s.keys[j] != E2_CELL_EMPTY) { s.cidx[j] = (unsigned short)(base < E2_CELL_MAX ? base : 0); ++base; }
             if (tid == E2_CELL_THREADS - 1) { s.m = base; if (base > E2_CELL_JOIN) s.overflow = 1; }
         }
         for (int i = tid; i < E2_CELL_MAX; i += E2_CELL_THREADS) {
