@@ -606,7 +606,7 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labe
         du.S = (N + E2_SS_UNIT - 1) / E2_SS_UNIT;
         unsigned *next = (unsigned *)ctx->seg_next.p;
         const long long units = (long long)n_frames * du.S;
-        const int ctas = (int)std::min<long long>((units + E2_SS_WARPS - 1) / E2_SS_WARPS, (long long)ctx->sm_count * 7);
+        const int ctas = (int)std::min<long long>((units + E2_SS_WARPS - 1) / E2_SS_WARPS, (long long)ctx->sm_count * E2_SS_CTAS);
         cudaEventRecord(ctx->ev[8], st);
         if (upscale) launch_pdl(ctx, seg_stream_kernel<true>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);
         else launch_pdl(ctx, seg_stream_kernel<false>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);

@@ -25,8 +25,15 @@
 #define E2_SS_THREADS 128
 #define E2_SS_WARPS (E2_SS_THREADS / 32)
 #define E2_SS_TILE 128             // points per tile = 4 per lane
+#ifndef E2_SS_STAGES
 #define E2_SS_STAGES 3
+#endif
+#ifndef E2_SS_UNIT_TILES
 #define E2_SS_UNIT_TILES 16
+#endif
+#ifndef E2_SS_CTAS
+#define E2_SS_CTAS 7               // resident CTAs per SM (shared memory: 29 KB each)
+#endif
 #define E2_SS_UNIT (E2_SS_TILE * E2_SS_UNIT_TILES)
 
 struct SegStreamSmem {
@@ -41,7 +48,7 @@ extern __shared__ __align__(128) unsigned char seg_stream_smem_raw[];
 
 // d.S = units per frame; `next` = the unit counter (zero on entry, reset by seg_emit_kernel)
 template <bool UPSCALE>
-__global__ void __launch_bounds__(E2_SS_THREADS, 7) seg_stream_kernel(Dev d, unsigned *next)
+__global__ void __launch_bounds__(E2_SS_THREADS, E2_SS_CTAS) seg_stream_kernel(Dev d, unsigned *next)
 {
     pdl_enter();
     SegStreamSmem &s = *reinterpret_cast<SegStreamSmem *>(seg_stream_smem_raw);
