@@ -193,10 +193,14 @@ __device__ __forceinline__ void contact_sweep(const ContactSmem &s, unsigned mB,
             d32[k] = fmaf(uz, uz, fmaf(uy, uy, ux * ux));
             lo = fminf(lo, d32[k]);
         }
-        if (lo <= guard) {
+        // the loop is warp-uniform (same j in every lane): the lanes share their minimum whenever one of them improves it,
+        // so the guard follows the WARP's best pair and a "record" is a rare event (per-lane minima would send some lane of
+        // the warp into the float64 recheck at a third of the entries)
+        if (__any_sync(0xffffffffu, lo <= guard)) {
 #pragma unroll
             for (int k = 0; k < NK; ++k)
                 if (d32[k] <= guard) best = fmin(best, dist2(ax[k], ay[k], az[k], s.dx[j], s.dy[j], s.dz[j]));
+            best = warp_min_d(best);
             guard = contact_guard(best, c0);
         }
     }
