@@ -30,9 +30,9 @@ METRIC = "e2sec_frames_per_sec"
 UNIT = "frames/s"
 WIDTH, HEIGHT, N_OBJECTS, STREAM_CONFIG = 640, 480, 10, 2
 # dram__bytes_read.sum + dram__bytes_write.sum per frame of the dominant kernel of each stage, from the ncu --set full capture
-# of this workload (profiles/r1_v13_ncu_full_summary.csv: 400-frame launches): seg_stream_kernel + seg_emit_kernel,
+# of this workload (profiles/r1_v16_ncu_full_summary.csv: 400-frame launches): seg_stream_kernel + seg_emit_kernel,
 # cell_filter_kernel, contact_work_kernel
-NCU_TRAFFIC_PER_FRAME = {"segment": 8.334e6, "radius": 2.007e6, "pairs": 0.821e6}
+NCU_TRAFFIC_PER_FRAME = {"segment": 8.334e6, "radius": 2.454e6, "pairs": 0.822e6}
 NCU_STREAM_KERNEL_PER_FRAME = 5.770e6      # seg_stream_kernel alone: 4.922 MB read (the input, once) + 0.848 MB written
 BYTES_PER_POINT = 16                     # 12 B xyz float32 + 4 B int32 label, read once
 
