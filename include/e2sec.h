@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define E2SEC_ABI_VERSION 3
+#define E2SEC_ABI_VERSION 4
 #define E2SEC_MAX_ENTITIES 64      /* len(total_unique_labels) upper bound                           */
 #define E2SEC_LABEL_LUT 4096       /* raw labels must be integers in [0, E2SEC_LABEL_LUT)            */
 
@@ -183,6 +183,20 @@ int e2sec_resolver_state(const e2sec_resolver *r, int32_t labels[3], int32_t abs
  * the H,G / 3,G rows, removes repeated columns; returns the new column count, thins final_columns.   */
 int32_t e2sec_esec_to_e2sec(const char *codes, int32_t rows, int32_t n_cols, int32_t relations,
                             char *out_codes, int32_t *final_columns, int32_t *n_final);
+
+/* ---- the consumer of the tables: eSEC_analyser.getDissimilarityMatrix (eSEC_analyser.py:782-841, with
+ * _make_triple :866-889 and _compare_triple_matrics :915-944) and similarity_manipulations (:843-864).
+ * n_tables tables of `rows` (= 3 blocks of rows/3: T/N, SSR, DSR) x n_cols[m] codes of 6 bytes each
+ * (NUL-terminated, e2sec_resolver_table's / e2sec_esec_to_e2sec's layout) start at codes + offsets[m].
+ * Every pair is compared on the device, the shorter table continued by its last column.
+ * D (n_tables x n_tables, host) = sum over triples of sqrt(l)/sqrt(3) / (max(n_i, n_j) * divisor), l = the
+ * components of the triple that differ; divisor is 10 in getDissimilarityMatrix, 8 in
+ * similarity_manipulations (which returns (1 - D) * 100).  counts (may be NULL): n_tables x n_tables x 3
+ * triples with l = 1, 2, 3 -- the integers D is made of.                                             */
+int e2sec_dissimilarity(e2sec_ctx *ctx, const char *codes, const int64_t *offsets, const int32_t *n_cols,
+                        int32_t n_tables, int32_t rows, double divisor, double *D, uint32_t *counts);
+/* device time of the two kernels of the last e2sec_dissimilarity call, in ms */
+int e2sec_dissimilarity_ms(e2sec_ctx *ctx, float *ms);
 
 /* ---- input decode (host): o3d.io.read_point_cloud :1441 and pd.read_csv :1391 -------------------- */
 int e2sec_read_pcd_xyz(const char *path, float *xyz, int64_t capacity_points, int32_t *width,

@@ -62,6 +62,8 @@ def _load():
         "e2sec_pairwise_median": (C.c_int, [vp, vp, i32, vp]),
         "e2sec_axis_median": (C.c_int, [vp, vp, i32, vp]),
         "e2sec_min_distance": (C.c_int, [vp, vp, i32, vp, i32, dbl, vp]),
+        "e2sec_dissimilarity": (C.c_int, [vp, vp, vp, vp, i32, i32, dbl, vp, vp]),
+        "e2sec_dissimilarity_ms": (C.c_int, [vp, vp]),
         "e2sec_resolver_create": (C.c_int, [C.POINTER(Params), C.POINTER(vp)]),
         "e2sec_resolver_destroy": (None, [vp]),
         "e2sec_resolver_feed": (C.c_int, [vp, vp, i32]),

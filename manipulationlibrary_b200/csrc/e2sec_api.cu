@@ -19,6 +19,7 @@
 #include "cells.cuh"
 #include "pairs.cuh"
 #include "contact.cuh"
+#include "dissim.cuh"
 
 #define E2_MAX_REFINE 6        // histogram rounds launched per batch (each narrows the key interval 256x)
 
@@ -45,6 +46,9 @@ struct e2sec_ctx {
     Dev d;
     std::vector<DevBuf *> bufs;
     DevBuf lab8_stage, gsub, amb_count, cell_state;
+    DevBuf ds_codes, ds_off, ds_ncols, ds_packed, ds_counts, ds_D;     // e2sec_dissimilarity
+    cudaEvent_t ds_ev[2];
+    bool ds_timed = false;
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
@@ -114,6 +118,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    for (auto &ev : ctx->ds_ev) cudaEventCreate(&ev);
     cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
     for (int i = 0; i < 2; ++i) {
         cudaEventCreateWithFlags(&ctx->copy_done[i], cudaEventDisableTiming);
@@ -140,7 +145,8 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
                  &ctx->gz, &ctx->pair_key, &ctx->records, &ctx->error, &ctx->plan_off, &ctx->plan_total,
                  &ctx->below_acc, &ctx->min_above, &ctx->single_count, &ctx->cross_key, &ctx->frame_used, &ctx->prev_slot,
-                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->ct_map, &ctx->seg_list, &ctx->seg_len, &ctx->seg_next};
+                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->ct_map, &ctx->seg_list, &ctx->seg_len, &ctx->seg_next,
+                 &ctx->ds_codes, &ctx->ds_off, &ctx->ds_ncols, &ctx->ds_packed, &ctx->ds_counts, &ctx->ds_D};
     *out = ctx;
     return E2SEC_OK;
 }
@@ -154,6 +160,8 @@ extern "C" void e2sec_destroy(e2sec_ctx *ctx)
         if (b->p) cudaFree(b->p);
     if (ctx->ev_valid)
         for (auto &ev : ctx->ev) cudaEventDestroy(ev);
+    if (ctx->ev_valid)
+        for (auto &ev : ctx->ds_ev) cudaEventDestroy(ev);
     if (ctx->copy_stream) {
         cudaStreamSynchronize(ctx->copy_stream);
         for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->copy_done[i]); cudaEventDestroy(ctx->slot_free[i]); }
@@ -904,4 +912,69 @@ extern "C" int e2sec_min_distance(e2sec_ctx *ctx, const double *a, int32_t na, c
     memcpy(&d2, &key, sizeof(double));
     *dist = std::sqrt(d2);
     return check_device_error(ctx);
+}
+
+// ---- eSEC_analyser.getDissimilarityMatrix (:782-841) / similarity_manipulations (:843-864) -----------------------------
+extern "C" int e2sec_dissimilarity(e2sec_ctx *ctx, const char *codes, const int64_t *offsets, const int32_t *n_cols,
+                                   int32_t n_tables, int32_t rows, double divisor, double *D, uint32_t *counts)
+{
+    if (!ctx) return E2SEC_ERR_ARG;
+    if (!codes || !offsets || !n_cols || !D) return fail(ctx, E2SEC_ERR_ARG, "e2sec_dissimilarity: NULL argument");
+    if (n_tables < 1 || rows < 3 || rows % 3 || !(divisor > 0.0))
+        return fail(ctx, E2SEC_ERR_ARG, "e2sec_dissimilarity: need n_tables >= 1, rows a positive multiple of 3, divisor > 0");
+    const int M = n_tables, opal = rows / 3;
+    int Lmax = 0;
+    int64_t end = 0;
+    for (int m = 0; m < M; ++m) {
+        // a table without columns has no last column to repeat (the reference raises KeyError at :932 / :940)
+        if (n_cols[m] < 1) return fail(ctx, E2SEC_ERR_ARG, "e2sec_dissimilarity: table " + std::to_string(m) + " has no columns");
+        if (offsets[m] < 0) return fail(ctx, E2SEC_ERR_ARG, "e2sec_dissimilarity: negative offset");
+        Lmax = std::max(Lmax, (int)n_cols[m]);
+        end = std::max<int64_t>(end, offsets[m] + (int64_t)rows * n_cols[m] * E2_DS_CODE);
+    }
+    const size_t E = (size_t)Lmax * opal;
+    const size_t smem = 3 * E * sizeof(u64);
+    if (smem > 200 * 1024) return fail(ctx, E2SEC_ERR_CAPACITY, "e2sec_dissimilarity: a table has more than 200 KB of codes");
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    int rc = 0;
+    rc |= ensure(ctx, ctx->ds_codes, (size_t)end);
+    rc |= ensure(ctx, ctx->ds_off, sizeof(long long) * M);
+    rc |= ensure(ctx, ctx->ds_ncols, sizeof(int) * M);
+    rc |= ensure(ctx, ctx->ds_packed, sizeof(u64) * 3 * E * M);
+    rc |= ensure(ctx, ctx->ds_counts, sizeof(unsigned) * 3 * M * M);
+    rc |= ensure(ctx, ctx->ds_D, sizeof(double) * M * M);
+    if (rc) return E2SEC_ERR_CUDA;
+    static_assert(sizeof(long long) == sizeof(int64_t), "offset width");
+    CU(cudaMemcpyAsync(ctx->ds_codes.p, codes, (size_t)end, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->ds_off.p, offsets, sizeof(long long) * M, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(ctx->ds_ncols.p, n_cols, sizeof(int) * M, cudaMemcpyHostToDevice, st));
+    DissimDev d;
+    d.codes = (const unsigned char *)ctx->ds_codes.p;
+    d.off = (const long long *)ctx->ds_off.p;
+    d.ncols = (const int *)ctx->ds_ncols.p;
+    d.M = M; d.rows = rows; d.opal = opal; d.Lmax = Lmax; d.E = (int)E;
+    d.packed = (u64 *)ctx->ds_packed.p;
+    d.counts = (unsigned *)ctx->ds_counts.p;
+    d.D = (double *)ctx->ds_D.p;
+    d.divisor = divisor;
+    CU(cudaFuncSetAttribute(dissim_pairs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaEventRecord(ctx->ds_ev[0], st));
+    dissim_pack_kernel<<<M, E2_DS_THREADS, 0, st>>>(d); LAUNCHED();
+    dissim_pairs_kernel<<<dim3((M + E2_DS_JTILE - 1) / E2_DS_JTILE, M), E2_DS_THREADS, smem, st>>>(d); LAUNCHED();
+    CU(cudaEventRecord(ctx->ds_ev[1], st));
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(D, d.D, sizeof(double) * M * M, cudaMemcpyDeviceToHost, st));
+    if (counts) CU(cudaMemcpyAsync(counts, d.counts, sizeof(unsigned) * 3 * M * M, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    ctx->ds_timed = true;
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_dissimilarity_ms(e2sec_ctx *ctx, float *ms)
+{
+    if (!ctx || !ms) return E2SEC_ERR_ARG;
+    if (!ctx->ds_timed) return fail(ctx, E2SEC_ERR_STATE, "e2sec_dissimilarity_ms: no call to time yet");
+    CU(cudaEventElapsedTime(ms, ctx->ds_ev[0], ctx->ds_ev[1]));
+    return E2SEC_OK;
 }

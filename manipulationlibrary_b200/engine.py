@@ -131,6 +131,41 @@ class Engine:
         self._check(lib.e2sec_pairwise_median(self._h, ptr(pts), len(pts), C.byref(out)), "e2sec_pairwise_median")
         return out.value
 
+    def dissimilarity(self, tables, divisor=10.0, want_counts=False):
+        """tables: sequence of 2-D arrays of relation codes (rows x n_cols, the same row count, a multiple of 3).
+        -> D (M, M) float64 [, counts (M, M, 3) uint32]; eSEC_analyser._calc_D_shaped (:819-841) on the device."""
+        tabs = [np.asarray(t) for t in tables]
+        if not tabs:
+            raise ValueError("no tables")
+        rows = tabs[0].shape[0]
+        enc = []
+        for t in tabs:
+            if t.ndim != 2 or t.shape[0] != rows:
+                raise ValueError("every table needs the same number of rows")
+            if t.dtype.kind == "O":                    # pandas hands out object arrays
+                t = t.astype(str)
+            if t.dtype.kind not in "US":
+                raise ValueError("tables hold strings")
+            width = t.dtype.itemsize // (4 if t.dtype.kind == "U" else 1)
+            if width > 5 and t.size and int(np.char.str_len(t).max()) > 5:
+                raise ValueError("relation codes are at most 5 characters")
+            enc.append(np.ascontiguousarray(t.astype("S6")))
+        n_cols = np.array([t.shape[1] for t in enc], np.int32)
+        sizes = np.array([t.size * 6 for t in enc], np.int64)
+        offsets = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.int64)
+        blob = np.concatenate([t.reshape(-1).view(np.uint8) for t in enc]) if sizes.sum() else np.zeros(1, np.uint8)
+        M = len(enc)
+        D = np.empty((M, M), np.float64)
+        counts = np.empty((M, M, 3), np.uint32) if want_counts else None
+        self._check(lib.e2sec_dissimilarity(self._h, ptr(blob), ptr(offsets), ptr(n_cols), M, int(rows), float(divisor),
+                                            ptr(D), ptr(counts) if want_counts else None), "e2sec_dissimilarity")
+        return (D, counts) if want_counts else D
+
+    def dissimilarity_ms(self):
+        ms = C.c_float()
+        self._check(lib.e2sec_dissimilarity_ms(self._h, C.byref(ms)), "e2sec_dissimilarity_ms")
+        return ms.value
+
     def axis_median(self, pts):
         pts = np.ascontiguousarray(pts, np.float64)
         out = np.empty(3, np.float64)
