@@ -146,14 +146,19 @@ class Engine:
                 t = t.astype(str)
             if t.dtype.kind not in "US":
                 raise ValueError("tables hold strings")
-            width = t.dtype.itemsize // (4 if t.dtype.kind == "U" else 1)
-            if width > 5 and t.size and int(np.char.str_len(t).max()) > 5:
-                raise ValueError("relation codes are at most 5 characters")
-            enc.append(np.ascontiguousarray(t.astype("S6")))
+            # code units of every entry as integers (no per-element Python work): code points for str, bytes for bytes
+            unit = np.uint32 if t.dtype.kind == "U" else np.uint8
+            width = t.dtype.itemsize // np.dtype(unit).itemsize
+            cp = np.ascontiguousarray(t).view(unit).reshape(t.shape + (width,))
+            if cp.size and (int(cp.max()) > 127 or (width > 5 and cp[..., 5:].any())):
+                raise ValueError("relation codes are at most 5 ASCII characters")
+            b = np.zeros(t.shape + (6,), np.uint8)
+            b[..., :min(width, 5)] = cp[..., :5]
+            enc.append(b)
         n_cols = np.array([t.shape[1] for t in enc], np.int32)
-        sizes = np.array([t.size * 6 for t in enc], np.int64)
+        sizes = np.array([t.size for t in enc], np.int64)
         offsets = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.int64)
-        blob = np.concatenate([t.reshape(-1).view(np.uint8) for t in enc]) if sizes.sum() else np.zeros(1, np.uint8)
+        blob = np.concatenate([t.reshape(-1) for t in enc]) if sizes.sum() else np.zeros(1, np.uint8)
         M = len(enc)
         D = np.empty((M, M), np.float64)
         counts = np.empty((M, M, 3), np.uint32) if want_counts else None
