@@ -50,6 +50,9 @@ def parse():
                     help="bounded: cell-table bounds of np.median(pdist) with exact fallback; exact: always the O(n^2) selection")
     ap.add_argument("--cpu-frames", type=int, default=4, help="frames of the cpu_baseline sample (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--contexts", type=int, default=3,
+                    help="contexts (streams) per GPU: batch i runs on context i %% C with its one-frame halo in front, so the "
+                         "HBM-bound segmentation of one batch overlaps the issue-bound kernels of another (1: one stream)")
     ap.add_argument("--e2e-labels", default="u8", choices=["u8", "i32"],
                     help="host label images of the e2e leg: uint8 (e2sec_process_batch_labels8, 13 B/point over PCIe) or int32")
     return ap.parse_args()
@@ -248,6 +251,10 @@ def run_b200(args):
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     hx, hl = generate_pool(stream, rank_first, pool)
+    # one more frame in front: a copy of the pool's last frame, so that batch s can be handed over together with the frame
+    # before it (its halo) as one contiguous block even where the pool wraps
+    hx = np.concatenate([hx[-1:], hx])
+    hl = np.concatenate([hl[-1:], hl])
     hx_t = torch.from_numpy(hx).pin_memory()
     hl_t = torch.from_numpy(hl).pin_memory()
     lab8 = args.e2e_labels == "u8" and not args.no_e2e and int(hl.max()) < 256 and int(hl.min()) >= 0
@@ -258,31 +265,97 @@ def run_b200(args):
 
     p, keep = nat.make_params(**stream.params(filter_mode=args.filter_mode, filter_seed=20261104,
                                                radius_mode=args.radius_mode))
-    eng = Engine(local)
-    eng.configure(p, B, N, keep)
-    est = torch.cuda.ExternalStream(eng.stream, device=dev)
+    C = max(1, args.contexts)
+    engs = [Engine(local) for _ in range(C)]
+    for e in engs:
+        e.configure(p, B + 1, N, keep)
+    eng = engs[0]
+    ests = [torch.cuda.ExternalStream(e.stream, device=dev) for e in engs]
+    est = ests[0]
     rec_w = nat.record_doubles(int(p.n_entities))
     total_frames = (K + W) * B
-    rec_host = torch.empty((total_frames, rec_w), dtype=torch.float64).pin_memory()
-    rec_np = rec_host.numpy()
+    # batch i writes rows [i, 1:]; row [i, 0] receives the record of its halo frame when the batch carries one
+    rec_host = torch.empty((K + W, B + 1, rec_w), dtype=torch.float64).pin_memory()
+    rec3 = rec_host.numpy()
     ids_all = np.arange(rank_first, rank_first + total_frames, dtype=np.int32)
+    KEPT = float(nat.FLAG_HAND_LABEL | nat.FLAG_HAND_POINTS)
+    halo_of = {}                               # batch -> True when it was queued with its halo frame in front
 
-    def step(i, on_device):
-        s = (i * B) % pool
-        ids = ids_all[i * B: (i + 1) * B]
-        out = rec_np[i * B: (i + 1) * B]
-        # batches are queued back to back on the context's stream; finish() waits once (e2sec_sync) before the resolver
+    def inputs(on_device, first_frame):
+        """pointers to the frame with local index first_frame (pool position + 1 because of the leading copy)"""
+        s = first_frame % pool + 1
         if on_device:
-            eng.process_batch_device_async(dx[s].data_ptr(), dl[s].data_ptr(), B, ids, N, records=out)
-        else:
-            eng.process_batch_device_async(hx_t[s].data_ptr(), (hl8_t if lab8 else hl_t)[s].data_ptr(), B, ids, N, records=out,
-                                           on_device=False, labels8=lab8)
+            return dx[s].data_ptr(), dl[s].data_ptr()
+        return hx_t[s].data_ptr(), (hl8_t if lab8 else hl_t)[s].data_ptr()
 
-    def finish(n_steps, first_step, res, fed):
+    def halo_inputs(on_device, batch_first):
+        """the block that starts one frame before batch_first: pool position batch_first % pool of the extended arrays"""
+        s = batch_first % pool
+        if on_device:
+            return dx[s].data_ptr(), dl[s].data_ptr()
+        return hx_t[s].data_ptr(), (hl8_t if lab8 else hl_t)[s].data_ptr()
+
+    def queue(e, px, pl, n, ids, out, on_device):
+        if on_device:
+            e.process_batch_device_async(px, pl, n, ids, N, records=out)
+        else:
+            e.process_batch_device_async(px, pl, n, ids, N, records=out, on_device=False, labels8=lab8)
+
+    def step(i, on_device, seq_first):
+        """Queues batch i (frames i*B .. (i+1)*B-1 of this rank's block) on context i % C.  With one context the batches of
+        a sequence follow each other on its stream and the context carries the previous kept frame itself.  With several,
+        every batch is its own little sequence on its context: the frame before it goes in front as the halo (its record
+        lands in row 0 and is dropped) -- the same one-frame halo the frame sharding across GPUs uses."""
+        c = i % C
+        e = engs[c]
+        ids = ids_all[i * B: (i + 1) * B]
+        if C == 1 or i == seq_first:
+            if C > 1:
+                e.reset_sequence()
+            px, pl = inputs(on_device, i * B)
+            queue(e, px, pl, B, ids, rec3[i, 1:], on_device)
+            halo_of[i] = False
+        else:
+            e.reset_sequence()
+            px, pl = halo_inputs(on_device, i * B)
+            queue(e, px, pl, B + 1, ids_all[i * B - 1: (i + 1) * B], rec3[i], on_device)
+            halo_of[i] = True
+        return c
+
+    def settle(i, on_device, seq_first):
+        """batch i is on the host.  If its halo frame turned out not to be a kept frame (no hand in it), the previous kept
+        frame lies further back: redo the batch behind a walk back to it (sharding.run_shard's rule).  Rare, synchronous."""
+        if not halo_of.get(i) or rec3[i, 0, 1] == KEPT:
+            return
+        e = engs[i % C]
+        e.sync()
+        j = i * B - 2
+        one = np.empty((1, rec_w), np.float64)
+        while True:
+            e.reset_sequence()
+            if j < seq_first * B:
+                break
+            px, pl = inputs(on_device, j)
+            queue(e, px, pl, 1, ids_all[j: j + 1], one, on_device)
+            e.sync()
+            if one[0, 1] == KEPT:
+                break
+            j -= 1
+        px, pl = inputs(on_device, i * B)
+        queue(e, px, pl, B, ids_all[i * B: (i + 1) * B], rec3[i, 1:], on_device)
+        e.sync()
+
+    def sync_all():
+        for e in engs:
+            e.sync()
+
+    def finish(n_steps, first_step, res, fed, on_device):
         """one GPU: the resolver has been following the batches while the GPU worked (`res` has seen `fed` batches); the
         rest is fed here, after every queued batch is done and device-side errors have been raised"""
-        eng.sync()
-        res.feed(rec_np[(first_step + fed) * B: (first_step + n_steps) * B])
+        sync_all()
+        for i in range(first_step + fed, first_step + n_steps):
+            settle(i, on_device, first_step)
+            res.feed(rec3[i, 1:])
         cols = res.n_columns
         res.close()
         return cols
@@ -306,30 +379,33 @@ def run_b200(args):
 
     def pipelined_gather(on_device, first_step, n_steps):
         resolvers = [Resolver(p, keep) for _ in range(world)] if rank == 0 else None
-        gdone, LAG = [], 2
+        gdone, LAG = [], max(2, C)
 
         def feed(j):
             if rank == 0:
                 list(tpool.map(lambda r: resolvers[r].feed(ghost_np[j, r * B: (r + 1) * B]), range(world)))
 
         for i in range(n_steps):
-            step(first_step + i, on_device)
-            with torch.cuda.stream(est):
+            c = step(first_step + i, on_device, first_step)
+            with torch.cuda.stream(ests[c]):
                 e = torch.cuda.Event()
                 e.record()
             with torch.cuda.stream(gst):
                 gst.wait_event(e)                      # the batch's records are in the pinned host buffer
-                gbuf[i & 1].copy_(rec_host[(first_step + i) * B: (first_step + i + 1) * B], non_blocking=True)
+                gbuf[i & 1].copy_(rec_host[first_step + i, 1:], non_blocking=True)
                 dist.all_gather_into_tensor(gfull[i & 1], gbuf[i & 1])
                 if rank == 0:
                     ghost[i].copy_(gfull[i & 1], non_blocking=True)
                 ge = torch.cuda.Event()
                 ge.record()
             gdone.append(ge)
-            if i >= LAG:                               # two batches of slack: a rank that runs late does not stall the others
+            if i >= LAG:                               # batches of slack: a rank that runs late does not stall the others
                 gdone[i - LAG].synchronize()
                 feed(i - LAG)
-        eng.sync()
+        sync_all()
+        for i in range(n_steps):                       # every halo frame of the synthetic stream is a kept frame; say so if not
+            if halo_of.get(first_step + i) and rec3[first_step + i, 0, 1] != KEPT:
+                raise SystemExit("bench.py: batch %d starts behind a frame without a hand; run with --contexts 1" % (first_step + i))
         for j in range(max(n_steps - LAG, 0), n_steps):
             gdone[j].synchronize()
             feed(j)
@@ -341,48 +417,54 @@ def run_b200(args):
         return cols
 
     def timed(on_device, first_step, n_steps):
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        eng.reset_sequence()                # the timed block is its own sequence (the resolver starts at its first frame)
+        ev0 = torch.cuda.Event(enable_timing=True)
+        ev1 = [torch.cuda.Event(enable_timing=True) for _ in engs]
+        for e in engs:
+            e.reset_sequence()              # the timed block is its own sequence (the resolver starts at its first frame)
         barrier()
-        l0 = eng.launch_count
+        l0 = sum(e.launch_count for e in engs)
         t0 = time.perf_counter()
         with torch.cuda.stream(est):
-            ev0.record()
+            ev0.record()                    # every stream is idle here (barrier); the last stream to finish ends the region
         if world == 1:
-            # one GPU: phase 2 (host, sequential) runs one batch behind the GPU instead of after it
+            # one GPU: phase 2 (host, sequential) follows C batches behind the GPU instead of after it, so that C batches
+            # stay in flight while the resolver works
             res = Resolver(p, keep)
             done, fed = [], 0
             for i in range(n_steps):
-                step(first_step + i, on_device)
-                with torch.cuda.stream(est):
+                c = step(first_step + i, on_device, first_step)
+                with torch.cuda.stream(ests[c]):
                     e = torch.cuda.Event()
                     e.record()
                 done.append(e)
-                if i >= 1:
-                    done[i - 1].synchronize()          # batch i-1 is on the host; batch i keeps the GPU busy meanwhile
-                    res.feed(rec_np[(first_step + i - 1) * B: (first_step + i) * B])
-                    fed = i
-            cols = finish(n_steps, first_step, res, fed)
+                if i >= C:
+                    done[i - C].synchronize()          # batch i-C is on the host; the later ones keep the GPU busy meanwhile
+                    settle(first_step + i - C, on_device, first_step)
+                    res.feed(rec3[first_step + i - C, 1:])
+                    fed = i - C + 1
+            cols = finish(n_steps, first_step, res, fed, on_device)
         else:
             cols = pipelined_gather(on_device, first_step, n_steps)
-        with torch.cuda.stream(est):
-            ev1.record()
+        for c in range(C):
+            with torch.cuda.stream(ests[c]):
+                ev1[c].record()
         barrier()
         t1 = time.perf_counter()
-        ms = max(ev0.elapsed_time(ev1), 0.0)
+        ms = max(max(ev0.elapsed_time(e) for e in ev1), 0.0)
         wall = (t1 - t0) * 1e3
         t = torch.tensor([ms, wall], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t[0]), float(t[1]), eng.launch_count - l0, cols, (t0, t1)
+        return float(t[0]), float(t[1]), sum(e.launch_count for e in engs) - l0, cols, (t0, t1)
 
-    eng.reset_sequence()
+    for e in engs:
+        e.reset_sequence()
     if world > 1:
         pipelined_gather(True, 0, W)        # also brings up the NCCL communicator outside the timed region
     else:
         for i in range(W):
-            step(i, True)
-    eng.sync()
+            step(i, True, 0)
+    sync_all()
     if saved_stdout is not None:            # the warm-up has run the first collectives: the banner is out
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
@@ -391,25 +473,35 @@ def run_b200(args):
     sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if rank == 0 else None
     time.sleep(0.3 if sampler else 0.0)
     ms, wall_ms, launches, cols, (t0, t1) = timed(True, W, K)
-    stages = eng.stage_ms()
     clocks = sampler.stop(t0, t1) if sampler else None
     # the event pair brackets device work AND the host resolver between launches; wall is reported beside it
     frames = K * B * world
     value = frames / (ms * 1e-3)
     # how many filtered entities of the timed frames needed the exact O(n^2) path (radius field not NaN)
     Kent = int(p.n_entities)
-    ent = rec_np[W * B: (W + K) * B, nat.REC_HEADER: nat.REC_HEADER + nat.REC_ENTITY * Kent].reshape(-1, Kent, nat.REC_ENTITY)
+    ent = rec3[W: W + K, 1:, nat.REC_HEADER: nat.REC_HEADER + nat.REC_ENTITY * Kent].reshape(-1, Kent, nat.REC_ENTITY)
     n_filtered = int((ent[:, :, 2] >= 0).sum())
     n_exact = int(((ent[:, :, 2] >= 0) & ~np.isnan(ent[:, :, 3])).sum())
+    # stage split and the streaming kernel's own time: one more batch on one context with nothing else on the GPU
+    # (inside the timed region the stages of different batches overlap, their event pairs would count each other's work)
+    eng.reset_sequence()
+    px, pl = inputs(True, W * B)
+    queue(eng, px, pl, B, ids_all[W * B: (W + 1) * B], rec3[0, 1:], True)      # rows of a warm-up batch, no longer needed
+    eng.sync()
+    stages = eng.stage_ms()
 
     e2e = None
     if not args.no_e2e:
-        eng.reset_sequence()
-        step(0, False)
-        eng.sync()
+        for e in engs:
+            e.reset_sequence()
+        for i in range(C):
+            step(i, False, 0)
+        sync_all()
         ems, ewall, _, _, _ = timed(False, W, K)
-        e2e = {"value": frames / (ewall * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * N * (13 if lab8 else BYTES_PER_POINT),
-               "d2h_bytes_per_step": B * rec_w * 8, "host_labels": "uint8" if lab8 else "int32",
+        h2d_frames = B + (1 if C > 1 else 0)             # the halo frame travels with its batch
+        e2e = {"value": frames / (ewall * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": h2d_frames * N * (13 if lab8 else BYTES_PER_POINT),
+               "d2h_bytes_per_step": h2d_frames * rec_w * 8, "host_labels": "uint8" if lab8 else "int32",
                "timing": "wall clock around the C-ABI calls, pinned host buffers"}
 
     if rank == 0:
@@ -434,9 +526,10 @@ def run_b200(args):
                        "filtered_entities": n_filtered, "exact_path_entities": n_exact,
                        "l2": "inputs larger than L2 (one step reads %d MB)" % (alg // 2 ** 20),
                        "parallelism": ("frame-sharded x%d, records all-gathered per batch behind the GPU work" % world) if world > 1
-                       else "one GPU, host resolver one batch behind"},
+                       else "one GPU, host resolver %d batch(es) behind" % C,
+                       "contexts_per_gpu": C},
             "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": wall_ms / K, "esec_columns": cols,
-            "stages_ms_last_step": stages,
+            "stages_ms_solo_step": stages, "stages_ms_last_step": stages,
             "roofline": {"bound": "hbm", "kernel": dom + " stage of one step", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                          "traffic": (NCU_TRAFFIC_PER_FRAME[dom] * B) if (dom in NCU_TRAFFIC_PER_FRAME and N == 307200) else None,
@@ -461,7 +554,8 @@ def run_b200(args):
         if cpu:
             out["cpu_baseline"] = cpu
         print(json.dumps(out), flush=True)
-    eng.close()
+    for e in engs:
+        e.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -188,8 +188,8 @@ extern "C" int e2sec_reset_sequence(e2sec_ctx *ctx)
 {
     if (!ctx) return E2SEC_ERR_ARG;
     if (!ctx->halo_info.p) return E2SEC_OK;
+    // stream-ordered: the batches queued before it still see the old halo, the ones after it start a sequence
     CU(cudaMemsetAsync(ctx->halo_info.p, 0, 4 * sizeof(int), ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
     return E2SEC_OK;
 }
 

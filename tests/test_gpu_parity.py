@@ -566,3 +566,41 @@ def test_labels8_equals_int32(shape):
     finally:
         eng.close()
     np.testing.assert_array_equal(a, b)
+
+
+@pytest.mark.gpu
+def test_batches_with_explicit_halo_equal_one_sequence():
+    """bench.py --contexts 2: every batch is its own sequence on one of two contexts, with the frame before it in front
+    as the halo.  The records (cross-frame fields included) must equal those of one context walking the whole sequence."""
+    import numpy as np
+    from manipulationlibrary_b200 import _native as nat
+    from manipulationlibrary_b200.engine import Engine
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    s = SyntheticStream(width=320, height=240, n_objects=4, config=99, cycle=24)
+    p, keep = nat.make_params(**s.params())
+    B, nb = 6, 3
+    ids = np.arange(0, B * nb)
+    xyz, lab = s.fetch(ids)
+    one = Engine(0)
+    one.configure(p, B + 1, s.N, keep)
+    one.reset_sequence()
+    want = np.concatenate([one.process_batch(xyz[i * B:(i + 1) * B], lab[i * B:(i + 1) * B], ids[i * B:(i + 1) * B])
+                           for i in range(nb)])
+    one.close()
+    engs = [Engine(0), Engine(0)]
+    for e in engs:
+        e.configure(p, B + 1, s.N, keep)
+    got = []
+    for i in range(nb):
+        e = engs[i % 2]
+        e.reset_sequence()
+        lo = i * B - (1 if i else 0)
+        rec = e.process_batch(xyz[lo:(i + 1) * B], lab[lo:(i + 1) * B], ids[lo:(i + 1) * B])
+        if i:
+            assert int(rec[0, 1]) == (nat.FLAG_HAND_LABEL | nat.FLAG_HAND_POINTS)      # the halo frame is a kept frame
+        got.append(rec[1:] if i else rec)
+    for e in engs:
+        e.close()
+    got = np.concatenate(got)
+    assert got.shape == want.shape
+    assert np.array_equal(got.view(np.uint64), want.view(np.uint64))
