@@ -279,6 +279,10 @@ def run_b200(args):
     rec3 = rec_host.numpy()
     ids_all = np.arange(rank_first, rank_first + total_frames, dtype=np.int32)
     KEPT = float(nat.FLAG_HAND_LABEL | nat.FLAG_HAND_POINTS)
+    import threading
+    from concurrent.futures import ThreadPoolExecutor
+    follower = ThreadPoolExecutor(max_workers=1)    # phase 2 follows the GPU on its own thread, in frame order
+    locks = [threading.Lock() for _ in engs]        # reset + queue on a context is one unit (the follower may redo a batch)
     halo_of = {}                               # batch -> True when it was queued with its halo frame in front
 
     def inputs(on_device, first_frame):
@@ -309,17 +313,18 @@ def run_b200(args):
         c = i % C
         e = engs[c]
         ids = ids_all[i * B: (i + 1) * B]
-        if C == 1 or i == seq_first:
-            if C > 1:
+        with locks[c]:
+            if C == 1 or i == seq_first:
+                if C > 1:
+                    e.reset_sequence()
+                px, pl = inputs(on_device, i * B)
+                queue(e, px, pl, B, ids, rec3[i, 1:], on_device)
+                halo_of[i] = False
+            else:
                 e.reset_sequence()
-            px, pl = inputs(on_device, i * B)
-            queue(e, px, pl, B, ids, rec3[i, 1:], on_device)
-            halo_of[i] = False
-        else:
-            e.reset_sequence()
-            px, pl = halo_inputs(on_device, i * B)
-            queue(e, px, pl, B + 1, ids_all[i * B - 1: (i + 1) * B], rec3[i], on_device)
-            halo_of[i] = True
+                px, pl = halo_inputs(on_device, i * B)
+                queue(e, px, pl, B + 1, ids_all[i * B - 1: (i + 1) * B], rec3[i], on_device)
+                halo_of[i] = True
         return c
 
     def settle(i, on_device, seq_first):
@@ -328,37 +333,27 @@ def run_b200(args):
         if not halo_of.get(i) or rec3[i, 0, 1] == KEPT:
             return
         e = engs[i % C]
-        e.sync()
-        j = i * B - 2
-        one = np.empty((1, rec_w), np.float64)
-        while True:
-            e.reset_sequence()
-            if j < seq_first * B:
-                break
-            px, pl = inputs(on_device, j)
-            queue(e, px, pl, 1, ids_all[j: j + 1], one, on_device)
+        with locks[i % C]:
             e.sync()
-            if one[0, 1] == KEPT:
-                break
-            j -= 1
-        px, pl = inputs(on_device, i * B)
-        queue(e, px, pl, B, ids_all[i * B: (i + 1) * B], rec3[i, 1:], on_device)
-        e.sync()
+            j = i * B - 2
+            one = np.empty((1, rec_w), np.float64)
+            while True:
+                e.reset_sequence()
+                if j < seq_first * B:
+                    break
+                px, pl = inputs(on_device, j)
+                queue(e, px, pl, 1, ids_all[j: j + 1], one, on_device)
+                e.sync()
+                if one[0, 1] == KEPT:
+                    break
+                j -= 1
+            px, pl = inputs(on_device, i * B)
+            queue(e, px, pl, B, ids_all[i * B: (i + 1) * B], rec3[i, 1:], on_device)
+            e.sync()
 
     def sync_all():
         for e in engs:
             e.sync()
-
-    def finish(n_steps, first_step, res, fed, on_device):
-        """one GPU: the resolver has been following the batches while the GPU worked (`res` has seen `fed` batches); the
-        rest is fed here, after every queued batch is done and device-side errors have been raised"""
-        sync_all()
-        for i in range(first_step + fed, first_step + n_steps):
-            settle(i, on_device, first_step)
-            res.feed(rec3[i, 1:])
-        cols = res.n_columns
-        res.close()
-        return cols
 
     def barrier():
         if world > 1:
@@ -369,7 +364,6 @@ def run_b200(args):
     # resolves the gathered batch one step behind -- every shard is its own sequence here, so the shards' resolvers run
     # side by side (one C call each, the GIL is released).  No collective on the data path itself.
     if world > 1:
-        from concurrent.futures import ThreadPoolExecutor
         gst = torch.cuda.Stream(device=dev)
         gbuf = [torch.empty((B, rec_w), dtype=torch.float64, device=dev) for _ in range(2)]
         gfull = [torch.empty((world * B, rec_w), dtype=torch.float64, device=dev) for _ in range(2)]
@@ -379,11 +373,11 @@ def run_b200(args):
 
     def pipelined_gather(on_device, first_step, n_steps):
         resolvers = [Resolver(p, keep) for _ in range(world)] if rank == 0 else None
-        gdone, LAG = [], max(2, C)
+        futs = []
 
-        def feed(j):
-            if rank == 0:
-                list(tpool.map(lambda r: resolvers[r].feed(ghost_np[j, r * B: (r + 1) * B]), range(world)))
+        def feed(j, ge):
+            ge.synchronize()                           # the gathered batch is in rank 0's pinned buffer
+            list(tpool.map(lambda r: resolvers[r].feed(ghost_np[j, r * B: (r + 1) * B]), range(world)))
 
         for i in range(n_steps):
             c = step(first_step + i, on_device, first_step)
@@ -398,17 +392,16 @@ def run_b200(args):
                     ghost[i].copy_(gfull[i & 1], non_blocking=True)
                 ge = torch.cuda.Event()
                 ge.record()
-            gdone.append(ge)
-            if i >= LAG:                               # batches of slack: a rank that runs late does not stall the others
-                gdone[i - LAG].synchronize()
-                feed(i - LAG)
+            if rank == 0:                              # the resolvers follow on their own thread, batch by batch
+                futs.append(follower.submit(feed, i, ge))
+                if i >= 2 * C:
+                    futs[i - 2 * C].result()           # bounds how far the launches run ahead of phase 2
         sync_all()
         for i in range(n_steps):                       # every halo frame of the synthetic stream is a kept frame; say so if not
             if halo_of.get(first_step + i) and rec3[first_step + i, 0, 1] != KEPT:
                 raise SystemExit("bench.py: batch %d starts behind a frame without a hand; run with --contexts 1" % (first_step + i))
-        for j in range(max(n_steps - LAG, 0), n_steps):
-            gdone[j].synchronize()
-            feed(j)
+        for f in futs:
+            f.result()
         cols = 0
         if rank == 0:
             cols = sum(r.n_columns for r in resolvers)
@@ -427,22 +420,29 @@ def run_b200(args):
         with torch.cuda.stream(est):
             ev0.record()                    # every stream is idle here (barrier); the last stream to finish ends the region
         if world == 1:
-            # one GPU: phase 2 (host, sequential) follows C batches behind the GPU instead of after it, so that C batches
-            # stay in flight while the resolver works
+            # one GPU: phase 2 (host, sequential) follows the GPU on its own thread instead of after it, so that the launch
+            # thread keeps C batches in flight
             res = Resolver(p, keep)
-            done, fed = [], 0
+            futs = []
+
+            def follow(i, ev):
+                ev.synchronize()                       # batch i is on the host; the later ones keep the GPU busy meanwhile
+                settle(i, on_device, first_step)
+                res.feed(rec3[i, 1:])
+
             for i in range(n_steps):
                 c = step(first_step + i, on_device, first_step)
                 with torch.cuda.stream(ests[c]):
                     e = torch.cuda.Event()
                     e.record()
-                done.append(e)
-                if i >= C:
-                    done[i - C].synchronize()          # batch i-C is on the host; the later ones keep the GPU busy meanwhile
-                    settle(first_step + i - C, on_device, first_step)
-                    res.feed(rec3[first_step + i - C, 1:])
-                    fed = i - C + 1
-            cols = finish(n_steps, first_step, res, fed, on_device)
+                futs.append(follower.submit(follow, first_step + i, e))
+                if i >= 2 * C:
+                    futs[i - 2 * C].result()           # bounds how far the launches run ahead of phase 2
+            for f in futs:
+                f.result()
+            sync_all()                                 # raises device-side errors of the queued batches
+            cols = res.n_columns
+            res.close()
         else:
             cols = pipelined_gather(on_device, first_step, n_steps)
         for c in range(C):
@@ -528,7 +528,7 @@ def run_b200(args):
                        "filtered_entities": n_filtered, "exact_path_entities": n_exact,
                        "l2": "inputs larger than L2 (one step reads %d MB)" % (alg // 2 ** 20),
                        "parallelism": ("frame-sharded x%d, records all-gathered per batch behind the GPU work" % world) if world > 1
-                       else "one GPU, host resolver %d batch(es) behind" % C,
+                       else "one GPU, host resolver following on its own thread",
                        "contexts_per_gpu": C},
             "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": wall_ms / K, "esec_columns": cols,
             "stages_ms_solo_step": stages, "stages_ms_last_step": stages,
