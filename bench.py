@@ -361,7 +361,9 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     # N > 1: the records of batch i are all-gathered (NCCL, its own stream) while the GPUs work on batch i+1, and rank 0
-    # resolves the gathered batch one step behind -- every shard is its own sequence here, so the shards' resolvers run
+    # resolves the gathered batch a few steps behind ON THE LAUNCH THREAD: that wait is what keeps the ranks loosely in step
+    # (with free-running launches a rank's all-gather kernel sits on its SMs waiting for the slowest rank: 729 k instead of
+    # 766 k frames/s at 8 GPUs) -- every shard is its own sequence here, so the shards' resolvers run
     # side by side (one C call each, the GIL is released).  No collective on the data path itself.
     if world > 1:
         gst = torch.cuda.Stream(device=dev)
@@ -373,11 +375,11 @@ def run_b200(args):
 
     def pipelined_gather(on_device, first_step, n_steps):
         resolvers = [Resolver(p, keep) for _ in range(world)] if rank == 0 else None
-        futs = []
+        gdone, LAG = [], max(2, C)
 
-        def feed(j, ge):
-            ge.synchronize()                           # the gathered batch is in rank 0's pinned buffer
-            list(tpool.map(lambda r: resolvers[r].feed(ghost_np[j, r * B: (r + 1) * B]), range(world)))
+        def feed(j):
+            if rank == 0:
+                list(tpool.map(lambda r: resolvers[r].feed(ghost_np[j, r * B: (r + 1) * B]), range(world)))
 
         for i in range(n_steps):
             c = step(first_step + i, on_device, first_step)
@@ -392,16 +394,17 @@ def run_b200(args):
                     ghost[i].copy_(gfull[i & 1], non_blocking=True)
                 ge = torch.cuda.Event()
                 ge.record()
-            if rank == 0:                              # the resolvers follow on their own thread, batch by batch
-                futs.append(follower.submit(feed, i, ge))
-                if i >= 2 * C:
-                    futs[i - 2 * C].result()           # bounds how far the launches run ahead of phase 2
+            gdone.append(ge)
+            if i >= LAG:                               # batches of slack: a rank that runs late does not stall the others
+                gdone[i - LAG].synchronize()
+                feed(i - LAG)
         sync_all()
         for i in range(n_steps):                       # every halo frame of the synthetic stream is a kept frame; say so if not
             if halo_of.get(first_step + i) and rec3[first_step + i, 0, 1] != KEPT:
                 raise SystemExit("bench.py: batch %d starts behind a frame without a hand; run with --contexts 1" % (first_step + i))
-        for f in futs:
-            f.result()
+        for j in range(max(n_steps - LAG, 0), n_steps):
+            gdone[j].synchronize()
+            feed(j)
         cols = 0
         if rank == 0:
             cols = sum(r.n_columns for r in resolvers)
