@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define E2SEC_ABI_VERSION 4
+#define E2SEC_ABI_VERSION 5
 #define E2SEC_MAX_ENTITIES 64      /* len(total_unique_labels) upper bound                           */
 #define E2SEC_LABEL_LUT 4096       /* raw labels must be integers in [0, E2SEC_LABEL_LUT)            */
 
@@ -68,6 +68,7 @@ typedef struct e2sec_params {
     int32_t filter_mode;                         /* E2SEC_FILTER_*                                     */
     uint32_t filter_seed;                        /* base seed for REFERENCE_SEEDED                     */
     int32_t radius_mode;                         /* E2SEC_RADIUS_*                                     */
+    int32_t relations;                           /* 1: T/N, 2: + SSR, 3 (or 0): + DSR (:1744-1829)     */
 } e2sec_params;
 
 /* ---- records: phase-1 output, one per frame, all doubles (integers are exact in a double) --------
@@ -174,8 +175,9 @@ int e2sec_resolver_feed(e2sec_resolver *r, const double *records, int32_t n_fram
 /* Number of eSEC columns so far (0 before the first column; the reference's '-' column is implicit). */
 int32_t e2sec_resolver_columns(const e2sec_resolver *r);
 const char *e2sec_resolver_error(const e2sec_resolver *r);
-/* Copies the raw eSEC table: codes as 30 x n_cols x 6 bytes (NUL-terminated, lower/mixed case as the
- * reference writes them) and final_columns (n_cols).                                                 */
+/* Copies the raw eSEC table: codes as (10 * relations) x n_cols x 6 bytes (NUL-terminated, lower/mixed case as the
+ * reference writes them) and the frame id of every column (n_cols).  With relations 1 / 2 column 0 is the '-' column
+ * the reference's table starts with (frame id -1) unless frame 0 itself produced a column (:1753, :1778).            */
 int e2sec_resolver_table(const e2sec_resolver *r, char *codes, int32_t *final_columns);
 /* o1/o2/o3 entity indices (-1 while unassigned) and sticky absent flags (:389-427).                  */
 int e2sec_resolver_state(const e2sec_resolver *r, int32_t labels[3], int32_t absent[3]);
@@ -183,6 +185,26 @@ int e2sec_resolver_state(const e2sec_resolver *r, int32_t labels[3], int32_t abs
  * the H,G / 3,G rows, removes repeated columns; returns the new column count, thins final_columns.   */
 int32_t e2sec_esec_to_e2sec(const char *codes, int32_t rows, int32_t n_cols, int32_t relations,
                             char *out_codes, int32_t *final_columns, int32_t *n_final);
+
+/* _fillTN_absent (:363-487), _fillSSR_8 (:636-1061) and _fillDSR_new_2 (:1064-1353) on explicit inputs -- the
+ * reference's own seam for the relation rows (the resolver and the device classifier run the same code, csrc/relations.h).
+ * Slots of cur / prev follow previous_array (:1799): 0 hand, 1 ground, 2..4 o1..o3.  defined = 0 means the Python variable
+ * is None.  center = what the DSR rows read: the cloud mean for the hand, the AABB centre for objects and ground.
+ * min_distance[r] = np.min(a.compute_point_cloud_distance(b)) of row r's pair in the order (H,1) (H,2) (H,3) (H,G) (1,2)
+ * (1,3) (1,G) (2,3) (2,G) (3,G) (:373-383); ignored where a cloud is None or empty.  absent = absent_o1..3 on entry;
+ * absent_out (may be NULL) receives them after the call (sticky flags, :394-396).
+ * codes: 10 * relations entries of 6 bytes, NUL-terminated, spelled as the reference writes them.               */
+typedef struct e2sec_relation_entity {
+    int32_t defined, n_points;
+    double aabb_min[3], aabb_max[3], center[3];
+} e2sec_relation_entity;
+typedef struct e2sec_relation_input {
+    e2sec_relation_entity cur[5], prev[5];
+    double min_distance[10];
+    double thresh;
+    int32_t absent[3];
+} e2sec_relation_input;
+int e2sec_relation_rows(const e2sec_relation_input *in, int32_t relations, char *codes, int32_t absent_out[3]);
 
 /* ---- the consumer of the tables: eSEC_analyser.getDissimilarityMatrix (eSEC_analyser.py:782-841, with
  * _make_triple :866-889 and _compare_triple_matrics :915-944) and similarity_manipulations (:843-864).

@@ -8,6 +8,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libe2sec.so")
 
+ABI_VERSION = 5            # E2SEC_ABI_VERSION of include/e2sec.h this binding was written against
 MAX_ENTITIES = 64
 REC_HEADER = 4
 REC_ENTITY = 16
@@ -27,7 +28,8 @@ class Params(C.Structure):
                 ("n_replace", C.c_int32), ("replace_old", C.c_int32 * 16), ("replace_new", C.c_int32 * 16),
                 ("thresh", C.c_double), ("translation", C.c_double * 16), ("roll", C.c_double * 16),
                 ("n_ground", C.c_int32), ("ground_xyz", C.POINTER(C.c_double)),
-                ("filter_mode", C.c_int32), ("filter_seed", C.c_uint32), ("radius_mode", C.c_int32)]
+                ("filter_mode", C.c_int32), ("filter_seed", C.c_uint32), ("radius_mode", C.c_int32),
+                ("relations", C.c_int32)]
 
 
 class E2SecError(RuntimeError):
@@ -72,6 +74,7 @@ def _load():
         "e2sec_resolver_table": (C.c_int, [vp, vp, vp]),
         "e2sec_resolver_state": (C.c_int, [vp, vp, vp]),
         "e2sec_esec_to_e2sec": (i32, [vp, i32, i32, i32, vp, vp, vp]),
+        "e2sec_relation_rows": (C.c_int, [vp, i32, vp, vp]),
         "e2sec_read_pcd_xyz": (C.c_int, [C.c_char_p, vp, i64, vp, vp]),
         "e2sec_read_labels": (C.c_int, [C.c_char_p, vp, i64, vp, vp]),
     }
@@ -83,6 +86,9 @@ def _load():
 
 
 lib, EXPORTS = _load()
+if lib.e2sec_abi_version() != ABI_VERSION:
+    raise ImportError("libe2sec.so has ABI %d, this binding needs %d: rebuild with `python -m manipulationlibrary_b200.build --force`"
+                      % (lib.e2sec_abi_version(), ABI_VERSION))
 
 
 def ptr(a):
@@ -90,7 +96,7 @@ def ptr(a):
 
 
 def make_params(total_unique_labels, hand_label, ground_label, support_hand, thresh, translation, roll, ground,
-                replace=False, old=(), new=(), filter_mode="closure", filter_seed=0, radius_mode="bounded"):
+                replace=False, old=(), new=(), filter_mode="closure", filter_seed=0, radius_mode="bounded", relations=3):
     """-> (Params, keepalive). Labels must be integer valued, as the MANIAC label images are."""
     tul = np.asarray(total_unique_labels, np.float64)
     if len(tul) > MAX_ENTITIES:
@@ -120,7 +126,48 @@ def make_params(total_unique_labels, hand_label, ground_label, support_hand, thr
     p.filter_mode = FILTER_MODES[filter_mode] if isinstance(filter_mode, str) else int(filter_mode)
     p.filter_seed = int(filter_seed) & 0xFFFFFFFF
     p.radius_mode = RADIUS_MODES[radius_mode] if isinstance(radius_mode, str) else int(radius_mode)
+    if int(relations) not in (1, 2, 3):
+        raise ValueError("relations must be 1, 2 or 3")
+    p.relations = int(relations)
     return p, g
+
+
+class RelationEntity(C.Structure):
+    _fields_ = [("defined", C.c_int32), ("n_points", C.c_int32), ("aabb_min", C.c_double * 3), ("aabb_max", C.c_double * 3),
+                ("center", C.c_double * 3)]
+
+
+class RelationInput(C.Structure):
+    _fields_ = [("cur", RelationEntity * 5), ("prev", RelationEntity * 5), ("min_distance", C.c_double * 10),
+                ("thresh", C.c_double), ("absent", C.c_int32 * 3)]
+
+
+def relation_rows(cur, prev, min_distance, thresh, absent, relations=3):
+    """_fillTN_absent / _fillSSR_8 / _fillDSR_new_2 (manipulation_analyser.py:363-1353) through e2sec_relation_rows.
+    cur / prev: 5 entries [hand, ground, o1, o2, o3], each None or dict(n, lo, hi, center).  -> (codes, absent_out)."""
+    inp = RelationInput()
+    for dst, src in ((inp.cur, cur), (inp.prev, prev)):
+        for s in range(5):
+            e = src[s] if src is not None else None
+            dst[s].defined = 0 if e is None else 1
+            if e is None:
+                continue
+            dst[s].n_points = int(e["n"])
+            for k in range(3):
+                dst[s].aabb_min[k] = float(e["lo"][k]) if e["n"] else 0.0
+                dst[s].aabb_max[k] = float(e["hi"][k]) if e["n"] else 0.0
+                dst[s].center[k] = float(e["center"][k]) if e["n"] else 0.0
+    for r in range(10):
+        inp.min_distance[r] = float(min_distance[r])
+    inp.thresh = float(thresh)
+    for k in range(3):
+        inp.absent[k] = int(bool(absent[k]))
+    codes = np.zeros((10 * relations, 6), np.uint8)
+    out = np.zeros(3, np.int32)
+    rc = lib.e2sec_relation_rows(C.byref(inp), int(relations), ptr(codes), ptr(out))
+    if rc != 0:
+        raise E2SecError("e2sec_relation_rows failed (%d)" % rc)
+    return [bytes(row).split(b"\0")[0].decode() for row in codes], out.astype(bool).tolist()
 
 
 def record_doubles(K):

@@ -15,98 +15,42 @@
 #include <vector>
 
 #include "../../include/e2sec.h"
-
-namespace {
-
-const double kCenterDistance = 0.005107632747118286;   // :1121
-const double kStableDist = 0.0045302034127268085;      // :1122
-
-struct Ent {              // what the relation rows read of one cloud
-    bool defined = false; // false = the Python variable is None
-    int n = 0;            // len(points)
-    double lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
-    double center[3] = {0, 0, 0};   // hand: cloud mean; objects and ground: AABB centre (:1173-1353)
-    int index = -1;       // entity index in total_unique_labels (K = ground)
-};
-
-struct Code {
-    char c[6];
-};
-
-Code mk(const char *s)
-{
-    Code c;
-    memset(c.c, 0, 6);
-    strncpy(c.c, s, 5);
-    return c;
-}
-bool same(const Code &a, const char *s) { return strcmp(a.c, s) == 0; }
-
-struct Box {   // SSR axis naming (:660-675): x = data[:,0], z = data[:,1], y = data[:,2]
-    double min_x, max_x, min_z, max_z, min_y, max_y;
-};
-Box box_of(const Ent &e) { return Box{e.lo[0], e.hi[0], e.lo[1], e.hi[1], e.lo[2], e.hi[2]}; }
-
-bool ov_x(const Box &a, const Box &b) { return a.min_x < b.max_x && a.max_x > b.min_x; }
-bool ov_y(const Box &a, const Box &b) { return a.min_y < b.max_y && a.max_y > b.min_y; }
-bool ov_z(const Box &a, const Box &b) { return a.min_z < b.max_z && a.max_z > b.min_z; }
-
-bool around(const Box &a, const Box &b)   // _R or _L or _F or _Ba (:491-550)
-{
-    const bool R = a.max_x > b.max_x && ov_y(a, b) && ov_z(a, b);
-    const bool L = a.min_x < b.min_x && ov_y(a, b) && ov_z(a, b);
-    const bool F = a.max_z > b.max_z && (a.min_x < b.max_x && b.min_x < a.max_x) && ov_y(a, b);
-    const bool Ba = a.min_z < b.min_z && (a.min_x < b.max_x && b.min_x < a.max_x) && ov_y(a, b);
-    return R || L || F || Ba;
-}
-
-Code tail(const Box &a, const Box &b, bool touching)   // the elif chain every SSR row ends with (:729-745)
-{
-    if (around(a, b)) return mk(touching ? "HArT" : "HAr");
-    if (a.max_y > b.max_y || a.min_y < b.min_y) return mk(touching ? "VArT" : "VAr");   // _Ab or _Be (:570-599)
-    return mk("O");
-}
-
-bool between(const Box &m, const Box &a, const Box &b)   // one disjunct of _Bw (:615-633)
-{
-    return m.min_x >= std::fmin(a.max_x, b.max_x) && m.max_x <= std::fmax(a.min_x, b.min_x) &&
-           m.min_y >= std::fmax(a.min_y, b.min_y) && m.max_y <= std::fmin(a.max_y, b.max_y) &&
-           m.min_z >= std::fmax(a.min_z, b.min_z) && m.max_z <= std::fmin(a.max_z, b.max_z);
-}
-
-double dist3(const double *p, const double *q)   // _distance :200-209
-{
-    return std::sqrt((p[0] - q[0]) * (p[0] - q[0]) + (p[1] - q[1]) * (p[1] - q[1]) + (p[2] - q[2]) * (p[2] - q[2]));
-}
-
-}   // namespace
+#include "relations.h"
 
 struct e2sec_resolver {
     e2sec_params p;
     int K = 0, hand_idx = -1, ground_idx = -1, support_idx = -1;
+    int relations = 3;
     size_t rec = 0;
-    Ent ground;
+    RelEnt ground;
     // globals :32-59
-    Ent o[3];
+    RelEnt o[3];
+    int oindex[3] = {-1, -1, -1};   // entity index bound to o1..o3 (o1_label etc. index total_unique_labels)
     int count[3] = {0, 0, 0};
-    int olabel[3] = {0, 0, 0};
-    bool absent[3] = {false, false, false};
+    int absent[3] = {0, 0, 0};
     int internal_count = 0;
     bool have_prev = false;
-    Ent prev[5];                 // previous_array = [hand, ground, o1, o2, o3] (:1799, :1822)
+    RelEnt prev[5];              // previous_array = [hand, ground, o1, o2, o3] (:1799, :1822)
     int prev_frame_id = -1;      // frame id of the previous kept frame
-    std::vector<double> prev_rec;   // its record (for the stale o1/o2/o3 clouds of the selection loop)
-    std::vector<Code> table;     // 30 codes per column, column-major
-    std::vector<int> final_columns;
+    std::vector<uint8_t> table;  // rows codes per column, column-major (RelCode)
+    std::vector<int> final_columns;   // frame id of every column (the reference only fills it for relations == 3)
     std::string err;
 };
 
-static Ent ent_from_record(const double *rec, int e, bool is_hand)
+static int rows_of(int relations) { return 10 * relations; }
+
+static RelEnt undefined_ent()
+{
+    RelEnt x;
+    memset(&x, 0, sizeof(x));
+    return x;
+}
+
+static RelEnt ent_from_record(const double *rec, int e, bool is_hand)
 {
     const double *r = rec + E2SEC_REC_HEADER + E2SEC_REC_ENTITY * e;
-    Ent x;
-    x.defined = true;
-    x.index = e;
+    RelEnt x;
+    x.defined = 1;
     x.n = (int)r[1];
     for (int k = 0; k < 3; ++k) {
         x.lo[k] = r[7 + k];
@@ -121,10 +65,12 @@ extern "C" int e2sec_resolver_create(const e2sec_params *p, e2sec_resolver **out
     if (!p || !out) return E2SEC_ERR_ARG;
     *out = nullptr;
     if (p->n_entities < 2 || p->n_entities > E2SEC_MAX_ENTITIES) return E2SEC_ERR_ARG;
+    if (p->relations != 0 && (p->relations < 1 || p->relations > 3)) return E2SEC_ERR_ARG;
     e2sec_resolver *r = new e2sec_resolver();
     r->p = *p;
     r->p.ground_xyz = nullptr;
     r->K = p->n_entities;
+    r->relations = p->relations ? p->relations : 3;
     r->rec = e2sec_record_doubles(r->K);
     for (int e = 0; e < r->K; ++e) {
         if (p->entity_label[e] == p->hand_label) r->hand_idx = e;
@@ -135,9 +81,11 @@ extern "C" int e2sec_resolver_create(const e2sec_params *p, e2sec_resolver **out
         delete r;
         return E2SEC_ERR_ARG;
     }
-    Ent &g = r->ground;
-    g.defined = true;
-    g.index = r->K;
+    for (auto &x : r->o) x = undefined_ent();
+    for (auto &x : r->prev) x = undefined_ent();
+    RelEnt &g = r->ground;
+    g = undefined_ent();
+    g.defined = 1;
     g.n = p->n_ground;
     for (int i = 0; i < p->n_ground; ++i)
         for (int a = 0; a < 3; ++a) {
@@ -146,6 +94,10 @@ extern "C" int e2sec_resolver_create(const e2sec_params *p, e2sec_resolver **out
             if (i == 0 || v > g.hi[a]) g.hi[a] = v;
         }
     for (int a = 0; a < 3; ++a) g.center[a] = (g.lo[a] + g.hi[a]) * 0.5;
+    if (r->relations < 3) {                                  // the '-' column the table starts with (:2252-2260) stays column 0
+        r->table.assign(rows_of(r->relations), (uint8_t)REL_DASH);
+        r->final_columns.push_back(-1);
+    }
     *out = r;
     return E2SEC_OK;
 }
@@ -157,7 +109,6 @@ namespace {
 struct FrameView {
     const e2sec_resolver *R;
     const double *rec;        // this frame
-    const double *prev_rec;   // previous kept frame (may be null)
     double pair(int a, int b) const   // in-frame distance, b may be K (ground)
     {
         const int W = R->K + 1;
@@ -172,131 +123,7 @@ struct FrameView {
     }
 };
 
-// distance between the cloud currently bound to an o-variable and the frame's entity i.
-// `fresh` = the variable was (re)bound during this frame's loop, so it is this frame's cloud; otherwise it is
-// still the cloud of the previous kept frame (:1669-1675 rebinds only after the loop).
-double dist_to(const FrameView &v, const Ent &o, bool fresh, int i)
-{
-    if (o.n == 0) return INFINITY;   // compute_point_cloud_distance on an empty cloud: np.min raises in the reference
-    return fresh ? v.pair(o.index, i) : v.cross(o.index, i);
-}
-
 }   // namespace
-
-static void fill_tn(e2sec_resolver *R, const FrameView &v, const Ent &H, const Ent *o, Code *out)
-{
-    const double th = R->p.thresh;
-    for (int k = 0; k < 3; ++k) {                         // rows 0-2 (:389-427)
-        if (!o[k].defined) out[k] = mk("U");
-        else if (o[k].n == 0 || R->absent[k]) { out[k] = mk("A"); R->absent[k] = true; }
-        else out[k] = mk(v.pair(H.index, o[k].index) < th ? "T" : "N");
-    }
-    out[3] = mk(v.pair(H.index, R->K) < th ? "T" : "N");   // row 3 (:429-433)
-    const int pr[3][3] = {{4, 0, 1}, {5, 0, 2}, {7, 1, 2}};
-    for (auto &q : pr) {                                   // rows 4,5,7 (:435-451, :462-469)
-        const Ent &a = o[q[1]], &b = o[q[2]];
-        if (!a.defined || !b.defined) out[q[0]] = mk("U");
-        else if (a.n == 0 || b.n == 0 || R->absent[q[1]] || R->absent[q[2]]) out[q[0]] = mk("A");
-        else out[q[0]] = mk(v.pair(a.index, b.index) < th ? "T" : "N");
-    }
-    const int gr[3][2] = {{6, 0}, {8, 1}, {9, 2}};
-    for (auto &q : gr) {                                   // rows 6,8,9 (:453-460, :471-487)
-        const Ent &a = o[q[1]];
-        if (!a.defined) out[q[0]] = mk("U");
-        else if (a.n == 0 || R->absent[q[1]]) out[q[0]] = mk("A");
-        else out[q[0]] = mk(v.pair(a.index, R->K) < th ? "T" : "N");
-    }
-}
-
-static void fill_ssr(const e2sec_resolver *R, const Ent &Hh, const Ent *o, const Code *tn, Code *out)
-{
-    const Box H = box_of(Hh), G = box_of(R->ground);
-    Box B[3];
-    bool have[3];
-    for (int k = 0; k < 3; ++k) {
-        have[k] = o[k].defined && !same(tn[k], "A");
-        if (o[k].defined) B[k] = box_of(o[k]);
-    }
-    const bool all_there = o[0].defined && o[1].defined && o[2].defined;
-    for (int k = 0; k < 3; ++k) {                          // rows 10-12 (:706-812)
-        if (!o[k].defined) out[k] = mk("U");
-        else if (same(tn[k], "A")) out[k] = mk("A");
-        else {
-            const Box &b = B[k];
-            const bool sa = (b.min_z < H.min_z && b.max_z > H.max_z) &&
-                            ((b.max_x < H.min_x && b.max_x > H.max_x) || (b.min_x < H.min_x && b.min_x > H.max_x) ||
-                             (b.min_x > H.min_x && b.max_x < H.max_x)) &&
-                            (H.min_y < b.max_y && b.max_y <= H.max_y);
-            out[k] = sa ? mk("Sa") : tail(H, b, same(tn[k], "T"));
-        }
-    }
-    out[3] = tail(H, G, same(tn[3], "T"));                 // row 13 (:814-842)
-    const bool bw_gate = all_there && !same(tn[0], "A") && !same(tn[1], "A") && !same(tn[2], "A");
-    const int pr[3][4] = {{4, 0, 1, 12}, {5, 0, 2, 13}, {7, 1, 2, 23}};
-    for (auto &q : pr) {                                   // rows 14,15,17 (:844-1000)
-        const int r = q[0], j = q[1], k = q[2];
-        if (!o[j].defined || !o[k].defined) out[r] = mk("U");
-        else if (same(tn[r], "A")) out[r] = mk("A");
-        else {
-            const Box &a = B[j], &b = B[k];
-            const bool in = (b.min_z < a.min_z && b.max_z > a.max_z) &&
-                            ((a.max_x > b.min_x && a.max_x < b.max_x) || (a.min_x > b.min_x && a.min_x < b.max_x) ||
-                             (a.min_x < b.min_x && a.max_x > b.max_x)) &&
-                            (a.min_y < b.max_y && b.max_y <= a.max_y);
-            const bool sa = (a.min_z < b.min_z && a.max_z > b.max_z) &&
-                            ((a.max_x < b.min_x && a.max_x > b.max_x) || (a.min_x < b.min_x && a.min_x > b.max_x) ||
-                             (a.min_x > b.min_x && a.max_x < b.max_x)) &&
-                            (b.min_y < a.max_y && a.max_y <= b.max_y);
-            out[r] = in ? mk("In") : sa ? mk("Sa") : tail(a, b, same(tn[r], "T"));
-        }
-        if (bw_gate) {                                     // :884-888, :925-929, :994-998
-            const bool B1 = between(B[0], B[1], B[2]), B2 = between(B[1], B[0], B[2]), B3 = between(B[2], B[0], B[1]);
-            // Python's `x == k and A or B` precedence inside _Bw (:621-633): row 17 loses the B1 disjunct
-            const bool bw = (q[3] == 23) ? (B2 || B3) : (B1 || B2 || B3);
-            if (bw) out[r] = mk("Bw");
-        }
-    }
-    const int gr[3][2] = {{6, 0}, {8, 1}, {9, 2}};
-    for (auto &q : gr) {                                   // rows 16,18,19
-        if (!o[q[1]].defined) out[q[0]] = mk("U");
-        else if (same(tn[q[0]], "A")) out[q[0]] = mk("A");
-        else out[q[0]] = tail(B[q[1]], G, same(tn[q[0]], "T"));
-    }
-    (void)have;
-}
-
-static void fill_dsr(const e2sec_resolver *R, const Ent *cur /*H,G,1,2,3*/, const Ent *prev, const Code *tn, Code *out)
-{
-    // entity slots: 0 = H, 1 = G, 2..4 = o1..o3 (previous_array order, :1799)
-    const int rows[10][2] = {{0, 2}, {0, 3}, {0, 4}, {0, 1}, {2, 3}, {2, 4}, {2, 1}, {3, 4}, {3, 1}, {4, 1}};
-    for (int r = 0; r < 10; ++r) {
-        const int a = rows[r][0], b = rows[r][1];
-        bool undef = false;
-        for (int s : {a, b})
-            if (s >= 2 && (!cur[s].defined || !prev[s].defined)) undef = true;
-        if (undef) { out[r] = mk("U"); continue; }
-        if (same(tn[r], "A")) { out[r] = mk("A"); continue; }
-        if (same(tn[r], "T")) {
-            const bool moved = dist3(cur[a].center, prev[a].center) > kCenterDistance ||
-                               dist3(cur[b].center, prev[b].center) > kCenterDistance;
-            out[r] = mk(moved ? "MT" : "HT");
-            continue;
-        }
-        double d, pd;
-        if (b == 1) {        // ground rows use data axis 2 only (:1233, :1291, :1330, :1347)
-            d = std::fabs(cur[a].center[2] - cur[1].center[2]);
-            pd = std::fabs(prev[a].center[2] - prev[1].center[2]);
-        } else {
-            d = dist3(cur[a].center, cur[b].center);
-            pd = dist3(prev[a].center, prev[b].center);
-        }
-        if (same(tn[r], "N") && std::fabs(d - pd) < kStableDist) out[r] = mk("S");
-        else if (d > pd) out[r] = mk("MA");
-        else if (d < pd) out[r] = mk("GC");
-        else out[r] = mk("Q");
-    }
-    (void)R;
-}
 
 // one call of _process (:1355) on one record
 static int process_record(e2sec_resolver *R, const double *rec)
@@ -315,63 +142,82 @@ static int process_record(e2sec_resolver *R, const double *rec)
                  " (feed frames in order; a shard must start with its halo frame)";
         return E2SEC_ERR_STATE;
     }
-    FrameView v{R, rec, R->prev_rec.empty() ? nullptr : R->prev_rec.data()};
+    FrameView v{R, rec};
     const double th = R->p.thresh;
-    const Ent hand = ent_from_record(rec, R->hand_idx, true);
+    const RelEnt hand = ent_from_record(rec, R->hand_idx, true);
     bool fresh[3] = {false, false, false};
     // ---- selection :1562-1658 ---------------------------------------------------------------------
+    // distance between the cloud currently bound to o_k and the frame's entity i: o_k is this frame's cloud when it was
+    // bound during this loop, otherwise still the cloud of the previous kept frame (:1669-1675 rebinds after the loop).
+    // np.min over an empty distance array raises in the reference; here an empty stale cloud is "far" (deviations)
+    auto near_o = [&](int k, int i) {
+        if (R->o[k].n == 0) return false;
+        return (fresh[k] ? v.pair(R->oindex[k], i) : v.cross(R->oindex[k], i)) < th;
+    };
     for (int i = 0; i < K; ++i) {
         if (i == R->hand_idx || i == R->ground_idx || i <= 0) continue;
         if (R->support_idx >= 0 && i == R->support_idx) continue;
-        const Ent ci = ent_from_record(rec, i, false);
+        const RelEnt ci = ent_from_record(rec, i, false);
         if (ci.n == 0) continue;
         auto near_hand = [&]() { return v.pair(R->hand_idx, i) < th; };
-        auto near_o = [&](int k) { return dist_to(v, R->o[k], fresh[k], i) < th; };
-        auto take = [&](int k) { R->olabel[k] = i; R->count[k] = 1; R->o[k] = ci; fresh[k] = true; };
+        auto take = [&](int k) { R->oindex[k] = i; R->count[k] = 1; R->o[k] = ci; fresh[k] = true; };
         if (R->count[0] == 0 && near_hand()) take(0);
-        else if (R->o[0].defined && R->count[1] == 0 && i != R->olabel[0]) {
-            if (near_hand() || near_o(0)) take(1);
+        else if (R->o[0].defined && R->count[1] == 0 && i != R->oindex[0]) {
+            if (near_hand() || near_o(0, i)) take(1);
         } else if (R->support_idx >= 0) {
-            if (R->o[1].defined && R->count[2] == 0 && i != R->olabel[0] && i != R->olabel[1])
-                if (near_hand() || near_o(0) || near_o(1)) take(2);
-        } else if (R->o[1].defined && R->count[2] == 0 && i != R->olabel[0] && i != R->olabel[1]) {
+            if (R->o[1].defined && R->count[2] == 0 && i != R->oindex[0] && i != R->oindex[1])
+                if (near_hand() || near_o(0, i) || near_o(1, i)) take(2);
+        } else if (R->o[1].defined && R->count[2] == 0 && i != R->oindex[0] && i != R->oindex[1]) {
             const int n1 = R->o[0].n, n2 = R->o[1].n;
             bool ok = false;
-            if (n2 > 0 && n1 > 0) ok = near_hand() || near_o(0) || near_o(1);
-            else if (n2 > 0 && n1 == 0) ok = near_hand() || near_o(1);
-            else if (n1 > 0 && n2 == 0) ok = near_hand() || near_o(0);
+            if (n2 > 0 && n1 > 0) ok = near_hand() || near_o(0, i) || near_o(1, i);
+            else if (n2 > 0 && n1 == 0) ok = near_hand() || near_o(1, i);
+            else if (n1 > 0 && n2 == 0) ok = near_hand() || near_o(0, i);
             if (ok) take(2);
         }
     }
     for (int k = 0; k < 3; ++k)                              // icp == False :1669-1675
-        if (R->count[k] == 1) R->o[k] = ent_from_record(rec, R->olabel[k], false);
-    const Ent cur[5] = {hand, R->ground, R->o[0], R->o[1], R->o[2]};
+        if (R->count[k] == 1) R->o[k] = ent_from_record(rec, R->oindex[k], false);
+    const RelEnt cur[5] = {hand, R->ground, R->o[0], R->o[1], R->o[2]};
     auto remember = [&]() {
         for (int s = 0; s < 5; ++s) R->prev[s] = cur[s];
         R->have_prev = true;
         R->prev_frame_id = frame;
-        R->prev_rec.assign(rec, rec + R->rec);
     };
-    if (R->internal_count == 0) {                            // :1798-1801 the first kept frame only primes
+    const int rows = rows_of(R->relations);
+    if (R->relations == 3 && R->internal_count == 0) {       // :1798-1801 the first kept frame only primes
         remember();
         R->internal_count = 1;
         return E2SEC_OK;
     }
-    Code add[30];
-    fill_tn(R, v, hand, R->o, add);
-    fill_ssr(R, hand, R->o, add, add + 10);
-    fill_dsr(R, cur, R->prev, add, add + 20);
-    remember();                                              // :1822
-    bool emit = true;
-    if (R->internal_count == 1) R->internal_count = 2;       // :1826-1829
-    else {
-        const Code *last = R->table.data() + R->table.size() - 30;
-        emit = false;
-        for (int r = 0; r < 30; ++r)
-            if (strcmp(last[r].c, add[r].c) != 0) { emit = true; break; }   // :2001-2002
+    // np.min(a.compute_point_cloud_distance(b)) of the ten row pairs (entity index K = ground)
+    double d[10];
+    {
+        const int slot_idx[5] = {R->hand_idx, K, R->oindex[0], R->oindex[1], R->oindex[2]};
+        const int pairs[10][2] = REL_ROW_PAIRS;
+        for (int r = 0; r < 10; ++r) {
+            const int a = slot_idx[pairs[r][0]], b = slot_idx[pairs[r][1]];
+            const bool ok = cur[pairs[r][0]].defined && cur[pairs[r][1]].defined && a >= 0 && b >= 0;
+            d[r] = ok ? v.pair(a, b) : INFINITY;
+        }
     }
-    if (emit) {
-        R->table.insert(R->table.end(), add, add + 30);
+    uint8_t add[30];
+    rel_fill_column(cur, R->prev, d, th, R->relations, R->absent, add);
+    remember();                                              // :1822 (relations 1 / 2 keep no previous_array; harmless)
+    bool emit = true, replace_first = false;
+    if (R->relations == 3) {
+        if (R->internal_count == 1) R->internal_count = 2;   // :1826-1829
+        else emit = memcmp(R->table.data() + R->table.size() - rows, add, rows) != 0;   // :2001-2002
+    } else {
+        // :1744-1794: `if frame == 0` the '-' table is replaced by the column; otherwise compare with the last column
+        if (frame == 0) replace_first = true;
+        else emit = memcmp(R->table.data() + R->table.size() - rows, add, rows) != 0;
+    }
+    if (replace_first) {
+        R->table.assign(add, add + rows);
+        R->final_columns.assign(1, frame);
+    } else if (emit) {
+        R->table.insert(R->table.end(), add, add + rows);
         R->final_columns.push_back(frame);
     }
     return E2SEC_OK;
@@ -394,10 +240,14 @@ extern "C" const char *e2sec_resolver_error(const e2sec_resolver *r) { return r 
 extern "C" int e2sec_resolver_table(const e2sec_resolver *r, char *codes, int32_t *final_columns)
 {
     if (!r) return E2SEC_ERR_ARG;
-    const int n = (int)r->final_columns.size();
+    const int n = (int)r->final_columns.size(), rows = rows_of(r->relations);
     if (codes)
         for (int c = 0; c < n; ++c)
-            for (int row = 0; row < 30; ++row) memcpy(codes + ((size_t)row * n + c) * 6, r->table[(size_t)c * 30 + row].c, 6);
+            for (int row = 0; row < rows; ++row) {
+                char *dst = codes + ((size_t)row * n + c) * 6;
+                memset(dst, 0, 6);
+                strncpy(dst, rel_code_name(r->table[(size_t)c * rows + row]), 5);
+            }
     if (final_columns)
         for (int c = 0; c < n; ++c) final_columns[c] = r->final_columns[c];
     return E2SEC_OK;
@@ -407,9 +257,34 @@ extern "C" int e2sec_resolver_state(const e2sec_resolver *r, int32_t labels[3], 
 {
     if (!r) return E2SEC_ERR_ARG;
     for (int k = 0; k < 3; ++k) {
-        if (labels) labels[k] = r->count[k] ? r->olabel[k] : -1;
+        if (labels) labels[k] = r->count[k] ? r->oindex[k] : -1;
         if (absent) absent[k] = r->absent[k] ? 1 : 0;
     }
+    return E2SEC_OK;
+}
+
+// _fillTN_absent / _fillSSR_8 / _fillDSR_new_2 on explicit inputs: the reference's own seam (include/e2sec.h)
+extern "C" int e2sec_relation_rows(const e2sec_relation_input *in, int32_t relations, char *codes, int32_t absent_out[3])
+{
+    if (!in || !codes || relations < 1 || relations > 3) return E2SEC_ERR_ARG;
+    RelEnt cur[5], prev[5];
+    for (int s = 0; s < 5; ++s) {
+        const e2sec_relation_entity *src[2] = {&in->cur[s], &in->prev[s]};
+        RelEnt *dst[2] = {&cur[s], &prev[s]};
+        for (int w = 0; w < 2; ++w) {
+            dst[w]->defined = src[w]->defined;
+            dst[w]->n = src[w]->n_points;
+            for (int k = 0; k < 3; ++k) { dst[w]->lo[k] = src[w]->aabb_min[k]; dst[w]->hi[k] = src[w]->aabb_max[k]; dst[w]->center[k] = src[w]->center[k]; }
+        }
+    }
+    int absent[3] = {in->absent[0], in->absent[1], in->absent[2]};
+    uint8_t out[30];
+    rel_fill_column(cur, prev, in->min_distance, in->thresh, relations, absent, out);
+    for (int r = 0; r < 10 * relations; ++r) {
+        memset(codes + 6 * r, 0, 6);
+        strncpy(codes + 6 * r, rel_code_name(out[r]), 5);
+    }
+    if (absent_out) for (int k = 0; k < 3; ++k) absent_out[k] = absent[k];
     return E2SEC_OK;
 }
 

@@ -196,6 +196,7 @@ class Resolver:
             raise E2SecError("e2sec_resolver_create failed (%d)" % rc)
         self._h = h
         self.K = int(params.n_entities)
+        self.rows = 10 * (int(params.relations) or 3)
 
     def close(self):
         if self._h:
@@ -219,13 +220,13 @@ class Resolver:
         return int(lib.e2sec_resolver_columns(self._h))
 
     def table(self):
-        """-> (codes (30, n) 'S5' array as the reference's chararray, final_columns list)."""
-        n = self.n_columns
-        codes = np.zeros((30, max(n, 1), 6), np.uint8)
+        """-> (codes (10 * relations, n) 'S5' array as the reference's chararray, frame id of every column)."""
+        n, rows = self.n_columns, self.rows
+        codes = np.zeros((rows, max(n, 1), 6), np.uint8)
         fc = np.zeros(max(n, 1), np.int32)
         if n:
             lib.e2sec_resolver_table(self._h, ptr(codes), ptr(fc))
-        arr = codes[:, :n].reshape(30, n, 6).view("S6").reshape(30, n).astype("S5")
+        arr = codes[:, :n].reshape(rows, n, 6).view("S6").reshape(rows, n).astype("S5")
         return arr, fc[:n].tolist()
 
     def state(self):

@@ -566,9 +566,24 @@ class E2SecOracle:
         for k in "123":                                                      # icp == False :1669-1675
             if cnt[k] == 1:
                 o[k] = ents[lab[k]]
-        if self.relations != 3:
-            raise NotImplementedError("oracle restates relations == 3 (the notebook's setting)")
         ent = {"H": hand, "G": self.ground, "1": o["1"], "2": o["2"], "3": o["3"]}
+        if self.relations != 3:
+            # relations 1 / 2 (:1744-1794): no priming frame, no previous_array; the '-' column the table was created
+            # with (:2252-2260) is replaced only when file index 0 itself yields a column, final_columns is never filled
+            pts = {k: (None if v is None else v["pts"]) for k, v in ent.items()}
+            rows = fill_tn(ent, self.absent, self.thresh, lambda a, b: md(pts[a], pts[b]))
+            if self.relations == 2:
+                rows = rows + fill_ssr(ent, rows)
+            add = np.array(rows, dtype="U5").reshape(-1, 1)
+            if self.table is None:
+                self.table = np.full((10 * self.relations, 1), "-", dtype="U5")
+            if frame == 0:
+                self.table = add
+            elif np.array_equal(add[:, 0], self.table[:, -1]):
+                return False
+            else:
+                self.table = np.column_stack((self.table, add))
+            return True
         if self.internal_count == 0:                                         # :1798-1801
             self.previous = dict(ent)
             self.internal_count = 1
@@ -597,7 +612,7 @@ class E2SecOracle:
         return emitted
 
     def finish(self):
-        table = self.table if self.table is not None else np.full((30, 1), "-", dtype="U5")
+        table = self.table if self.table is not None else np.full((10 * self.relations, 1), "-", dtype="U5")
         return esec_to_e2sec(table, self.relations, self.final_columns)
 
 

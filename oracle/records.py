@@ -36,7 +36,7 @@ class RecordOracle:
         filtered, det = o.entities_of_frame(frame, xyz32, label_flat)
         rec = np.zeros(record_doubles(K))
         flags = 1 if hand_in_raw else 0
-        stored = [i != 0 and i != o.ground_idx for i in range(K)]
+        stored = [(i != 0 or i == o.hand_idx) and i != o.ground_idx for i in range(K)]   # index 0 is only ever read as the hand (:1518-1520, :1549)
         if stored[o.hand_idx] and len(filtered[o.hand_idx]) > 0:
             flags |= 2
         rec[0], rec[1], rec[2] = frame, flags, K

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     for name in sorted(declared):
         assert hasattr(nat.lib, name), "libe2sec.so does not export %s" % name
     assert declared == set(nat.EXPORTS), declared ^ set(nat.EXPORTS)
-    assert nat.lib.e2sec_abi_version() == 4
+    assert nat.lib.e2sec_abi_version() == nat.ABI_VERSION
     assert nat.record_doubles(6) == 4 + 16 * 6 + 49 + 36 + 12
 
 
