@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define E2SEC_ABI_VERSION 5
+#define E2SEC_ABI_VERSION 6
 #define E2SEC_MAX_ENTITIES 64      /* len(total_unique_labels) upper bound                           */
 #define E2SEC_LABEL_LUT 4096       /* raw labels must be integers in [0, E2SEC_LABEL_LUT)            */
 
@@ -127,7 +127,8 @@ int e2sec_process_batch(e2sec_ctx *ctx, const float *xyz, const int32_t *labels,
                         const int32_t *frame_ids, int on_device, double *records);
 /* The same, stream-ordered and WITHOUT waiting: `records` (pinned host memory, or NULL) is filled by an asynchronous
  * copy, host inputs must stay untouched and device-side errors are reported by the next e2sec_sync / e2sec_process_batch.
- * Lets a caller queue several batches back to back (bench.py) -- the reference's loop (:2271-2281) has no equivalent. */
+ * Lets a caller queue several batches back to back (bench.py) -- the reference's loop (:2271-2281) has no equivalent.
+ * `records` may also be DEVICE memory here (a shard that keeps all its records for e2sec_phase2_run).                  */
 int e2sec_process_batch_async(e2sec_ctx *ctx, const float *xyz, const int32_t *labels, int32_t n_frames,
                               int32_t label_w, int32_t label_h, int32_t width, int32_t height,
                               const int32_t *frame_ids, int on_device, double *records);
@@ -205,6 +206,43 @@ typedef struct e2sec_relation_input {
     int32_t absent[3];
 } e2sec_relation_input;
 int e2sec_relation_rows(const e2sec_relation_input *in, int32_t relations, char *codes, int32_t absent_out[3]);
+
+/* ---- phase 2 on the device: the same selection / relation rows / column dedup as the resolver above, as ONE kernel over a
+ * run of records that are already in device memory (csrc/phase2.cuh; one thread per frame, the sequential state -- three
+ * bindings, three sticky bits, the previous kept frame, the last column -- carried by scans).  Only the emitted columns
+ * (E2SEC_PHASE2_COLUMN_BYTES code bytes + the frame id each) ever leave the GPU.
+ * The object belongs to a configured context (same device, the context's parameters) and works on its own stream.        */
+#define E2SEC_PHASE2_STATE_BYTES 512
+#define E2SEC_PHASE2_COLUMN_BYTES 32
+typedef struct e2sec_phase2 e2sec_phase2;
+int e2sec_phase2_create(e2sec_ctx *ctx, int32_t max_columns, e2sec_phase2 **out);
+void e2sec_phase2_destroy(e2sec_phase2 *p2);
+/* a new sequence: no bindings, no previous frame, no columns */
+int e2sec_phase2_reset(e2sec_phase2 *p2);
+/* Classifies n_frames records (frame order, device memory, e2sec_record_doubles(K) doubles each) behind everything fed
+ * before.  Does not wait.  src (may be NULL) = the context whose stream produces the records, e.g.
+ * e2sec_phase2_run(p2, ctx, e2sec_records_dev(ctx), n) right after e2sec_process_batch_async(ctx, ..., NULL): phase 2 waits
+ * for that batch, and the context's next batch waits until its record buffer has been read.                               */
+int e2sec_phase2_run(e2sec_phase2 *p2, e2sec_ctx *src, const double *records_dev, int32_t n_frames);
+/* The state a shard of a frame-sharded sequence hands to the next one (opaque, E2SEC_PHASE2_STATE_BYTES; dst / src may be
+ * host or device memory, e.g. the buffer of an NCCL send / recv).  Both wait for the object's stream.                     */
+int e2sec_phase2_state_get(e2sec_phase2 *p2, void *dst);
+int e2sec_phase2_state_set(e2sec_phase2 *p2, const void *src);
+/* Waits; reports device-side errors (records out of order, more than max_columns columns); n_columns (may be NULL) = the
+ * columns this object holds.                                                                                              */
+int e2sec_phase2_sync(e2sec_phase2 *p2, int32_t *n_columns);
+/* The packed columns (n x E2SEC_PHASE2_COLUMN_BYTES relation codes as csrc/relations.h numbers them, rows 0..10*relations-1
+ * used) and the frame id of each, to the host; and their device addresses for a gather between GPUs.                      */
+int e2sec_phase2_fetch(e2sec_phase2 *p2, uint8_t *columns, int32_t *frames, int32_t capacity, int32_t *n_columns);
+int e2sec_phase2_columns_dev(e2sec_phase2 *p2, const uint8_t **columns_dev, const int32_t **frames_dev, const int32_t **n_dev);
+/* o1/o2/o3 entity indices (-1 while unassigned) and the sticky absent flags, like e2sec_resolver_state */
+int e2sec_phase2_bindings(e2sec_phase2 *p2, int32_t labels[3], int32_t absent[3]);
+void *e2sec_phase2_stream(e2sec_phase2 *p2);
+/* Packed columns (host) -> the table of e2sec_resolver_table: codes (10*relations) x total x 6 bytes and the frame id per
+ * column; returns total = n (+ 1 for the initial '-' column with relations 1 / 2, :2252-2260, :1753).  With codes and
+ * final_columns both NULL only the count is returned.                                                                    */
+int32_t e2sec_columns_table(const uint8_t *columns, const int32_t *frames, int32_t n, int32_t relations, char *codes,
+                            int32_t *final_columns);
 
 /* ---- the consumer of the tables: eSEC_analyser.getDissimilarityMatrix (eSEC_analyser.py:782-841, with
  * _make_triple :866-889 and _compare_triple_matrics :915-944) and similarity_manipulations (:843-864).

@@ -8,12 +8,14 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libe2sec.so")
 
-ABI_VERSION = 5            # E2SEC_ABI_VERSION of include/e2sec.h this binding was written against
+ABI_VERSION = 6            # E2SEC_ABI_VERSION of include/e2sec.h this binding was written against
 MAX_ENTITIES = 64
 REC_HEADER = 4
 REC_ENTITY = 16
 FLAG_HAND_LABEL = 1
 FLAG_HAND_POINTS = 2
+PHASE2_STATE_BYTES = 512
+PHASE2_COLUMN_BYTES = 32
 FILTER_CLOSURE = 0
 FILTER_REFERENCE_SEEDED = 1
 FILTER_MODES = {"closure": FILTER_CLOSURE, "reference_seeded": FILTER_REFERENCE_SEEDED}
@@ -75,6 +77,18 @@ def _load():
         "e2sec_resolver_state": (C.c_int, [vp, vp, vp]),
         "e2sec_esec_to_e2sec": (i32, [vp, i32, i32, i32, vp, vp, vp]),
         "e2sec_relation_rows": (C.c_int, [vp, i32, vp, vp]),
+        "e2sec_phase2_create": (C.c_int, [vp, i32, C.POINTER(vp)]),
+        "e2sec_phase2_destroy": (None, [vp]),
+        "e2sec_phase2_reset": (C.c_int, [vp]),
+        "e2sec_phase2_run": (C.c_int, [vp, vp, vp, i32]),
+        "e2sec_phase2_state_get": (C.c_int, [vp, vp]),
+        "e2sec_phase2_state_set": (C.c_int, [vp, vp]),
+        "e2sec_phase2_sync": (C.c_int, [vp, vp]),
+        "e2sec_phase2_fetch": (C.c_int, [vp, vp, vp, i32, vp]),
+        "e2sec_phase2_columns_dev": (C.c_int, [vp, vp, vp, vp]),
+        "e2sec_phase2_bindings": (C.c_int, [vp, vp, vp]),
+        "e2sec_phase2_stream": (vp, [vp]),
+        "e2sec_columns_table": (i32, [vp, vp, i32, i32, vp, vp]),
         "e2sec_read_pcd_xyz": (C.c_int, [C.c_char_p, vp, i64, vp, vp]),
         "e2sec_read_labels": (C.c_int, [C.c_char_p, vp, i64, vp, vp]),
     }

@@ -410,7 +410,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
     const double *X = d.px + pb, *Y = d.py + pb, *Z = d.pz + pb;
     unsigned *flist = d.flist + pb;
     unsigned short *pcell = d.pcell + pb;
-    const bool filtered = n > 3;               // :1520
+    const bool filtered = entity_filtered(d, fe, n);               // :1520
 
     if (FINISH) {
         // the cell closure of the first visit + the candidate points, settled at the exact float32 radius (pyx:35)

@@ -40,6 +40,9 @@ struct Dev {
                                       // frame of the previous batches (its clouds feed the cross-frame distances)
     int S;                            // segments per frame = ceil(N / E2_SEG)
     int hand_idx, ground_idx;
+    int ent_shift;                    // 1 when the hand is index 0 of total_unique_labels: the device then works on K + 1 entities (a
+                                      // phantom in front, so that "index 0 is never stored" keeps holding) and the hand is left
+                                      // unfiltered as :1518-1520 does for i == 0; assemble_kernel writes the caller's K-entity record
     int hand_label;
     int n_ground;
     int filter_mode;
@@ -117,6 +120,13 @@ __device__ __forceinline__ void pdl_enter()
 __device__ __forceinline__ bool exact_path_idle(const Dev &d)
 {
     return d.radius_mode == E2SEC_RADIUS_BOUNDED && *((volatile int *)d.amb_count) == 0;
+}
+
+// :1518-1520: an entity is filtered when it has more than 3 points and is neither the ground nor index 0 (not stored, or the
+// hand itself when ent_shift is set)
+__device__ __forceinline__ bool entity_filtered(const Dev &d, int fe, int n)
+{
+    return n > 3 && !(d.ent_shift && fe % d.K == d.hand_idx);
 }
 
 __device__ __forceinline__ u64 d2key(double v) { return (u64)__double_as_longlong(v); }

@@ -20,6 +20,7 @@
 #include "pairs.cuh"
 #include "contact.cuh"
 #include "dissim.cuh"
+#include "phase2.cuh"
 
 #define E2_MAX_REFINE 6        // histogram rounds launched per batch (each narrows the key interval 256x)
 
@@ -62,6 +63,7 @@ struct e2sec_ctx {
     int sf_cluster = 8;
     bool seg_cluster = false;      // E2SEC_SEG_MODE=cluster: the one-kernel cluster segmentation instead of the unit stream
     bool pdl = true;
+    cudaError_t launch_err = cudaSuccess;
     bool force_two_pass = false;   // E2SEC_SEG_TWO_PASS=1: always take the two-pass segmentation (tests compare both)
 };
 
@@ -117,12 +119,20 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
         return fail(nullptr, E2SEC_ERR_CUDA, "e2sec_create: cannot create a stream");
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
-    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
-    for (auto &ev : ctx->ds_ev) cudaEventCreate(&ev);
-    cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
+    cudaError_t ce = cudaSuccess;
+    auto keep = [&](cudaError_t r) { if (ce == cudaSuccess) ce = r; };
+    for (auto &ev : ctx->ev) keep(cudaEventCreate(&ev));
+    for (auto &ev : ctx->ds_ev) keep(cudaEventCreate(&ev));
+    keep(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 2; ++i) {
-        cudaEventCreateWithFlags(&ctx->copy_done[i], cudaEventDisableTiming);
-        cudaEventCreateWithFlags(&ctx->slot_free[i], cudaEventDisableTiming);
+        keep(cudaEventCreateWithFlags(&ctx->copy_done[i], cudaEventDisableTiming));
+        keep(cudaEventCreateWithFlags(&ctx->slot_free[i], cudaEventDisableTiming));
+    }
+    if (ce != cudaSuccess) {
+        const std::string msg = std::string("e2sec_create: cannot create events / copy stream: ") + cudaGetErrorString(ce);
+        cudaStreamDestroy(ctx->stream);
+        delete ctx;
+        return fail(nullptr, E2SEC_ERR_CUDA, msg);
     }
     ctx->ev_valid = true;
     cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -200,60 +210,59 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     const int S = (N + E2_SEG - 1) / E2_SEG;
     const size_t FK = (size_t)(F + 1) * K;
     int rc = 0;
-    rc |= ensure(ctx, ctx->xyz_stage, (size_t)2 * F * N * 3 * sizeof(float));     // two staging slots
-    rc |= ensure(ctx, ctx->lab_stage, (size_t)2 * F * N * sizeof(int));
-    rc |= ensure(ctx, ctx->cross_key, (size_t)F * K * K * sizeof(u64));
-    rc |= ensure(ctx, ctx->frame_used, (size_t)(F + 1) * sizeof(int));
-    rc |= ensure(ctx, ctx->prev_slot, (size_t)F * sizeof(int));
-    rc |= ensure(ctx, ctx->prev_id, (size_t)F * sizeof(int));
-    rc |= ensure(ctx, ctx->halo_info, 4 * sizeof(int));
-    rc |= ensure(ctx, ctx->lut, E2SEC_LABEL_LUT * sizeof(int));
-    rc |= ensure(ctx, ctx->frame_ids, F * sizeof(int));
-    rc |= ensure(ctx, ctx->seg_cnt, (size_t)F * S * K * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->ent_raw, FK * sizeof(int));
-    rc |= ensure(ctx, ctx->ent_off, FK * sizeof(int));
-    rc |= ensure(ctx, ctx->flags, F * sizeof(int));
-    rc |= ensure(ctx, ctx->px, cap * sizeof(double));
-    rc |= ensure(ctx, ctx->py, cap * sizeof(double));
-    rc |= ensure(ctx, ctx->pz, cap * sizeof(double));
-    rc |= ensure(ctx, ctx->pidx, cap * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->med, FK * 3 * sizeof(double));
-    rc |= ensure(ctx, ctx->radius, FK * sizeof(double));
-    rc |= ensure(ctx, ctx->rs, FK * sizeof(RadiusState));
-    rc |= ensure(ctx, ctx->hist, FK * E2_NBINS * sizeof(u64));
-    rc |= ensure(ctx, ctx->cand, FK * E2_CAND_CAP * sizeof(u64));
-    rc |= ensure(ctx, ctx->cand_n, FK * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->seed_pos, FK * sizeof(int));
-    rc |= ensure(ctx, ctx->member, cap);
-    rc |= ensure(ctx, ctx->front_a, cap * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->front_b, cap * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->flist, cap * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->n_list, FK * sizeof(int));
-    rc |= ensure(ctx, ctx->aabb, FK * 6 * sizeof(double));
-    rc |= ensure(ctx, ctx->mean, FK * 3 * sizeof(double));
-    rc |= ensure(ctx, ctx->pair_key, (size_t)F * (K + 1) * (K + 1) * sizeof(u64));
-    rc |= ensure(ctx, ctx->records, (size_t)F * e2sec_record_doubles(K) * sizeof(double));
-    rc |= ensure(ctx, ctx->error, sizeof(int));
-    rc |= ensure(ctx, ctx->plan_off, (FK + 1) * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->plan_total, sizeof(unsigned));
-    rc |= ensure(ctx, ctx->below_acc, FK * sizeof(u64));
-    rc |= ensure(ctx, ctx->min_above, FK * sizeof(u64));
-    rc |= ensure(ctx, ctx->single_count, FK * sizeof(u64));
-    rc |= ensure(ctx, ctx->pcell, cap * sizeof(unsigned short));
-    rc |= ensure(ctx, ctx->rad_lo, FK * sizeof(double));
-    rc |= ensure(ctx, ctx->rad_hi, FK * sizeof(double));
-    rc |= ensure(ctx, ctx->amb, FK * sizeof(int));
-    rc |= ensure(ctx, ctx->amb_count, sizeof(int));
-    rc |= ensure(ctx, ctx->cell_state, FK * sizeof(CellState));
+    if ((rc = ensure(ctx, ctx->xyz_stage, (size_t)2 * F * N * 3 * sizeof(float)))) return rc;     // two staging slots
+    if ((rc = ensure(ctx, ctx->lab_stage, (size_t)2 * F * N * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->cross_key, (size_t)F * K * K * sizeof(u64)))) return rc;
+    if ((rc = ensure(ctx, ctx->frame_used, (size_t)(F + 1) * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->prev_slot, (size_t)F * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->prev_id, (size_t)F * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->halo_info, 4 * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->lut, E2SEC_LABEL_LUT * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->frame_ids, F * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->seg_cnt, (size_t)F * S * K * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->ent_raw, FK * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->ent_off, FK * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->flags, F * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->px, cap * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->py, cap * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->pz, cap * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->pidx, cap * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->med, FK * 3 * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->radius, FK * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->rs, FK * sizeof(RadiusState)))) return rc;
+    if ((rc = ensure(ctx, ctx->hist, FK * E2_NBINS * sizeof(u64)))) return rc;
+    if ((rc = ensure(ctx, ctx->cand, FK * E2_CAND_CAP * sizeof(u64)))) return rc;
+    if ((rc = ensure(ctx, ctx->cand_n, FK * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->seed_pos, FK * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->member, cap))) return rc;
+    if ((rc = ensure(ctx, ctx->front_a, cap * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->front_b, cap * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->flist, cap * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->n_list, FK * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->aabb, FK * 6 * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->mean, FK * 3 * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->pair_key, (size_t)F * (K + 1) * (K + 1) * sizeof(u64)))) return rc;
+    if ((rc = ensure(ctx, ctx->records, (size_t)F * e2sec_record_doubles(K) * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->error, sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->plan_off, (FK + 1) * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->plan_total, sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->below_acc, FK * sizeof(u64)))) return rc;
+    if ((rc = ensure(ctx, ctx->min_above, FK * sizeof(u64)))) return rc;
+    if ((rc = ensure(ctx, ctx->single_count, FK * sizeof(u64)))) return rc;
+    if ((rc = ensure(ctx, ctx->pcell, cap * sizeof(unsigned short)))) return rc;
+    if ((rc = ensure(ctx, ctx->rad_lo, FK * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->rad_hi, FK * sizeof(double)))) return rc;
+    if ((rc = ensure(ctx, ctx->amb, FK * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->amb_count, sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->cell_state, FK * sizeof(CellState)))) return rc;
     const size_t slots = (size_t)K * (K - 1) / 2 + K + (size_t)K * K;
-    rc |= ensure(ctx, ctx->ct_cnt, (size_t)F * slots * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->ct_off, ((size_t)F * slots + 1) * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->ct_next, sizeof(unsigned));
-    rc |= ensure(ctx, ctx->ct_map, std::max((size_t)F * slots * 4, (size_t)65536) * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->seg_list, (size_t)F * N * sizeof(uint4));
-    rc |= ensure(ctx, ctx->seg_len, (size_t)F * ((N + E2_SS_UNIT - 1) / E2_SS_UNIT) * sizeof(unsigned));
-    rc |= ensure(ctx, ctx->seg_next, sizeof(unsigned));
-    if (rc) return E2SEC_ERR_CUDA;
+    if ((rc = ensure(ctx, ctx->ct_cnt, (size_t)F * slots * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->ct_off, ((size_t)F * slots + 1) * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->ct_next, sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->ct_map, std::max((size_t)F * slots * 4, (size_t)65536) * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->seg_list, (size_t)F * N * sizeof(uint4)))) return rc;
+    if ((rc = ensure(ctx, ctx->seg_len, (size_t)F * ((N + E2_SS_UNIT - 1) / E2_SS_UNIT) * sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->seg_next, sizeof(unsigned)))) return rc;
     CU(cudaMemset(ctx->error.p, 0, sizeof(int)));
     CU(cudaMemset(ctx->seg_next.p, 0, sizeof(unsigned)));
     CU(cudaMemset(ctx->amb_count.p, 0, sizeof(int)));
@@ -322,7 +331,13 @@ extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t ma
     if (hand_idx < 0) return fail(ctx, E2SEC_ERR_ARG, "hand_label is not in total_unique_labels");
     if (ground_idx < 0) return fail(ctx, E2SEC_ERR_ARG, "ground_label is not in total_unique_labels");
     if (p->n_ground < 0 || (p->n_ground > 0 && !p->ground_xyz)) return fail(ctx, E2SEC_ERR_ARG, "ground cloud missing");
-    int rc = allocate(ctx, max_frames, n_points, p->n_entities);
+    // The hand as the lowest tracked label sits at index 0 of total_unique_labels, which the reference never filters or
+    // relates EXCEPT as the hand (:1456-1475, :1518-1520, :1549).  The device keeps "index 0 is never stored" by working on
+    // one phantom entity in front (Dev::ent_shift); records come out in the caller's K-entity layout.
+    const int shift = hand_idx == 0 ? 1 : 0;
+    const int Kd = p->n_entities + shift;
+    if (Kd > E2SEC_MAX_ENTITIES) return fail(ctx, E2SEC_ERR_ARG, "n_entities out of range (the hand at index 0 takes one more slot)");
+    int rc = allocate(ctx, max_frames, n_points, Kd);
     if (rc) return rc;
     ctx->params = *p;
     ctx->ground.assign(p->ground_xyz, p->ground_xyz + (size_t)3 * p->n_ground);
@@ -335,7 +350,7 @@ extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t ma
             if (v == p->replace_old[i]) v = p->replace_new[i];
         int idx = -1;
         for (int e = 0; e < p->n_entities; ++e)
-            if (p->entity_label[e] == v) { idx = e; break; }
+            if (p->entity_label[e] == v) { idx = e + shift; break; }
         lut[raw] = idx;
     }
     CU(cudaMemcpyAsync(ctx->lut.p, lut.data(), lut.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
@@ -401,10 +416,11 @@ extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t ma
     }
     CU(cudaStreamSynchronize(ctx->stream));
     Dev &d = ctx->d;
-    d.K = p->n_entities;
+    d.K = Kd;
     d.N = n_points;
-    d.hand_idx = hand_idx;
-    d.ground_idx = ground_idx;
+    d.hand_idx = hand_idx + shift;
+    d.ground_idx = ground_idx + shift;
+    d.ent_shift = shift;
     d.hand_label = p->hand_label;
     d.n_ground = G;
     d.filter_mode = p->filter_mode;
@@ -422,7 +438,7 @@ extern "C" int e2sec_configure(e2sec_ctx *ctx, const e2sec_params *p, int32_t ma
     d.gy = (const double *)ctx->gy.p;
     d.gz = (const double *)ctx->gz.p;
     memcpy(d.gaabb, box, sizeof(box));
-    d.rec_doubles = (int)e2sec_record_doubles(d.K);
+    d.rec_doubles = (int)e2sec_record_doubles(p->n_entities);
     ctx->configured = true;
     return e2sec_reset_sequence(ctx);
 }
@@ -461,8 +477,19 @@ static inline void launch_pdl(e2sec_ctx *ctx, void (*k)(P...), dim3 g, dim3 b, s
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = ctx->pdl ? 1 : 0;
-    cudaLaunchKernelEx(&cfg, k, P(a)...);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, k, P(a)...);
+    if (e != cudaSuccess && ctx->launch_err == cudaSuccess) ctx->launch_err = e;     // the first failing launch is the one reported
     ++ctx->launches;
+}
+
+// every launch is checked; the pipeline functions report the first failure once they have queued their launches
+static int launch_status(e2sec_ctx *ctx, const char *where)
+{
+    if (ctx->launch_err == cudaSuccess) return E2SEC_OK;
+    const cudaError_t e = ctx->launch_err;
+    ctx->launch_err = cudaSuccess;
+    cudaGetLastError();
+    return fail(ctx, E2SEC_ERR_CUDA, std::string(where) + ": kernel launch failed: " + cudaGetErrorString(e));
 }
 
 // Everything after segmentation: medians, radius, filter, stats, pairs, records. `d` already describes the batch.
@@ -516,6 +543,7 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
     cudaEventRecord(ctx->ev[6], st);
     if (do_records) { launch_pdl(ctx, assemble_kernel, dim3(d.F), dim3(128), 0, st, d); }
     cudaEventRecord(ctx->ev[7], st);
+    if (int rc = launch_status(ctx, "entity stages")) return rc;
     CU(cudaGetLastError());
     return E2SEC_OK;
 }
@@ -648,12 +676,13 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labe
         launch_pdl(ctx, seg_scan_kernel, dim3(n_frames), dim3(E2SEC_MAX_ENTITIES), 0, st, d);
         launch_pdl(ctx, seg_scatter_kernel, dim3(sgrid), dim3(32 * E2_SEG_WARPS), 0, st, d);
     }
+    if (int lrc = launch_status(ctx, "segmentation")) return lrc;
     if (stage_slot >= 0) { CU(cudaEventRecord(ctx->slot_free[stage_slot], st)); ctx->slot_used[stage_slot] = true; }   // inputs consumed
     cudaEventRecord(ctx->ev[1], st);
     int rc = run_entity_stages(ctx, d, true, true, true, true);
     if (rc) return rc;
     if (records)
-        CU(cudaMemcpyAsync(records, ctx->records.p, (size_t)n_frames * d.rec_doubles * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(records, ctx->records.p, (size_t)n_frames * d.rec_doubles * sizeof(double), cudaMemcpyDefault, st));
     return wait ? check_device_error(ctx) : E2SEC_OK;
 }
 
@@ -727,6 +756,7 @@ static int load_clouds(e2sec_ctx *ctx, Dev &d, int ne, const double *const *pts,
     d.N = d.cap;
     d.S = 0;
     d.hand_idx = 1;
+    d.ent_shift = 0;
     d.ground_idx = -1;
     d.n_ground = 0;
     d.rec_doubles = (int)e2sec_record_doubles(K);
@@ -978,3 +1008,197 @@ extern "C" int e2sec_dissimilarity_ms(e2sec_ctx *ctx, float *ms)
     CU(cudaEventElapsedTime(ms, ctx->ds_ev[0], ctx->ds_ev[1]));
     return E2SEC_OK;
 }
+
+// ---- phase 2 on the device (phase2.cuh) ------------------------------------------------------------------------------------
+static_assert(sizeof(Phase2State) <= E2SEC_PHASE2_STATE_BYTES, "Phase2State outgrew its ABI size");
+static_assert(E2_P2_COL == E2SEC_PHASE2_COLUMN_BYTES, "packed column width");
+
+struct e2sec_phase2 {
+    e2sec_ctx *ctx = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ready = nullptr, done = nullptr;
+    Phase2Dev a;
+    DevBuf state, cols, col_frame, n_cols;
+};
+
+static void phase2_initial_state(Phase2State &s)
+{
+    memset(&s, 0, sizeof(s));
+    for (int k = 0; k < 3; ++k) s.sel.oindex[k] = -1;
+    s.prev_frame_id = -1;
+}
+
+extern "C" int e2sec_phase2_create(e2sec_ctx *ctx, int32_t max_columns, e2sec_phase2 **out)
+{
+    if (!ctx || !out) return E2SEC_ERR_ARG;
+    *out = nullptr;
+    if (!ctx->configured) return fail(ctx, E2SEC_ERR_STATE, "e2sec_phase2_create: e2sec_configure has not been called");
+    if (max_columns < 1) return fail(ctx, E2SEC_ERR_ARG, "e2sec_phase2_create: max_columns must be positive");
+    cudaSetDevice(ctx->device);
+    const e2sec_params &p = ctx->params;
+    e2sec_phase2 *q = new e2sec_phase2();
+    q->ctx = ctx;
+    Phase2Dev &a = q->a;
+    memset(&a, 0, sizeof(a));
+    a.K = p.n_entities;
+    a.hand_idx = a.ground_idx = a.support_idx = -1;
+    for (int e = 0; e < a.K; ++e) {
+        if (p.entity_label[e] == p.hand_label) a.hand_idx = e;
+        if (p.entity_label[e] == p.ground_label) a.ground_idx = e;
+        if (p.support_hand >= 0 && p.entity_label[e] == p.support_hand) a.support_idx = e;
+    }
+    if (p.support_hand >= 0 && a.support_idx < 0) { delete q; return fail(ctx, E2SEC_ERR_ARG, "support_hand is not in total_unique_labels"); }
+    a.relations = p.relations ? p.relations : 3;
+    a.thresh = p.thresh;
+    a.rec_doubles = (int)e2sec_record_doubles(a.K);
+    a.ground = rel_ent_undefined();
+    a.ground.defined = 1;
+    a.ground.n = p.n_ground;
+    for (int i = 0; i < p.n_ground; ++i)
+        for (int k = 0; k < 3; ++k) {
+            const double v = ctx->ground[3 * (size_t)i + k];
+            if (i == 0 || v < a.ground.lo[k]) a.ground.lo[k] = v;
+            if (i == 0 || v > a.ground.hi[k]) a.ground.hi[k] = v;
+        }
+    for (int k = 0; k < 3; ++k) a.ground.center[k] = (a.ground.lo[k] + a.ground.hi[k]) * 0.5;
+    a.max_columns = max_columns;
+    bool ok = cudaStreamCreateWithFlags(&q->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreateWithFlags(&q->ready, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&q->done, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && !ensure(ctx, q->state, sizeof(Phase2State)) && !ensure(ctx, q->cols, (size_t)max_columns * E2_P2_COL) &&
+         !ensure(ctx, q->col_frame, (size_t)max_columns * sizeof(int)) && !ensure(ctx, q->n_cols, sizeof(int));
+    if (!ok) { e2sec_phase2_destroy(q); return fail(ctx, E2SEC_ERR_CUDA, "e2sec_phase2_create: cannot allocate"); }
+    a.state = (Phase2State *)q->state.p;
+    a.cols = (unsigned char *)q->cols.p;
+    a.col_frame = (int *)q->col_frame.p;
+    a.n_cols = (int *)q->n_cols.p;
+    *out = q;
+    return e2sec_phase2_reset(q);
+}
+
+extern "C" void e2sec_phase2_destroy(e2sec_phase2 *q)
+{
+    if (!q) return;
+    cudaSetDevice(q->ctx->device);
+    if (q->stream) cudaStreamSynchronize(q->stream);
+    for (DevBuf *b : {&q->state, &q->cols, &q->col_frame, &q->n_cols})
+        if (b->p) cudaFree(b->p);
+    if (q->ready) cudaEventDestroy(q->ready);
+    if (q->done) cudaEventDestroy(q->done);
+    if (q->stream) cudaStreamDestroy(q->stream);
+    delete q;
+}
+
+extern "C" int e2sec_phase2_reset(e2sec_phase2 *q)
+{
+    if (!q) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    Phase2State s;
+    phase2_initial_state(s);
+    CU(cudaMemcpyAsync(q->state.p, &s, sizeof(s), cudaMemcpyHostToDevice, q->stream));
+    CU(cudaMemsetAsync(q->n_cols.p, 0, sizeof(int), q->stream));
+    CU(cudaStreamSynchronize(q->stream));       // `s` lives on this stack frame
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_run(e2sec_phase2 *q, e2sec_ctx *src, const double *records_dev, int32_t n_frames)
+{
+    if (!q || !records_dev || n_frames < 0) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    if (n_frames == 0) return E2SEC_OK;
+    if (src) {                                   // the records are produced on src's stream
+        CU(cudaEventRecord(q->ready, src->stream));
+        CU(cudaStreamWaitEvent(q->stream, q->ready, 0));
+    }
+    Phase2Dev a = q->a;
+    a.records = records_dev;
+    a.n_frames = n_frames;
+    phase2_kernel<<<1, E2_P2_THREADS, 0, q->stream>>>(a);
+    ++ctx->launches;
+    CU(cudaGetLastError());
+    if (src) {                                   // and may be overwritten by src's next batch only once they have been read
+        CU(cudaEventRecord(q->done, q->stream));
+        CU(cudaStreamWaitEvent(src->stream, q->done, 0));
+    }
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_state_get(e2sec_phase2 *q, void *dst)
+{
+    if (!q || !dst) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    CU(cudaMemcpyAsync(dst, q->state.p, sizeof(Phase2State), cudaMemcpyDefault, q->stream));
+    CU(cudaStreamSynchronize(q->stream));
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_state_set(e2sec_phase2 *q, const void *src)
+{
+    if (!q || !src) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    CU(cudaMemcpyAsync(q->state.p, src, sizeof(Phase2State), cudaMemcpyDefault, q->stream));
+    CU(cudaStreamSynchronize(q->stream));
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_sync(e2sec_phase2 *q, int32_t *n_columns)
+{
+    if (!q) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    Phase2State s;
+    int n = 0;
+    CU(cudaMemcpyAsync(&s, q->state.p, sizeof(s), cudaMemcpyDeviceToHost, q->stream));
+    CU(cudaMemcpyAsync(&n, q->n_cols.p, sizeof(int), cudaMemcpyDeviceToHost, q->stream));
+    CU(cudaStreamSynchronize(q->stream));
+    if (n_columns) *n_columns = n;
+    if (s.error == E2SEC_ERR_CAPACITY) return fail(ctx, E2SEC_ERR_CAPACITY, "phase 2: more columns than max_columns");
+    if (s.error) return fail(ctx, E2SEC_ERR_STATE, "phase 2: a record was measured against another previous kept frame than the one "
+                                                   "phase 2 saw last (feed frames in order; a shard starts with its halo frame)");
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_fetch(e2sec_phase2 *q, uint8_t *columns, int32_t *frames, int32_t capacity, int32_t *n_columns)
+{
+    if (!q || !n_columns) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    int n = 0;
+    int rc = e2sec_phase2_sync(q, &n);
+    if (rc) return rc;
+    *n_columns = n;
+    if (n > capacity) return fail(ctx, E2SEC_ERR_CAPACITY, "e2sec_phase2_fetch: capacity too small");
+    if (n && columns) CU(cudaMemcpyAsync(columns, q->cols.p, (size_t)n * E2_P2_COL, cudaMemcpyDeviceToHost, q->stream));
+    if (n && frames) CU(cudaMemcpyAsync(frames, q->col_frame.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, q->stream));
+    CU(cudaStreamSynchronize(q->stream));
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_columns_dev(e2sec_phase2 *q, const uint8_t **columns_dev, const int32_t **frames_dev, const int32_t **n_dev)
+{
+    if (!q) return E2SEC_ERR_ARG;
+    if (columns_dev) *columns_dev = (const uint8_t *)q->cols.p;
+    if (frames_dev) *frames_dev = (const int32_t *)q->col_frame.p;
+    if (n_dev) *n_dev = (const int32_t *)q->n_cols.p;
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_bindings(e2sec_phase2 *q, int32_t labels[3], int32_t absent[3])
+{
+    if (!q) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    Phase2State s;
+    CU(cudaMemcpyAsync(&s, q->state.p, sizeof(s), cudaMemcpyDeviceToHost, q->stream));
+    CU(cudaStreamSynchronize(q->stream));
+    for (int k = 0; k < 3; ++k) {
+        if (labels) labels[k] = s.sel.count[k] ? s.sel.oindex[k] : -1;
+        if (absent) absent[k] = s.absent[k] ? 1 : 0;
+    }
+    return E2SEC_OK;
+}
+
+extern "C" void *e2sec_phase2_stream(e2sec_phase2 *q) { return q ? (void *)q->stream : nullptr; }

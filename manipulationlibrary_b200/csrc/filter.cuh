@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(E2_FILTER_THREADS) region_filter_kernel(Dev d)
     }
     const size_t pb = (size_t)f * d.cap + off;
     unsigned *flist = d.flist + pb;
-    if (n <= 3) {                         // :1543-1546 the raw cloud is used
+    if (!entity_filtered(d, fe, n)) {                         // :1543-1546 the raw cloud is used
         for (int i = tid; i < n; i += E2_FILTER_THREADS) flist[i] = (unsigned)i;
         if (tid == 0) { d.n_list[fe] = n; d.seed_pos[fe] = -1; }
         return;
@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(E2_FILTER_THREADS) region_filter_kernel(Dev d)
     unsigned *rem = d.front_a + pb, *nxt = d.front_b + pb;
     for (int i = tid; i < n; i += E2_FILTER_THREADS) rem[i] = (unsigned)i;
     if (tid == 0) {
-        const unsigned s = d.filter_seed + 1000003u * (unsigned)d.frame_ids[f] + 7919u * (unsigned)e;
+        const unsigned s = d.filter_seed + 1000003u * (unsigned)d.frame_ids[f] + 7919u * (unsigned)(e - d.ent_shift);      // label_index as the caller counts it
         rng.seed(s);
         sm.n_out = 0;
         sm.pv[0] = X[seed]; sm.pv[1] = Y[seed]; sm.pv[2] = Z[seed];
@@ -248,6 +248,7 @@ __global__ void __launch_bounds__(E2_FILTER_THREADS) region_filter_kernel(Dev d)
         abort_cnt = (n_out == out0) ? abort_cnt + 1 : 0;       // pyx:80-83
         n_rem = (int)n_keep;
         unsigned *t = rem; rem = nxt; nxt = t;
+        if (n_rem == 0) __syncthreads();                       // a dry pass ran no barrier: every thread has read sm.pv / sm.n_out
         if (tid == 0) {
             sm.n_out = n_out;
             const unsigned c = rng.randbelow(n_out + 1u);      // random.choice(list(dicti.values())), pyx:78

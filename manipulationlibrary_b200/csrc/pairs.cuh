@@ -257,7 +257,8 @@ __global__ void __launch_bounds__(E2_PD_THREADS) pair_distance_kernel(Dev d)
 __global__ void assemble_kernel(Dev d)
 {
     pdl_enter();
-    const int f = blockIdx.x, K = d.K;
+    // d.K entities on the device, Ke = d.K - d.ent_shift in the caller's record (the phantom in front is dropped)
+    const int f = blockIdx.x, K = d.K, sh = d.ent_shift, Ke = K - sh;
     double *rec = d.records + (size_t)f * d.rec_doubles;
     const double NaN = __longlong_as_double(0x7ff8000000000000ll);
     const double INF = __longlong_as_double(0x7ff0000000000000ll);
@@ -267,11 +268,11 @@ __global__ void assemble_kernel(Dev d)
         if (hoff >= 0 && d.n_list[f * K + d.hand_idx] > 0) flags |= E2SEC_FLAG_HAND_POINTS;
         rec[0] = (double)d.frame_ids[f];
         rec[1] = (double)flags;
-        rec[2] = (double)K;
+        rec[2] = (double)Ke;
         rec[3] = (double)d.prev_id[f];
     }
-    for (int e = threadIdx.x; e < K; e += blockDim.x) {
-        const int fe = f * K + e;
+    for (int e = threadIdx.x; e < Ke; e += blockDim.x) {
+        const int fe = f * K + e + sh;
         double *r = rec + E2SEC_REC_HEADER + E2SEC_REC_ENTITY * e;
         const bool stored = d.ent_off[fe] >= 0;
         const int m = stored ? d.n_list[fe] : 0;
@@ -284,27 +285,27 @@ __global__ void assemble_kernel(Dev d)
         for (int k = 0; k < 6; ++k) r[7 + k] = stored ? d.aabb[(size_t)fe * 6 + k] : 0.0;
         for (int k = 0; k < 3; ++k) r[13 + k] = stored ? d.mean[(size_t)fe * 3 + k] : 0.0;
     }
-    double *pt = rec + E2SEC_REC_HEADER + E2SEC_REC_ENTITY * K;
-    const int W = K + 1;
+    double *pt = rec + E2SEC_REC_HEADER + E2SEC_REC_ENTITY * Ke;
+    const int W = Ke + 1, Wd = K + 1;
     for (int i = threadIdx.x; i < W * W; i += blockDim.x) {
-        int a = i / W, b = i - a * W;
+        const int a = i / W + sh, b = i % W + sh;                 // the ground cloud: Ke -> K
         double v = INF;
         if (a != b) {
             const int lo = a < b ? a : b, hi = a < b ? b : a;
             const bool ok = (lo != 0 && lo != d.ground_idx && (hi == K || (hi != 0 && hi != d.ground_idx)));
-            if (ok) v = sqrt(key2d(d.pair_key[((size_t)f * W + lo) * W + hi]));
+            if (ok) v = sqrt(key2d(d.pair_key[((size_t)f * Wd + lo) * Wd + hi]));
         }
         pt[i] = v;
     }
     double *ct = pt + W * W;
-    for (int i = threadIdx.x; i < K * K; i += blockDim.x) {
-        const int a = i / K, b = i - a * K;
+    for (int i = threadIdx.x; i < Ke * Ke; i += blockDim.x) {
+        const int a = i / Ke + sh, b = i % Ke + sh;
         const bool ok = a != b && a != 0 && b != 0 && a != d.ground_idx && b != d.ground_idx;
-        ct[i] = ok ? sqrt(key2d(d.cross_key[(size_t)f * K * K + i])) : INF;
+        ct[i] = ok ? sqrt(key2d(d.cross_key[(size_t)f * K * K + (size_t)a * K + b])) : INF;
     }
-    double *rb = ct + K * K;
-    for (int e = threadIdx.x; e < K; e += blockDim.x) {
-        const int fe = f * K + e;
+    double *rb = ct + Ke * Ke;
+    for (int e = threadIdx.x; e < Ke; e += blockDim.x) {
+        const int fe = f * K + e + sh;
         const bool filt = d.ent_off[fe] >= 0 && d.seed_pos[fe] >= 0;
         const double r = d.radius[fe];
         const bool exact = filt && !(r != r);

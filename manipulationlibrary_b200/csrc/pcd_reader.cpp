@@ -115,7 +115,13 @@ extern "C" int e2sec_read_pcd_xyz(const char *path, float *xyz, int64_t capacity
     const size_t nf = h.fields.size();
     if (h.sizes.size() != nf || h.types.size() != nf) return E2SEC_ERR_IO;
     if (h.counts.empty()) h.counts.assign(nf, 1);
+    // the header is untrusted: one COUNT per FIELD, positive sizes that cannot make stride * POINTS wrap
+    if (h.counts.size() != nf || nf == 0 || nf > 64) return E2SEC_ERR_IO;
+    for (size_t k = 0; k < nf; ++k)
+        if (h.sizes[k] <= 0 || h.sizes[k] > 8 || h.counts[k] <= 0 || h.counts[k] > 4096) return E2SEC_ERR_IO;
+    if (h.width < 0 || h.height < 0 || h.width > (1 << 24) || h.height > (1 << 24)) return E2SEC_ERR_IO;
     if (h.points <= 0) h.points = h.width * h.height;
+    if (h.points <= 0 || h.points > (1ll << 31)) return E2SEC_ERR_IO;
     if (h.points > capacity_points) return E2SEC_ERR_CAPACITY;
     int fi[3] = {-1, -1, -1};
     std::vector<size_t> foff(nf);
@@ -134,7 +140,7 @@ extern "C" int e2sec_read_pcd_xyz(const char *path, float *xyz, int64_t capacity
         uint32_t comp, raw;
         memcpy(&comp, &buf[h.body], 4);
         memcpy(&raw, &buf[h.body + 4], 4);
-        if (h.body + 8 + comp > buf.size() || raw < stride * P) return E2SEC_ERR_IO;
+        if ((uint64_t)comp > buf.size() - h.body - 8 || (uint64_t)raw < (uint64_t)stride * P) return E2SEC_ERR_IO;
         std::vector<unsigned char> plain;
         if (!lzf_expand(&buf[h.body + 8], comp, plain, raw)) return E2SEC_ERR_IO;
         for (int a = 0; a < 3; ++a) {
@@ -142,7 +148,7 @@ extern "C" int e2sec_read_pcd_xyz(const char *path, float *xyz, int64_t capacity
             for (size_t i = 0; i < P; ++i) memcpy(&xyz[3 * i + a], col + 4 * i, 4);
         }
     } else if (h.data == "binary") {
-        if (h.body + stride * P > buf.size()) return E2SEC_ERR_IO;
+        if (h.body > buf.size() || (uint64_t)stride * P > buf.size() - h.body) return E2SEC_ERR_IO;
         for (size_t i = 0; i < P; ++i)
             for (int a = 0; a < 3; ++a) memcpy(&xyz[3 * i + a], &buf[h.body + i * stride + foff[fi[a]]], 4);
     } else if (h.data == "ascii") {

@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, u64 *min_above)
         min_above[fe] = ~0ull;
     }
     for (int b = threadIdx.x; b < E2_NBINS; b += blockDim.x) d.hist[(size_t)fe * E2_NBINS + b] = 0;
-    if (off < 0 || n <= 3 || (d.radius_mode == E2SEC_RADIUS_BOUNDED && !d.amb[fe])) {   // nothing to select for this entity
+    if (off < 0 || !entity_filtered(d, fe, n) || (d.radius_mode == E2SEC_RADIUS_BOUNDED && !d.amb[fe])) {   // nothing to select for this entity
         if (threadIdx.x == 0) { rs.phase = 3; rs.n = n; }
         return;
     }

@@ -236,3 +236,81 @@ REL_HD void rel_fill_column(const RelEnt *cur, const RelEnt *prev, const double 
     if (relations >= 2) rel_fill_ssr(cur, out, out + 10);
     if (relations >= 3) rel_fill_dsr(cur, prev, out, out + 20);
 }
+
+
+// ---- records (include/e2sec.h) -> what the rows read --------------------------------------------------------------------
+#define REL_REC_HEADER 4
+#define REL_REC_ENTITY 16
+REL_HD RelEnt rel_ent_undefined()
+{
+    RelEnt x;
+    x.defined = 0; x.n = 0;
+    for (int k = 0; k < 3; ++k) x.lo[k] = x.hi[k] = x.center[k] = 0.0;
+    return x;
+}
+REL_HD RelEnt rel_ent_from_record(const double *rec, int e, bool is_hand)
+{
+    const double *r = rec + REL_REC_HEADER + REL_REC_ENTITY * e;
+    RelEnt x;
+    x.defined = 1;
+    x.n = (int)r[1];
+    for (int k = 0; k < 3; ++k) {
+        x.lo[k] = r[7 + k];
+        x.hi[k] = r[10 + k];
+        x.center[k] = is_hand ? r[13 + k] : (x.lo[k] + x.hi[k]) * 0.5;
+    }
+    return x;
+}
+REL_HD double rel_rec_pair(const double *rec, int K, int a, int b)     // in-frame minimum distance, index K = the ground cloud
+{
+    const int W = K + 1;
+    const double *pt = rec + REL_REC_HEADER + REL_REC_ENTITY * K;
+    return a < b ? pt[a * W + b] : pt[b * W + a];
+}
+REL_HD double rel_rec_cross(const double *rec, int K, int a_prev, int b)   // entity a of the previous kept frame vs b of this frame
+{
+    const int W = K + 1;
+    return rec[REL_REC_HEADER + REL_REC_ENTITY * K + W * W + a_prev * K + b];
+}
+
+// ---- o1 / o2 / o3 selection (:1562-1658), one kept frame -----------------------------------------------------------------
+// The bindings are sticky and first come, first served in ascending entity index.  While the loop runs, o_k is still the
+// cloud of the previous kept frame unless it was bound in this very frame (:1669-1675 rebinds after the loop), so the
+// distances to o_k come from the cross table (stale) or the in-frame table (fresh).  stale_n[k] = len(o_k.points) of the
+// stale cloud.  np.min over an empty distance array raises in the reference; here an empty stale cloud is "far".
+struct RelSel {
+    int oindex[3];      // entity index bound to o1..o3 (-1: none)
+    int count[3];       // count1..3
+};
+REL_HD bool rel_select(const double *rec, int K, int hand_idx, int ground_idx, int support_idx, double th, RelSel &S,
+                       const int *stale_n)
+{
+    bool fresh[3] = {false, false, false}, changed = false;
+    int on[3] = {stale_n[0], stale_n[1], stale_n[2]};
+    if (S.count[0] && S.count[1] && S.count[2]) return false;
+    for (int i = 1; i < K; ++i) {
+        if (i == hand_idx || i == ground_idx || i == support_idx) continue;
+        const int ni = (int)rec[REL_REC_HEADER + REL_REC_ENTITY * i + 1];
+        if (ni == 0) continue;
+        const bool near_hand = rel_rec_pair(rec, K, hand_idx, i) < th;
+        bool near_k[2];
+        for (int k = 0; k < 2; ++k)
+            near_k[k] = S.count[k] && on[k] != 0 &&
+                        (fresh[k] ? rel_rec_pair(rec, K, S.oindex[k], i) : rel_rec_cross(rec, K, S.oindex[k], i)) < th;
+        int take = -1;
+        if (S.count[0] == 0 && near_hand) take = 0;
+        else if (S.count[0] && S.count[1] == 0 && i != S.oindex[0]) {
+            if (near_hand || near_k[0]) take = 1;
+        } else if (S.count[1] && S.count[2] == 0 && i != S.oindex[0] && i != S.oindex[1]) {
+            bool ok;
+            if (support_idx >= 0) ok = near_hand || near_k[0] || near_k[1];
+            else if (on[1] > 0 && on[0] > 0) ok = near_hand || near_k[0] || near_k[1];
+            else if (on[1] > 0 && on[0] == 0) ok = near_hand || near_k[1];
+            else if (on[0] > 0 && on[1] == 0) ok = near_hand || near_k[0];
+            else ok = false;
+            if (ok) take = 2;
+        }
+        if (take >= 0) { S.oindex[take] = i; S.count[take] = 1; on[take] = ni; fresh[take] = true; changed = true; }
+    }
+    return changed;
+}

@@ -39,26 +39,9 @@ struct e2sec_resolver {
 
 static int rows_of(int relations) { return 10 * relations; }
 
-static RelEnt undefined_ent()
-{
-    RelEnt x;
-    memset(&x, 0, sizeof(x));
-    return x;
-}
-
-static RelEnt ent_from_record(const double *rec, int e, bool is_hand)
-{
-    const double *r = rec + E2SEC_REC_HEADER + E2SEC_REC_ENTITY * e;
-    RelEnt x;
-    x.defined = 1;
-    x.n = (int)r[1];
-    for (int k = 0; k < 3; ++k) {
-        x.lo[k] = r[7 + k];
-        x.hi[k] = r[10 + k];
-        x.center[k] = is_hand ? r[13 + k] : (x.lo[k] + x.hi[k]) * 0.5;
-    }
-    return x;
-}
+static RelEnt undefined_ent() { return rel_ent_undefined(); }
+static RelEnt ent_from_record(const double *rec, int e, bool is_hand) { return rel_ent_from_record(rec, e, is_hand); }
+static_assert(REL_REC_HEADER == E2SEC_REC_HEADER && REL_REC_ENTITY == E2SEC_REC_ENTITY, "record layout");
 
 extern "C" int e2sec_resolver_create(const e2sec_params *p, e2sec_resolver **out)
 {
@@ -145,36 +128,13 @@ static int process_record(e2sec_resolver *R, const double *rec)
     FrameView v{R, rec};
     const double th = R->p.thresh;
     const RelEnt hand = ent_from_record(rec, R->hand_idx, true);
-    bool fresh[3] = {false, false, false};
-    // ---- selection :1562-1658 ---------------------------------------------------------------------
-    // distance between the cloud currently bound to o_k and the frame's entity i: o_k is this frame's cloud when it was
-    // bound during this loop, otherwise still the cloud of the previous kept frame (:1669-1675 rebinds after the loop).
-    // np.min over an empty distance array raises in the reference; here an empty stale cloud is "far" (deviations)
-    auto near_o = [&](int k, int i) {
-        if (R->o[k].n == 0) return false;
-        return (fresh[k] ? v.pair(R->oindex[k], i) : v.cross(R->oindex[k], i)) < th;
-    };
-    for (int i = 0; i < K; ++i) {
-        if (i == R->hand_idx || i == R->ground_idx || i <= 0) continue;
-        if (R->support_idx >= 0 && i == R->support_idx) continue;
-        const RelEnt ci = ent_from_record(rec, i, false);
-        if (ci.n == 0) continue;
-        auto near_hand = [&]() { return v.pair(R->hand_idx, i) < th; };
-        auto take = [&](int k) { R->oindex[k] = i; R->count[k] = 1; R->o[k] = ci; fresh[k] = true; };
-        if (R->count[0] == 0 && near_hand()) take(0);
-        else if (R->o[0].defined && R->count[1] == 0 && i != R->oindex[0]) {
-            if (near_hand() || near_o(0, i)) take(1);
-        } else if (R->support_idx >= 0) {
-            if (R->o[1].defined && R->count[2] == 0 && i != R->oindex[0] && i != R->oindex[1])
-                if (near_hand() || near_o(0, i) || near_o(1, i)) take(2);
-        } else if (R->o[1].defined && R->count[2] == 0 && i != R->oindex[0] && i != R->oindex[1]) {
-            const int n1 = R->o[0].n, n2 = R->o[1].n;
-            bool ok = false;
-            if (n2 > 0 && n1 > 0) ok = near_hand() || near_o(0, i) || near_o(1, i);
-            else if (n2 > 0 && n1 == 0) ok = near_hand() || near_o(1, i);
-            else if (n1 > 0 && n2 == 0) ok = near_hand() || near_o(0, i);
-            if (ok) take(2);
-        }
+    // ---- selection :1562-1658 (relations.h: rel_select, shared with the device classifier) --------
+    {
+        RelSel S;
+        int stale_n[3];
+        for (int k = 0; k < 3; ++k) { S.oindex[k] = R->oindex[k]; S.count[k] = R->count[k]; stale_n[k] = R->o[k].n; }
+        rel_select(rec, K, R->hand_idx, R->ground_idx, R->support_idx, th, S, stale_n);
+        for (int k = 0; k < 3; ++k) { R->oindex[k] = S.oindex[k]; R->count[k] = S.count[k]; }
     }
     for (int k = 0; k < 3; ++k)                              // icp == False :1669-1675
         if (R->count[k] == 1) R->o[k] = ent_from_record(rec, R->oindex[k], false);
@@ -349,4 +309,27 @@ extern "C" int32_t e2sec_esec_to_e2sec(const char *codes, int32_t rows, int32_t 
         *n_final = (int)outv.size();
     }
     return C2;
+}
+
+// packed phase-2 columns (device classifier, possibly gathered from several shards) -> the table layout of
+// e2sec_resolver_table.  With relations 1 / 2 the table starts with the '-' column (:2252-2260) unless frame 0 itself
+// produced the first column (`if frame == 0: ESEC_table = add`, :1753 / :1778).
+extern "C" int32_t e2sec_columns_table(const uint8_t *columns, const int32_t *frames, int32_t n, int32_t relations, char *codes,
+                                       int32_t *final_columns)
+{
+    if (n < 0 || relations < 1 || relations > 3 || (n > 0 && (!columns || !frames))) return E2SEC_ERR_ARG;
+    const int rows = 10 * relations;
+    const int dash = (relations < 3 && !(n > 0 && frames[0] == 0)) ? 1 : 0;
+    const int total = n + dash;
+    if (!codes && !final_columns) return total;
+    for (int c = 0; c < total; ++c) {
+        for (int row = 0; codes && row < rows; ++row) {
+            char *dst = codes + ((size_t)row * total + c) * 6;
+            memset(dst, 0, 6);
+            const uint8_t code = (c < dash) ? (uint8_t)REL_DASH : columns[(size_t)(c - dash) * E2SEC_PHASE2_COLUMN_BYTES + row];
+            strncpy(dst, rel_code_name(code), 5);
+        }
+        if (final_columns) final_columns[c] = (c < dash) ? -1 : frames[c - dash];
+    }
+    return total;
 }

@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(E2_SEL_THREADS) axis_median_kernel(Dev d)
     const int fe = blockIdx.y, axis = blockIdx.x;
     const int f = fe / d.K, e = fe - f * d.K;
     const int off = d.ent_off[fe], n = d.ent_raw[fe];
-    if (off < 0 || n <= 3) return;    // :1520 -- only clouds with more than 3 points are filtered
+    if (off < 0 || !entity_filtered(d, fe, n)) return;    // :1520 -- only clouds with more than 3 points are filtered
     const double *src = (axis == 0 ? d.px : axis == 1 ? d.py : d.pz) + (size_t)f * d.cap + off;
     u64 v1, v2;
     u64 k2 = (u64)(n / 2), k1 = (n & 1) ? k2 : k2 - 1;

@@ -50,9 +50,9 @@ class Engine:
     def process_batch(self, xyz, labels, frame_ids, label_shape=None, image_shape=None):
         """xyz (F, N, 3) float32, labels (F, N) or (F, h, w) int32 (host numpy). -> records (F, rec) float64."""
         xyz = np.ascontiguousarray(xyz, np.float32)
-        F = xyz.shape[0]
         labels = np.asarray(labels)
-        fid = np.ascontiguousarray(frame_ids, np.int32)
+        fid = np.ascontiguousarray(frame_ids, np.int32).reshape(-1)
+        F = self._check_batch(xyz.shape, labels.shape, len(fid))
         rec = np.empty((F, nat.record_doubles(self.K)), np.float64)
         if labels.dtype == np.uint8:                   # uint8 label images travel as they are (13 B/point over PCIe)
             labels = np.ascontiguousarray(labels).reshape(F, -1)
@@ -87,12 +87,35 @@ class Engine:
                        1 if on_device else 0, ptr(records) if records is not None else None), "e2sec_process_batch_async")
         return records
 
+    def _check_batch(self, xyz_shape, labels_shape, n_ids):
+        """The C side copies n_frames * n_points * 3 floats from a raw pointer: every shape is checked here (the reference
+        fails with a shape error at np.column_stack, manipulation_analyser.py:1448, when cloud and labels disagree)."""
+        if self.n_points is None:
+            raise E2SecError("configure() has not been called")
+        if len(xyz_shape) != 3 or xyz_shape[2] != 3 or xyz_shape[1] != self.n_points:
+            raise ValueError("xyz must be (frames, %d, 3), got %r" % (self.n_points, tuple(xyz_shape)))
+        F = int(xyz_shape[0])
+        if F > self.max_frames:
+            raise ValueError("%d frames exceed max_frames=%d of configure()" % (F, self.max_frames))
+        if n_ids != F:
+            raise ValueError("%d frame ids for %d frames" % (n_ids, F))
+        if len(labels_shape) < 2 or labels_shape[0] != F:
+            raise ValueError("labels must be (frames, ...) with %d frames, got %r" % (F, tuple(labels_shape)))
+        return F
+
     def _shapes(self, label_size, label_shape, image_shape):
-        if label_size == self.n_points:
+        if label_size == self.n_points and label_shape is None:
             return label_size, 1, self.n_points, 1
         if label_shape is None or image_shape is None:
             raise ValueError("label image smaller than the cloud: pass label_shape=(rows, cols) and image_shape=(rows, cols)")
-        return int(label_shape[1]), int(label_shape[0]), int(image_shape[1]), int(image_shape[0])
+        lh, lw, h, w = int(label_shape[0]), int(label_shape[1]), int(image_shape[0]), int(image_shape[1])
+        if lh * lw != label_size:
+            raise ValueError("label_shape %r does not match the %d labels per frame" % ((lh, lw), label_size))
+        if h * w != self.n_points:
+            raise ValueError("image_shape %r does not match the %d points per frame" % ((h, w), self.n_points))
+        if label_size == self.n_points:
+            return label_size, 1, self.n_points, 1
+        return lw, lh, w, h
 
     def sync(self):
         self._check(lib.e2sec_sync(self._h), "e2sec_sync")
@@ -234,6 +257,115 @@ class Resolver:
         ab = np.zeros(3, np.int32)
         lib.e2sec_resolver_state(self._h, ptr(lab), ptr(ab))
         return lab.tolist(), ab.astype(bool).tolist()
+
+
+def columns_table(columns, frames, relations):
+    """Packed phase-2 columns (n, 32) uint8 + frame ids -> (codes (10 * relations, total) 'S5', frame id per column) in the
+    layout Resolver.table() gives (e2sec_columns_table: the initial '-' column of relations 1 / 2 included)."""
+    columns = np.ascontiguousarray(columns, np.uint8).reshape(-1, nat.PHASE2_COLUMN_BYTES)
+    frames = np.ascontiguousarray(frames, np.int32).reshape(-1)
+    n, rows = len(frames), 10 * int(relations)
+    total = int(lib.e2sec_columns_table(ptr(columns), ptr(frames), n, int(relations), None, None))
+    if total < 0:
+        raise E2SecError("e2sec_columns_table failed (%d)" % total)
+    codes = np.zeros((rows, max(total, 1), 6), np.uint8)
+    fc = np.zeros(max(total, 1), np.int32)
+    if total:
+        lib.e2sec_columns_table(ptr(columns), ptr(frames), n, int(relations), ptr(codes), ptr(fc))
+    arr = codes[:, :total].reshape(rows, total, 6).view("S6").reshape(rows, total).astype("S5")
+    return arr, fc[:total].tolist()
+
+
+class Phase2:
+    """Device phase 2 (csrc/phase2.cuh): selection, relation rows and column dedup as one kernel over records that stay in
+    device memory.  Belongs to a configured Engine; same outputs as Resolver."""
+
+    def __init__(self, engine, max_columns=65536):
+        h = C.c_void_p()
+        rc = lib.e2sec_phase2_create(engine._h, int(max_columns), C.byref(h))
+        if rc != 0:
+            raise E2SecError("e2sec_phase2_create failed (%d): %s" % (rc, lib.e2sec_last_error(engine._h).decode()))
+        self._h, self._eng = h, engine
+        self.K = engine.K
+        self.relations = int(engine._keep[0].relations) or 3
+        self.max_columns = int(max_columns)
+
+    def close(self):
+        if self._h:
+            lib.e2sec_phase2_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            if self._eng._h:
+                self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise E2SecError("%s failed (%d): %s" % (what, rc, lib.e2sec_last_error(self._eng._h).decode()))
+
+    def reset(self):
+        self._check(lib.e2sec_phase2_reset(self._h), "e2sec_phase2_reset")
+
+    def run(self, records_dev_ptr, n_frames, src=None):
+        """records_dev_ptr: device address of n_frames records; src: the Engine whose stream produces them (or None)."""
+        self._check(lib.e2sec_phase2_run(self._h, src._h if src is not None else None, C.c_void_p(int(records_dev_ptr)),
+                                         int(n_frames)), "e2sec_phase2_run")
+
+    def run_engine_batch(self, engine, n_frames, skip=0):
+        """Phase 2 of the batch `engine` has just queued (its device record buffer), dropping the first `skip` records."""
+        base = lib.e2sec_records_dev(engine._h)
+        self.run(base + skip * nat.record_doubles(self.K) * 8, n_frames - skip, src=engine)
+
+    def state_get(self, dst_ptr=None):
+        if dst_ptr is None:
+            buf = np.zeros(nat.PHASE2_STATE_BYTES, np.uint8)
+            self._check(lib.e2sec_phase2_state_get(self._h, ptr(buf)), "e2sec_phase2_state_get")
+            return buf
+        self._check(lib.e2sec_phase2_state_get(self._h, C.c_void_p(int(dst_ptr))), "e2sec_phase2_state_get")
+
+    def state_set(self, src):
+        if isinstance(src, np.ndarray):
+            src = np.ascontiguousarray(src, np.uint8)
+            self._check(lib.e2sec_phase2_state_set(self._h, ptr(src)), "e2sec_phase2_state_set")
+        else:
+            self._check(lib.e2sec_phase2_state_set(self._h, C.c_void_p(int(src))), "e2sec_phase2_state_set")
+
+    def sync(self):
+        n = C.c_int32()
+        self._check(lib.e2sec_phase2_sync(self._h, C.byref(n)), "e2sec_phase2_sync")
+        return n.value
+
+    def fetch(self):
+        """-> (packed columns (n, 32) uint8, frame ids (n,) int32) on the host."""
+        n = self.sync()
+        cols = np.zeros((max(n, 1), nat.PHASE2_COLUMN_BYTES), np.uint8)
+        fr = np.zeros(max(n, 1), np.int32)
+        got = C.c_int32()
+        self._check(lib.e2sec_phase2_fetch(self._h, ptr(cols), ptr(fr), max(n, 1), C.byref(got)), "e2sec_phase2_fetch")
+        return cols[:got.value], fr[:got.value]
+
+    def columns_dev(self):
+        c, f, n = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._check(lib.e2sec_phase2_columns_dev(self._h, C.byref(c), C.byref(f), C.byref(n)), "e2sec_phase2_columns_dev")
+        return c.value, f.value, n.value
+
+    def table(self):
+        """Same as Resolver.table()."""
+        cols, fr = self.fetch()
+        return columns_table(cols, fr, self.relations)
+
+    def state(self):
+        lab = np.zeros(3, np.int32)
+        ab = np.zeros(3, np.int32)
+        self._check(lib.e2sec_phase2_bindings(self._h, ptr(lab), ptr(ab)), "e2sec_phase2_bindings")
+        return lab.tolist(), ab.astype(bool).tolist()
+
+    @property
+    def stream(self):
+        return lib.e2sec_phase2_stream(self._h)
 
 
 def esec_to_e2sec_native(table, relations, final_columns):

@@ -11,7 +11,7 @@ fallback: without a CUDA device the first call raises.
 Scope notes:
   * frame-0 setup (_getGroundiNewNew :278-361, _getTranslation :212-276) is random in the reference and outside
     this path; its products are INPUTS here: call set_frame0(translation, roll, ground) before the first frame.
-  * icp=True (:1677-1738) and relations 1 / 2 are not implemented: they raise NotImplementedError.
+  * icp=True (:1677-1738) is not implemented: it raises NotImplementedError.  relations = 1, 2, 3 are.
   * debug=True writes the data behind the reference's debug PNGs (:1830-1998) as
     debug_images/<savename>/<frame>.json (AABBs, centres, relation codes) and prunes them to final_columns like
     _clean_debug_images (:160-173); matplotlib rendering is unavailable on this box.
@@ -30,6 +30,7 @@ IMAGE_SHAPE = (480, 640)            # :1390, :1433
 BATCH_FRAMES = 25
 
 final_columns = []
+column_frames = []                  # frame id of every raw eSEC column (-1: the initial '-' column), all relation modes
 total_unique_labels = 0
 hand_label_inarray = -1
 _frame0 = None
@@ -73,12 +74,17 @@ def read_frame(pcd_file, label_file):
     rc = nat.lib.e2sec_read_labels(os.fsencode(label_file), nat.ptr(lab), lab.shape[0], nat.C.byref(rows), nat.C.byref(cols))
     if rc != 0:
         raise IOError("cannot read %s (e2sec_read_labels -> %d)" % (label_file, rc))
-    return xyz[: w.value * h.value], lab[: rows.value * cols.value].reshape(rows.value, cols.value)
+    if w.value * h.value != xyz.shape[0]:
+        raise ValueError("%s holds %d x %d points, this path reads organised %d x %d clouds (:1433)"
+                         % (pcd_file, w.value, h.value, IMAGE_SHAPE[1], IMAGE_SHAPE[0]))
+    if rows.value < 1 or cols.value < 1 or rows.value > IMAGE_SHAPE[0] or cols.value > IMAGE_SHAPE[1]:
+        raise ValueError("%s: label image %d x %d does not fit %d x %d" % (label_file, rows.value, cols.value, *IMAGE_SHAPE))
+    return xyz, lab[: rows.value * cols.value].reshape(rows.value, cols.value)
 
 
 def _check_args(relations, icp, cython):
-    if relations != 3:
-        raise NotImplementedError("relations=%r: this path implements relations=3 (T/N + SSR + DSR)" % (relations,))
+    if relations not in (1, 2, 3):
+        raise ValueError("relations must be 1 (T/N), 2 (+ SSR) or 3 (+ DSR), got %r" % (relations,))
     if icp:
         raise NotImplementedError("icp=True (rigid-model tracking, manipulation_analyser.py:1677-1738) is outside this "
                                   "path; call with icp=False")
@@ -87,7 +93,7 @@ def _check_args(relations, icp, cython):
 
 
 def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
-                    thresh, max_frames, filter_mode, filter_seed):
+                    thresh, max_frames, filter_mode, filter_seed, relations=3):
     global _state, total_unique_labels, hand_label_inarray, final_columns
     if _frame0 is None:
         raise NotImplementedError("frame-0 setup (_getGroundiNewNew / _getTranslation) is outside this path: call "
@@ -98,7 +104,7 @@ def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old
     int(np.where(tul == ground_label)[0][0])
     T, R, ground = _frame0
     p, keep = nat.make_params(tul, hand_label, ground_label, support_hand, thresh, T, R, ground, replace=replace,
-                              old=old, new=new, filter_mode=filter_mode, filter_seed=filter_seed)
+                              old=old, new=new, filter_mode=filter_mode, filter_seed=filter_seed, relations=relations)
     if _state is not None:
         _state["engine"].close()
         _state["resolver"].close()
@@ -109,9 +115,12 @@ def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old
 
 
 def _table_from_resolver(relations):
-    global final_columns
+    """The raw eSEC table so far.  final_columns follows the reference: frame ids of the columns with relations == 3
+    (:1813-1829), left empty with relations 1 / 2 (those branches never append, :1744-1794); column_frames has them always."""
+    global final_columns, column_frames
     table, fc = _state["resolver"].table()
-    final_columns = list(fc)
+    column_frames = list(fc)
+    final_columns = list(fc) if relations == 3 else []
     if table.shape[1] == 0:
         t = np.chararray((10 * relations, 1), itemsize=5)
         t[:] = "-"
@@ -138,7 +147,7 @@ def _process(pcd_file, label_file, ground_label, hand_label, support_hand, trans
     xyz, label = read_frame(pcd_file, label_file)
     if frame == 0 or _state is None:
         _start_sequence(label, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
-                        thresh, 1, filter_mode, filter_seed)
+                        thresh, 1, filter_mode, filter_seed, relations)
     _run_batch(np.array([frame], np.int32), xyz[None], label.reshape(1, -1).astype(np.int32), label.shape)
     T, R, _ = _frame0
     return T, R, _table_from_resolver(relations)
@@ -193,7 +202,7 @@ def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, 
             xyz, label = read_frame(pcl_path + f[0:-7] + "_pc.pcd", label_path + f[0:-7] + "_left-labels.dat")
             if not started:
                 _start_sequence(label, ground_label, hand_label, support_hand, replace, old, new, ignored_labels,
-                                cut_labels, thresh, BATCH_FRAMES, filter_mode, filter_seed)
+                                cut_labels, thresh, BATCH_FRAMES, filter_mode, filter_seed, relations)
                 started = True
             xs.append(xyz)
             ls.append(label.reshape(-1).astype(np.int32))
@@ -201,9 +210,11 @@ def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, 
             lshape = label.shape
         _run_batch(np.array(ids, np.int32), np.stack(xs), np.stack(ls), lshape)
     table = _table_from_resolver(relations)
-    raw_columns = list(final_columns)
+    raw_columns = list(column_frames)
     if debug:
         for j, f in enumerate(raw_columns):
+            if f < 0:
+                continue
             with open("debug_images/%s/%d.json" % (savename, f), "w") as fh:
                 json.dump(_debug_artefact(f, _state["records"][f], table[:, j], _state["K"]), fh)
     e2sec, esec = esec_to_e2sec(table, relations)
