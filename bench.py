@@ -28,12 +28,18 @@ if ROOT not in sys.path:
 
 METRIC = "e2sec_frames_per_sec"
 UNIT = "frames/s"
-WIDTH, HEIGHT, N_OBJECTS, STREAM_CONFIG = 640, 480, 10, 2
-# dram__bytes_read.sum + dram__bytes_write.sum per frame of the dominant kernel of each stage, from the ncu --set full capture
-# of this workload (profiles/r1_v16_ncu_full_summary.csv: 400-frame launches): seg_stream_kernel + seg_emit_kernel,
-# cell_filter_kernel, contact_work_kernel
-NCU_TRAFFIC_PER_FRAME = {"segment": 8.334e6, "radius": 2.454e6, "pairs": 0.822e6}
-NCU_STREAM_KERNEL_PER_FRAME = 5.770e6      # seg_stream_kernel alone: 4.922 MB read (the input, once) + 0.848 MB written
+# BASELINE.json configs[1], [3], [4]: workload -> stream shape and the default step size
+CONFIGS = {
+    2: dict(width=640, height=480, objects=10, batch=400, pool=1200, cpu_frames=4, near=False,
+            name="synthetic 640x480 organised cloud stream, 10 labelled objects"),
+    4: dict(width=1280, height=720, objects=20, batch=120, pool=360, cpu_frames=1, near=True,
+            name="synthetic 1280x720 stream, 20 objects (190 pairs), neighbours within +-5 mm of thresh"),
+    5: dict(width=2000, height=1000, objects=30, batch=40, pool=120, cpu_frames=1, near=False,
+            name="synthetic 2M-point clouds (2000x1000), 30 objects (435 pairs)"),
+}
+# dram__bytes_read.sum + dram__bytes_write.sum per frame of each stage's kernels: written by tools/ncu_traffic.py from an
+# `ncu --set full` capture of this very command (profiles/ncu_traffic.json names the capture); absent -> traffic is null
+NCU_TRAFFIC_FILE = os.path.join(ROOT, "profiles", "ncu_traffic.json")
 BYTES_PER_POINT = 16                     # 12 B xyz float32 + 4 B int32 label, read once
 
 
@@ -43,12 +49,18 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=400, help="frames per step and per GPU (larger batches amortise kernel tails: 100 -> 72k, 400 -> 88k frames/s)")
-    ap.add_argument("--pool", type=int, default=1200, help="distinct frames resident per GPU (cycled)")
+    ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS), help="BASELINE.json workload: 2 = 640x480 / 10 objects "
+                    "(the metric's configuration), 4 = 1280x720 / 20 objects, 5 = 2M points / 30 objects")
+    ap.add_argument("--batch", type=int, default=0, help="frames per step and per GPU (0: the config's default; larger batches amortise kernel tails)")
+    ap.add_argument("--pool", type=int, default=0, help="distinct frames resident per GPU, cycled (0: the config's default)")
+    ap.add_argument("--blocks", type=int, default=30, help="the K-step block is repeated this often; value = median block (>= 1 s of timed work)")
+    ap.add_argument("--e2e-blocks", type=int, default=5)
+    ap.add_argument("--phase2", default="device", choices=["device", "host"],
+                    help="device: relation classifiers as a kernel behind every batch (phase2.cuh); host: the C++ resolver (one GPU only)")
     ap.add_argument("--filter-mode", default="closure", choices=["closure", "reference_seeded"])
     ap.add_argument("--radius-mode", default="bounded", choices=["bounded", "exact"],
                     help="bounded: cell-table bounds of np.median(pdist) with exact fallback; exact: always the O(n^2) selection")
-    ap.add_argument("--cpu-frames", type=int, default=4, help="frames of the cpu_baseline sample (0 = skip)")
+    ap.add_argument("--cpu-frames", type=int, default=-1, help="frames of the cpu_baseline sample (0 = skip, -1: the config's default)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--contexts", type=int, default=3,
                     help="contexts (streams) per GPU: batch i runs on context i %% C with its one-frame halo in front, so the "
@@ -58,8 +70,10 @@ def parse():
     return ap.parse_args()
 
 
-def workload_name():
-    return "synthetic %dx%d organised cloud stream, %d labelled objects" % (WIDTH, HEIGHT, N_OBJECTS)
+def make_stream(config):
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    c = CONFIGS[config]
+    return SyntheticStream(c["width"], c["height"], c["objects"], config=config, near_thresh=c["near"])
 
 
 # ---- CPU oracle legs (the only places bench.py touches oracle/) ------------------------------------------------------
@@ -80,9 +94,8 @@ def cpu_baseline_single(stream, first, n_frames, mode):
     return n_frames / dt, dt
 
 
-def _ref_worker(conn, wid, first, mode):
-    from manipulationlibrary_b200.synthetic import SyntheticStream
-    stream = SyntheticStream(WIDTH, HEIGHT, N_OBJECTS, config=STREAM_CONFIG)
+def _ref_worker(conn, wid, first, mode, config):
+    stream = make_stream(config)
     orc = _oracle_for(stream, mode)
     nxt = None
     while True:
@@ -110,7 +123,8 @@ def run_reference(args):
         cores = os.cpu_count() or 1
     try:                                          # one worker holds ~0.5 GB of pdist output at a time
         import psutil
-        cores = max(1, min(cores, int(psutil.virtual_memory().available / 2 ** 30 / 1.5)))
+        per_worker_gb = 1.5 * (CONFIGS[args.config]["width"] * CONFIGS[args.config]["height"]) / 307200.0
+        cores = max(1, min(cores, int(psutil.virtual_memory().available / 2 ** 30 / per_worker_gb)))
     except Exception:
         pass
     cores = min(cores, 64)
@@ -119,7 +133,7 @@ def run_reference(args):
     workers = []
     for w in range(cores):
         a, b = ctx.Pipe()
-        p = ctx.Process(target=_ref_worker, args=(b, w, 30 + w * span, args.filter_mode), daemon=True)
+        p = ctx.Process(target=_ref_worker, args=(b, w, 30 + w * span, args.filter_mode, args.config), daemon=True)
         p.start()
         workers.append((p, a, 30 + w * span))
 
@@ -150,7 +164,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(), "filter_mode": args.filter_mode, "frames_per_step": cores},
+        "config": {"workload": CONFIGS[args.config]["name"], "filter_mode": args.filter_mode, "frames_per_step": cores},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -213,12 +227,18 @@ def generate_pool(stream, first, count):
     return xyz, lab
 
 
+def ncu_traffic(config):
+    try:
+        return json.load(open(NCU_TRAFFIC_FILE)).get(str(config))
+    except Exception:
+        return None
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from manipulationlibrary_b200 import _native as nat
-    from manipulationlibrary_b200.engine import Engine, Resolver
-    from manipulationlibrary_b200.synthetic import SyntheticStream
+    from manipulationlibrary_b200.engine import Engine, Phase2, Resolver, columns_table
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -227,19 +247,29 @@ def run_b200(args):
         raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU arm)")
-    stream = SyntheticStream(WIDTH, HEIGHT, N_OBJECTS, config=STREAM_CONFIG)
-    B, K, W = args.batch, args.steps, args.warmup
+    if args.phase2 == "host" and world > 1:
+        raise SystemExit("bench.py: --phase2 host is the one-GPU comparison mode; several GPUs shard ONE sequence, which needs the device classifier")
+    cfg = CONFIGS[args.config]
+    stream = make_stream(args.config)
+    B, K, W = (args.batch or cfg["batch"]), args.steps, max(args.warmup, 1)
     N = stream.N
-    pool = max(B, min(args.pool, (K + W) * B))
-    pool = (pool // B) * B
-    rank_first = rank * (K + W) * B               # every rank owns its block of the stream (weak scaling)
+    pool = args.pool or cfg["pool"]
+    pool = max(B, (pool // B) * B)
+    seq = K * B                                   # frames of a timed block per GPU; all ranks' blocks are ONE sequence
+    cpu_frames = cfg["cpu_frames"] if args.cpu_frames < 0 else args.cpu_frames
 
     # cpu_baseline before the CUDA context exists on this rank (rank 0, N = 1 only)
-    cpu = None
-    if rank == 0 and world == 1 and args.cpu_frames > 0:
-        v, dt = cpu_baseline_single(stream, 30, args.cpu_frames, args.filter_mode)
-        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
-               "sample": "%d consecutive frames of the same stream, oracle.esec_oracle.E2SecOracle.process_frame, %.1f s" % (args.cpu_frames, dt)}
+    cpu, oracle_table = None, None
+    if rank == 0 and world == 1 and cpu_frames > 0:
+        orc = _oracle_for(stream, args.filter_mode)
+        frames = [stream.frame(30 + i) for i in range(cpu_frames)]
+        t0 = time.perf_counter()
+        for i, (xyz, lab) in enumerate(frames):
+            orc.process_frame(30 + i, xyz, lab.reshape(stream.H, stream.W))
+        dt = time.perf_counter() - t0
+        cpu = {"value": cpu_frames / dt, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": "%d consecutive frames of the same stream, oracle.esec_oracle.E2SecOracle.process_frame, %.1f s" % (cpu_frames, dt)}
+        oracle_table = (orc.table, list(orc.final_columns), frames)
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -250,9 +280,10 @@ def run_b200(args):
         saved_stdout = os.dup(1)
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
-    hx, hl = generate_pool(stream, rank_first, pool)
-    # one more frame in front: a copy of the pool's last frame, so that batch s can be handed over together with the frame
-    # before it (its halo) as one contiguous block even where the pool wraps
+    # rank r holds stream frames [r * pool, (r + 1) * pool); local frame j of a block has the content of pool frame j % pool.
+    # One more frame in front (a copy of the pool's last frame) so that a batch can be handed over together with the frame
+    # before it (its halo) as one contiguous block even where the pool wraps.
+    hx, hl = generate_pool(stream, rank * pool, pool)
     hx = np.concatenate([hx[-1:], hx])
     hl = np.concatenate([hl[-1:], hl])
     hx_t = torch.from_numpy(hx).pin_memory()
@@ -261,6 +292,13 @@ def run_b200(args):
     hl8_t = torch.from_numpy(hl.astype(np.uint8)).pin_memory() if lab8 else None     # what a uint8 label reader hands over
     dx = hx_t.to(dev, non_blocking=True)
     dl = hl_t.to(dev, non_blocking=True)
+    # the frame in front of this rank's block = the last frame of the previous rank's block (the shard's halo)
+    if rank > 0:
+        px_, pl_ = stream.frame((rank - 1) * pool + (seq - 1) % pool)
+        sx_t = torch.from_numpy(px_[None].copy()).pin_memory()
+        sl_t = torch.from_numpy(pl_[None].astype(np.int32)).pin_memory()
+        sl8_t = torch.from_numpy(pl_[None].astype(np.uint8)).pin_memory()
+        sdx, sdl = sx_t.to(dev), sl_t.to(dev)
     torch.cuda.synchronize()
 
     p, keep = nat.make_params(**stream.params(filter_mode=args.filter_mode, filter_seed=20261104,
@@ -270,31 +308,23 @@ def run_b200(args):
     for e in engs:
         e.configure(p, B + 1, N, keep)
     eng = engs[0]
+    est = torch.cuda.ExternalStream(eng.stream, device=dev)
     ests = [torch.cuda.ExternalStream(e.stream, device=dev) for e in engs]
-    est = ests[0]
     rec_w = nat.record_doubles(int(p.n_entities))
-    total_frames = (K + W) * B
-    # batch i writes rows [i, 1:]; row [i, 0] receives the record of its halo frame when the batch carries one
-    rec_host = torch.empty((K + W, B + 1, rec_w), dtype=torch.float64).pin_memory()
+    p2 = Phase2(eng, max_columns=seq + 8)
+    shard_rec = torch.empty((seq, rec_w), dtype=torch.float64, device=dev) if world > 1 else None
+    # e2e / host phase 2 / verification: the records of a block on the host, batch i in rows [i, 1:] (row [i, 0]: its halo frame)
+    rec_host = torch.empty((K, B + 1, rec_w), dtype=torch.float64).pin_memory()
     rec3 = rec_host.numpy()
-    ids_all = np.arange(rank_first, rank_first + total_frames, dtype=np.int32)
-    KEPT = float(nat.FLAG_HAND_LABEL | nat.FLAG_HAND_POINTS)
-    import threading
+    g0 = rank * seq                                # global index of this rank's first frame inside the block's sequence
+    ids_block = np.arange(g0 - 1, g0 + seq, dtype=np.int32)       # [0] = the halo frame's id
+    state_t = torch.zeros(nat.PHASE2_STATE_BYTES, dtype=torch.uint8, device=dev)
     from concurrent.futures import ThreadPoolExecutor
-    follower = ThreadPoolExecutor(max_workers=1)    # phase 2 follows the GPU on its own thread, in frame order
-    locks = [threading.Lock() for _ in engs]        # reset + queue on a context is one unit (the follower may redo a batch)
-    halo_of = {}                               # batch -> True when it was queued with its halo frame in front
+    follower = ThreadPoolExecutor(max_workers=1)
 
-    def inputs(on_device, first_frame):
-        """pointers to the frame with local index first_frame (pool position + 1 because of the leading copy)"""
-        s = first_frame % pool + 1
-        if on_device:
-            return dx[s].data_ptr(), dl[s].data_ptr()
-        return hx_t[s].data_ptr(), (hl8_t if lab8 else hl_t)[s].data_ptr()
-
-    def halo_inputs(on_device, batch_first):
-        """the block that starts one frame before batch_first: pool position batch_first % pool of the extended arrays"""
-        s = batch_first % pool
+    def inputs(on_device, first_local, halo):
+        """pointers to local frame first_local (minus one with its halo): pool position + 1 because of the leading copy"""
+        s = first_local % pool + (0 if halo else 1)
         if on_device:
             return dx[s].data_ptr(), dl[s].data_ptr()
         return hx_t[s].data_ptr(), (hl8_t if lab8 else hl_t)[s].data_ptr()
@@ -305,209 +335,206 @@ def run_b200(args):
         else:
             e.process_batch_device_async(px, pl, n, ids, N, records=out, on_device=False, labels8=lab8)
 
-    def step(i, on_device, seq_first):
-        """Queues batch i (frames i*B .. (i+1)*B-1 of this rank's block) on context i % C.  With one context the batches of
-        a sequence follow each other on its stream and the context carries the previous kept frame itself.  With several,
-        every batch is its own little sequence on its context: the frame before it goes in front as the halo (its record
-        lands in row 0 and is dropped) -- the same one-frame halo the frame sharding across GPUs uses."""
+    def step(i, on_device, want_host, phase2_dev):
+        """Batch i of the block (local frames i*B .. (i+1)*B-1) on context i % C.  With one context the batches follow each
+        other on its stream.  With several, every batch is its own little sequence on its context: the frame before it goes
+        in front as the halo (its record is dropped) -- the same one-frame halo the frame sharding across GPUs uses.  The
+        first batch of a shard (rank > 0) runs behind the previous rank's last frame."""
         c = i % C
         e = engs[c]
-        ids = ids_all[i * B: (i + 1) * B]
-        with locks[c]:
-            if C == 1 or i == seq_first:
-                if C > 1:
-                    e.reset_sequence()
-                px, pl = inputs(on_device, i * B)
-                queue(e, px, pl, B, ids, rec3[i, 1:], on_device)
-                halo_of[i] = False
+        skip = 0
+        if i == 0 or C > 1:
+            e.reset_sequence()
+        if i == 0:
+            if rank > 0:
+                if on_device:
+                    queue(e, sdx.data_ptr(), sdl.data_ptr(), 1, ids_block[:1], None, True)
+                else:
+                    queue(e, sx_t.data_ptr(), (sl8_t if lab8 else sl_t).data_ptr(), 1, ids_block[:1], None, False)
+            px, pl = inputs(on_device, 0, False)
+            queue(e, px, pl, B, ids_block[1: 1 + B], rec3[i, 1:] if want_host else None, on_device)
+        elif C == 1:
+            px, pl = inputs(on_device, i * B, False)
+            queue(e, px, pl, B, ids_block[1 + i * B: 1 + (i + 1) * B], rec3[i, 1:] if want_host else None, on_device)
+        else:
+            px, pl = inputs(on_device, i * B, True)
+            queue(e, px, pl, B + 1, ids_block[i * B: 1 + (i + 1) * B], rec3[i] if want_host else None, on_device)
+            skip = 1
+        if phase2_dev:
+            if world == 1:
+                p2.run_engine_batch(e, B + skip, skip=skip)         # the classifier follows the batch on its own stream
             else:
-                e.reset_sequence()
-                px, pl = halo_inputs(on_device, i * B)
-                queue(e, px, pl, B + 1, ids_all[i * B - 1: (i + 1) * B], rec3[i], on_device)
-                halo_of[i] = True
+                e.copy_records(shard_rec[i * B].data_ptr(), skip, B)  # the shard keeps its records for the chained phase 2
         return c
-
-    def settle(i, on_device, seq_first):
-        """batch i is on the host.  If its halo frame turned out not to be a kept frame (no hand in it), the previous kept
-        frame lies further back: redo the batch behind a walk back to it (sharding.run_shard's rule).  Rare, synchronous."""
-        if not halo_of.get(i) or rec3[i, 0, 1] == KEPT:
-            return
-        e = engs[i % C]
-        with locks[i % C]:
-            e.sync()
-            j = i * B - 2
-            one = np.empty((1, rec_w), np.float64)
-            while True:
-                e.reset_sequence()
-                if j < seq_first * B:
-                    break
-                px, pl = inputs(on_device, j)
-                queue(e, px, pl, 1, ids_all[j: j + 1], one, on_device)
-                e.sync()
-                if one[0, 1] == KEPT:
-                    break
-                j -= 1
-            px, pl = inputs(on_device, i * B)
-            queue(e, px, pl, B, ids_all[i * B: (i + 1) * B], rec3[i, 1:], on_device)
-            e.sync()
-
-    def sync_all():
-        for e in engs:
-            e.sync()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # N > 1: the records of batch i are all-gathered (NCCL, its own stream) while the GPUs work on batch i+1, and rank 0
-    # resolves the gathered batch a few steps behind ON THE LAUNCH THREAD: that wait is what keeps the ranks loosely in step
-    # (with free-running launches a rank's all-gather kernel sits on its SMs waiting for the slowest rank: 729 k instead of
-    # 766 k frames/s at 8 GPUs) -- every shard is its own sequence here, so the shards' resolvers run
-    # side by side (one C call each, the GIL is released).  No collective on the data path itself.
-    if world > 1:
-        gst = torch.cuda.Stream(device=dev)
-        gbuf = [torch.empty((B, rec_w), dtype=torch.float64, device=dev) for _ in range(2)]
-        gfull = [torch.empty((world * B, rec_w), dtype=torch.float64, device=dev) for _ in range(2)]
-        ghost = torch.empty((max(K, W, 1), world * B, rec_w), dtype=torch.float64).pin_memory()
-        ghost_np = ghost.numpy()
-        tpool = ThreadPoolExecutor(max_workers=min(world, os.cpu_count() or 1)) if rank == 0 else None
-
-    def pipelined_gather(on_device, first_step, n_steps):
-        resolvers = [Resolver(p, keep) for _ in range(world)] if rank == 0 else None
-        gdone, LAG = [], int(os.environ.get("E2SEC_BENCH_LAG", 2))      # measured at 2 GPUs: lag 1: 202.8 k, 2: 206.3 k, 3: 202.5 k, 6: 191.5 k, 9: 185.1 k frames/s
-
-        def feed(j):
-            if rank == 0:
-                list(tpool.map(lambda r: resolvers[r].feed(ghost_np[j, r * B: (r + 1) * B]), range(world)))
-
-        for i in range(n_steps):
-            c = step(first_step + i, on_device, first_step)
-            with torch.cuda.stream(ests[c]):
-                e = torch.cuda.Event()
-                e.record()
-            with torch.cuda.stream(gst):
-                gst.wait_event(e)                      # the batch's records are in the pinned host buffer
-                gbuf[i & 1].copy_(rec_host[first_step + i, 1:], non_blocking=True)
-                dist.all_gather_into_tensor(gfull[i & 1], gbuf[i & 1])
-                if rank == 0:
-                    ghost[i].copy_(gfull[i & 1], non_blocking=True)
-                ge = torch.cuda.Event()
-                ge.record()
-            gdone.append(ge)
-            if i >= LAG:                               # batches of slack: a rank that runs late does not stall the others
-                gdone[i - LAG].synchronize()
-                feed(i - LAG)
-        sync_all()
-        for i in range(n_steps):                       # every halo frame of the synthetic stream is a kept frame; say so if not
-            if halo_of.get(first_step + i) and rec3[first_step + i, 0, 1] != KEPT:
-                raise SystemExit("bench.py: batch %d starts behind a frame without a hand; run with --contexts 1" % (first_step + i))
-        for j in range(max(n_steps - LAG, 0), n_steps):
-            gdone[j].synchronize()
-            feed(j)
-        cols = 0
-        if rank == 0:
-            cols = sum(r.n_columns for r in resolvers)
-            for r in resolvers:
-                r.close()
-        return cols
-
-    def timed(on_device, first_step, n_steps):
-        ev0 = torch.cuda.Event(enable_timing=True)
-        ev1 = [torch.cuda.Event(enable_timing=True) for _ in engs]
+    def finish_device(out):
+        """End of a block with the device classifier: one GPU just waits for it; several chain the phase-2 state through
+        the shards in rank order (512 bytes each way) and gather the emitted columns on rank 0 -- the one collective."""
         for e in engs:
-            e.reset_sequence()              # the timed block is its own sequence (the resolver starts at its first frame)
+            e.sync()                                   # raises device-side errors of the queued batches
+        if world == 1:
+            n = p2.sync()
+            if out is not None:
+                out["columns"], out["frames"] = p2.fetch()
+            return n
+        if rank > 0:
+            dist.recv(state_t, src=rank - 1)
+            torch.cuda.current_stream().synchronize()
+            p2.state_set(state_t.data_ptr())
+        p2.run(shard_rec.data_ptr(), seq)
+        p2.state_get(state_t.data_ptr())
+        if rank < world - 1:
+            dist.send(state_t, dst=rank + 1)
+        cols, frames = p2.fetch()
+        cnt = torch.tensor([len(frames)], dtype=torch.int32, device=dev)
+        counts = torch.empty(world, dtype=torch.int32, device=dev)
+        dist.all_gather_into_tensor(counts, cnt)
+        counts = counts.cpu().numpy()
+        width = nat.PHASE2_COLUMN_BYTES + 4
+        pad = torch.zeros((max(int(counts.max()), 1), width), dtype=torch.uint8, device=dev)
+        if len(frames):
+            packed = np.concatenate([cols, frames.view(np.uint8).reshape(-1, 4)], axis=1)
+            pad[: len(frames)] = torch.from_numpy(packed).to(dev)
+        parts = [torch.empty_like(pad) for _ in range(world)] if rank == 0 else None
+        dist.gather(pad, parts, dst=0)
+        if rank != 0:
+            return 0
+        allp = np.concatenate([parts[r][: int(counts[r])].cpu().numpy() for r in range(world)])
+        if out is not None:
+            out["columns"] = np.ascontiguousarray(allp[:, : nat.PHASE2_COLUMN_BYTES])
+            out["frames"] = np.ascontiguousarray(allp[:, nat.PHASE2_COLUMN_BYTES:]).view(np.int32).reshape(-1)
+        return len(allp)
+
+    def block(on_device, want_host=False, out=None):
+        """One timed block = one sequence of world * K * B frames.  -> (device ms, wall ms, launches, columns)"""
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dev_p2 = args.phase2 == "device"
+        if dev_p2:
+            p2.reset()
         barrier()
         l0 = sum(e.launch_count for e in engs)
         t0 = time.perf_counter()
         with torch.cuda.stream(est):
-            ev0.record()                    # every stream is idle here (barrier); the last stream to finish ends the region
-        if world == 1:
-            # one GPU: phase 2 (host, sequential) follows the GPU on its own thread instead of after it, so that the launch
-            # thread keeps C batches in flight
+            ev0.record()                    # every stream is idle here (barrier)
+        if dev_p2:
+            for i in range(K):
+                step(i, on_device, want_host, True)
+            cols = finish_device(out)
+        else:
+            # the C++ resolver follows the GPU on its own thread, in frame order
             res = Resolver(p, keep)
             futs = []
 
             def follow(i, ev):
-                ev.synchronize()                       # batch i is on the host; the later ones keep the GPU busy meanwhile
-                settle(i, on_device, first_step)
+                ev.synchronize()
                 res.feed(rec3[i, 1:])
 
-            for i in range(n_steps):
-                c = step(first_step + i, on_device, first_step)
+            for i in range(K):
+                c = step(i, on_device, True, False)
                 with torch.cuda.stream(ests[c]):
                     e = torch.cuda.Event()
                     e.record()
-                futs.append(follower.submit(follow, first_step + i, e))
+                futs.append(follower.submit(follow, i, e))
                 if i >= 2 * C:
-                    futs[i - 2 * C].result()           # bounds how far the launches run ahead of phase 2
+                    futs[i - 2 * C].result()
             for f in futs:
                 f.result()
-            sync_all()                                 # raises device-side errors of the queued batches
+            for e in engs:
+                e.sync()
             cols = res.n_columns
+            if out is not None:
+                out["table"] = res.table()
             res.close()
-        else:
-            cols = pipelined_gather(on_device, first_step, n_steps)
-        for c in range(C):
-            with torch.cuda.stream(ests[c]):
-                ev1[c].record()
-        barrier()
+        torch.cuda.synchronize()
+        ev1.record()
+        ev1.synchronize()
         t1 = time.perf_counter()
-        ms = max(max(ev0.elapsed_time(e) for e in ev1), 0.0)
-        wall = (t1 - t0) * 1e3
-        t = torch.tensor([ms, wall], dtype=torch.float64, device=dev)
+        t = torch.tensor([ev0.elapsed_time(ev1), (t1 - t0) * 1e3], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t[0]), float(t[1]), sum(e.launch_count for e in engs) - l0, cols, (t0, t1)
 
-    for e in engs:
-        e.reset_sequence()
-    if world > 1:
-        pipelined_gather(True, 0, W)        # also brings up the NCCL communicator outside the timed region
-    else:
-        for i in range(W):
-            step(i, True, 0)
-    sync_all()
-    if saved_stdout is not None:            # the warm-up has run the first collectives: the banner is out
+    for _ in range(max(1, (W + K - 1) // K)):        # warm-up: whole blocks (>= W steps); also brings up the NCCL communicator
+        block(True)
+    if saved_stdout is not None:                    # the warm-up has run the first collectives: the banner is out
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
         os.close(saved_stdout)
     uuid = str(torch.cuda.get_device_properties(dev).uuid)
     sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if rank == 0 else None
     time.sleep(0.3 if sampler else 0.0)
-    ms, wall_ms, launches, cols, (t0, t1) = timed(True, W, K)
-    clocks = sampler.stop(t0, t1) if sampler else None
-    # the event pair brackets device work AND the host resolver between launches; wall is reported beside it
+    runs = [block(True) for _ in range(max(1, args.blocks))]
+    clocks = sampler.stop(runs[0][4][0], runs[-1][4][1]) if sampler else None
+    ms_all = sorted(r[0] for r in runs)
+    ms = statistics.median(ms_all)
+    wall_ms = statistics.median(r[1] for r in runs)
+    launches, cols = runs[-1][2], runs[-1][3]
     frames = K * B * world
     value = frames / (ms * 1e-3)
-    # how many filtered entities of the timed frames needed the exact O(n^2) path (radius field not NaN)
-    Kent = int(p.n_entities)
-    ent = rec3[W: W + K, 1:, nat.REC_HEADER: nat.REC_HEADER + nat.REC_ENTITY * Kent].reshape(-1, Kent, nat.REC_ENTITY)
+
+    # ---- checks outside the timed region (rank 0 decides; a failed check ends the run loudly) --------------------------
+    checks = {}
+    got = {}
+    block(True, want_host=True, out=got)
+    ent_w = nat.REC_ENTITY * int(p.n_entities)
+    ent = rec3[:, 1:, nat.REC_HEADER: nat.REC_HEADER + ent_w].reshape(-1, int(p.n_entities), nat.REC_ENTITY)
     n_filtered = int((ent[:, :, 2] >= 0).sum())
     n_exact = int(((ent[:, :, 2] >= 0) & ~np.isnan(ent[:, :, 3])).sum())
-    # stage split and the streaming kernel's own time: one more batch on one context with nothing else on the GPU
-    # (inside the timed region the stages of different batches overlap, their event pairs would count each other's work)
-    # -- three batches back to back, the last one's events are read (steady state, like the batches of the timed region)
+    if rank == 0 and world == 1:
+        # the device classifier against the C++ resolver on the very records of that block
+        res = Resolver(p, keep)
+        for i in range(K):
+            res.feed(rec3[i, 1:])
+        want_t, want_fc = res.table()
+        res.close()
+        got_t, got_fc = columns_table(got["columns"], got["frames"], 3) if args.phase2 == "device" else got["table"]
+        ok = got_t.shape == want_t.shape and bool((got_t == want_t).all()) and list(got_fc) == list(want_fc)
+        checks["phase2_equals_host_resolver"] = ok
+        if not ok:
+            raise SystemExit("bench.py: device phase 2 and the host resolver disagree on the block's records")
+        if oracle_table is not None:
+            # the cpu_baseline frames through the GPU: same raw table as the oracle produced
+            otab, ofc, oframes = oracle_table
+            n = len(oframes)
+            xs = np.stack([f[0] for f in oframes])
+            ls = np.stack([f[1].reshape(-1) for f in oframes]).astype(np.int32)
+            eng.reset_sequence()
+            r = eng.process_batch(xs, ls, np.arange(30, 30 + n, dtype=np.int32))
+            res = Resolver(p, keep)
+            res.feed(r)
+            t, fc = res.table()
+            res.close()
+            ok = (otab is None and t.shape[1] == 0) or (otab is not None and t.shape == otab.shape and
+                                                         bool((t.astype("U5") == otab).all()) and list(fc) == list(ofc))
+            checks["cpu_baseline_frames_equal_oracle"] = ok
+            if not ok:
+                raise SystemExit("bench.py: the GPU path and the oracle disagree on the cpu_baseline frames")
+
+    # stage split and the streaming kernel's own time: batches on one context with nothing else on the GPU (inside the
+    # timed region the stages of different batches overlap) -- three back to back, the last one's events are read
     eng.reset_sequence()
-    for i in range(W, W + 3):
-        px, pl = inputs(True, i * B)
-        queue(eng, px, pl, B, ids_all[i * B: (i + 1) * B], rec3[0, 1:], True)  # rows of a warm-up batch, no longer needed
+    for i in range(3):
+        px, pl = inputs(True, (i % (pool // B)) * B, False)
+        queue(eng, px, pl, B, ids_block[1 + (i % K) * B: 1 + (i % K + 1) * B], None, True)
     eng.sync()
     stages = eng.stage_ms()
 
     e2e = None
     if not args.no_e2e:
-        for e in engs:
-            e.reset_sequence()
-        for i in range(C):
-            step(i, False, 0)
-        sync_all()
-        ems, ewall, _, _, _ = timed(False, W, K)
+        block(False, want_host=True)
+        eruns = [block(False, want_host=True) for _ in range(max(1, args.e2e_blocks))]
+        ewall = statistics.median(r[1] for r in eruns)
         h2d_frames = B + (1 if C > 1 else 0)             # the halo frame travels with its batch
         e2e = {"value": frames / (ewall * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": h2d_frames * N * (13 if lab8 else BYTES_PER_POINT),
                "d2h_bytes_per_step": h2d_frames * rec_w * 8, "host_labels": "uint8" if lab8 else "int32",
-               "timing": "wall clock around the C-ABI calls, pinned host buffers"}
+               "blocks": len(eruns), "best": frames / (min(r[1] for r in eruns) * 1e-3),
+               "timing": "wall clock around the C-ABI calls of a block (median block), pinned host buffers, records back to the host"}
 
     if rank == 0:
         peaks = {}
@@ -517,41 +544,47 @@ def run_b200(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         which = "measured" if "hbm_gbs" in peaks else "fallback"
-        dom = max(stages, key=lambda k: stages[k])
+        dom = max(("segment", "radius", "pairs"), key=lambda k: stages.get(k, 0.0))
         dom_ms = stages[dom]
         alg = B * N * BYTES_PER_POINT
         achieved = alg / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None
         step_gbs = frames / world * N * BYTES_PER_POINT / (ms * 1e-3) / 1e9
+        tr = ncu_traffic(args.config) or {}
+        tr_stage = tr.get("stage_bytes_per_frame", {})
+        tr_stream = tr.get("stream_kernel_bytes_per_frame")
+        sk_ms = getattr(eng, "seg_stream_ms", 0)
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": workload_name(), "frames_per_step_per_gpu": B, "frames_timed": frames,
-                       "pool_frames_per_gpu": pool, "filter_mode": args.filter_mode, "radius_mode": args.radius_mode,
-                       "filtered_entities": n_filtered, "exact_path_entities": n_exact,
+            "config": {"workload": cfg["name"], "baseline_config": args.config, "frames_per_step_per_gpu": B,
+                       "frames_timed": frames, "pool_frames_per_gpu": pool, "filter_mode": args.filter_mode,
+                       "radius_mode": args.radius_mode, "filtered_entities": n_filtered, "exact_path_entities": n_exact,
                        "l2": "inputs larger than L2 (one step reads %d MB)" % (alg // 2 ** 20),
-                       "parallelism": ("frame-sharded x%d, records all-gathered per batch behind the GPU work" % world) if world > 1
-                       else "one GPU, host resolver following on its own thread",
-                       "contexts_per_gpu": C},
+                       "parallelism": ("one sequence of %d frames, frame-sharded x%d in contiguous blocks behind a one-frame halo; "
+                                       "phase-2 state chained through the shards, one gather of the emitted columns" % (frames, world))
+                       if world > 1 else "one GPU",
+                       "phase2": args.phase2, "contexts_per_gpu": C},
+            "timed_blocks": {"blocks": len(runs), "steps_per_block": K, "median_ms": ms, "best_ms": ms_all[0],
+                             "worst_ms": ms_all[-1], "best_value": frames / (ms_all[0] * 1e-3),
+                             "total_timed_s": sum(ms_all) * 1e-3},
             "clocks": clocks, "gpu_launches": launches, "wall_ms_per_step": wall_ms / K, "esec_columns": cols,
-            "stages_ms_solo_step": stages, "stages_ms_last_step": stages,
+            "checks": checks, "stages_ms_solo_step": stages,
             "roofline": {"bound": "hbm", "kernel": dom + " stage of one step", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                         "traffic": (NCU_TRAFFIC_PER_FRAME[dom] * B) if (dom in NCU_TRAFFIC_PER_FRAME and N == 307200) else None,
+                         "traffic": (tr_stage[dom] * B) if dom in tr_stage else None, "traffic_source": tr.get("capture"),
                          "peak_source": which, "whole_step_gbs_per_gpu": step_gbs, "whole_step_frac": step_gbs / peak,
-                         # the streaming kernel (label filter + compaction) is the HBM-bound one; the other two stages are
-                         # bound by O(cells^2) / O(n_a n_b) arithmetic on L2-resident data
                          # the one kernel that streams the input (label filter + compaction, seg_stream.cuh), timed alone with
-                         # its own event pair: this is the HBM-bound kernel of the path
-                         "streaming_kernel": ({"name": "seg_stream_kernel", "ms": eng.seg_stream_ms,
-                                               "algorithmic_gbs": alg / (eng.seg_stream_ms * 1e-3) / 1e9,
-                                               "frac": alg / (eng.seg_stream_ms * 1e-3) / 1e9 / peak,
-                                               "dram_gbs": (NCU_STREAM_KERNEL_PER_FRAME * B / (eng.seg_stream_ms * 1e-3) / 1e9)
-                                               if N == 307200 else None}
-                                              if getattr(eng, "seg_stream_ms", 0) > 0 else None),
+                         # its own event pair: this is the HBM-bound kernel of the path; the entity-level stages work on the
+                         # stored points out of L2
+                         "streaming_kernel": ({"name": "seg_stream_kernel", "ms": sk_ms,
+                                               "algorithmic_gbs": alg / (sk_ms * 1e-3) / 1e9,
+                                               "frac": alg / (sk_ms * 1e-3) / 1e9 / peak,
+                                               "dram_gbs": (tr_stream * B / (sk_ms * 1e-3) / 1e9) if tr_stream else None}
+                                              if sk_ms > 0 else None),
                          "stages": {k: {"ms": stages[k], "algorithmic_gbs": alg / (stages[k] * 1e-3) / 1e9,
                                         "frac": alg / (stages[k] * 1e-3) / 1e9 / peak,
-                                        "dram_gbs": (NCU_TRAFFIC_PER_FRAME[k] * B / (stages[k] * 1e-3) / 1e9) if N == 307200 else None}
+                                        "dram_gbs": (tr_stage[k] * B / (stages[k] * 1e-3) / 1e9) if k in tr_stage else None}
                                     for k in ("segment", "radius", "pairs") if stages.get(k, 0) > 0}},
         }
         if e2e:
@@ -559,6 +592,7 @@ def run_b200(args):
         if cpu:
             out["cpu_baseline"] = cpu
         print(json.dumps(out), flush=True)
+    p2.close()
     for e in engs:
         e.close()
     if world > 1:

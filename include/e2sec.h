@@ -141,6 +141,9 @@ int e2sec_process_batch_labels8_async(e2sec_ctx *ctx, const float *xyz, const ui
                                       int32_t label_w, int32_t label_h, int32_t width, int32_t height,
                                       const int32_t *frame_ids, int on_device, double *records);
 const double *e2sec_records_dev(e2sec_ctx *ctx);
+/* Stream-ordered copy of records [first, first + count) of the batch queued last to dst (host or device memory): a shard
+ * that keeps its records on the device for e2sec_phase2_run, minus the halo frame's.  Does not wait.                  */
+int e2sec_copy_records(e2sec_ctx *ctx, double *dst, int32_t first, int32_t count);
 /* Waits for the context's stream; returns the first device-side error of the batches queued since the last check. */
 int e2sec_sync(e2sec_ctx *ctx);
 /* number of kernels launched by this context so far (bench.py's gpu_launches) */

@@ -58,6 +58,7 @@ def _load():
         "e2sec_process_batch_labels8": (C.c_int, [vp, vp, vp, i32, i32, i32, i32, i32, vp, C.c_int, vp]),
         "e2sec_process_batch_labels8_async": (C.c_int, [vp, vp, vp, i32, i32, i32, i32, i32, vp, C.c_int, vp]),
         "e2sec_records_dev": (vp, [vp]),
+        "e2sec_copy_records": (C.c_int, [vp, vp, i32, i32]),
         "e2sec_sync": (C.c_int, [vp]),
         "e2sec_launch_count": (i64, [vp]),
         "e2sec_stage_ms": (C.c_int, [vp, vp]),

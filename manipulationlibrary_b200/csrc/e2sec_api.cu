@@ -714,6 +714,16 @@ extern "C" int e2sec_process_batch_labels8_async(e2sec_ctx *ctx, const float *xy
     return process_batch_impl(ctx, xyz, labels, 1, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, false);
 }
 
+extern "C" int e2sec_copy_records(e2sec_ctx *ctx, double *dst, int32_t first, int32_t count)
+{
+    if (!ctx || !dst || first < 0 || count < 0) return E2SEC_ERR_ARG;
+    if (!ctx->configured || first + count > ctx->maxF) return fail(ctx, E2SEC_ERR_ARG, "e2sec_copy_records: range outside the batch");
+    cudaSetDevice(ctx->device);
+    const size_t w = (size_t)ctx->d.rec_doubles * sizeof(double);
+    if (count) CU(cudaMemcpyAsync(dst, (const char *)ctx->records.p + (size_t)first * w, (size_t)count * w, cudaMemcpyDefault, ctx->stream));
+    return E2SEC_OK;
+}
+
 extern "C" int e2sec_stage_ms(e2sec_ctx *ctx, float out[8])
 {
     if (!ctx || !out) return E2SEC_ERR_ARG;

@@ -117,6 +117,14 @@ class Engine:
             return label_size, 1, self.n_points, 1
         return lw, lh, w, h
 
+    def copy_records(self, dst_ptr, first, count):
+        """Stream-ordered copy of records [first, first + count) of the batch queued last to host or device memory."""
+        self._check(lib.e2sec_copy_records(self._h, C.c_void_p(int(dst_ptr)), int(first), int(count)), "e2sec_copy_records")
+
+    @property
+    def records_dev(self):
+        return lib.e2sec_records_dev(self._h)
+
     def sync(self):
         self._check(lib.e2sec_sync(self._h), "e2sec_sync")
 
