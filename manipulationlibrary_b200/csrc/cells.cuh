@@ -43,7 +43,10 @@
 #define E2_CELL_EMPTY 0xffffffffu
 #define E2_CELL_JOIN (E2_CELL_MAX - 1)   // virtual cell of candidate points that were settled as members one by one
 #define E2_CELL_UMAX 256          // candidate points settled at point level before giving up
-#define E2_CELL_MCAP 512          // median selection: values ranked directly once the middle bin holds no more than this
+#define E2_CELL_MCAP 1024         // median selection: values ranked in shared memory once the middle bin holds no more than this
+#define E2_CELL_MSMALL 64         // ... directly once a sub-bin of it holds no more than this
+#define E2_CELL_HPAD(b) ((b) + ((b) >> 5))   // histogram slot of bin b: a lane that walks 32 consecutive bins meets 32 banks
+#define E2_CELL_HSIZE (E2_CELL_BINS + E2_CELL_BINS / 32)
 #define E2_M_DONE 0
 #define E2_M_HIST 1               // needs a histogram round over [m_lo, m_hi]
 #define E2_M_COLLECT 2            // both middle ranks in bin b1, few values: collect them
@@ -52,9 +55,9 @@
 
 struct CellSmem {
     union {
-        unsigned mhist[3][E2_CELL_BINS];      // M: per-axis value histograms of the median selection
+        unsigned mhist[3][E2_CELL_HSIZE];     // M: per-axis value histograms of the median selection
         unsigned keys[E2_CELL_HASH];          // B: cell ids
-        u64 hist[2][E2_CELL_BINS];            // C, D: weights by dmin2 / dmax2 bin
+        u64 hist[2][E2_CELL_HSIZE];           // C, D: weights by dmin2 / dmax2 bin
     };
     unsigned short cidx[E2_CELL_HASH];        // slot -> compact cell index
     unsigned cnt[E2_CELL_MAX];
@@ -64,10 +67,13 @@ struct CellSmem {
     };
     // M: state of the three selections
     double m_lo[3], m_hi[3], m_scale[3], m_a[3], m_b[3];
-    unsigned m_below[3], m_before[3], m_ccnt[3];
+    unsigned m_below[3], m_before[3], m_ccnt[3], m_scnt[3], m_sbef[3][2];
+    int m_sb[3][2];
+    double msmall[3][E2_CELL_MSMALL];         // M: values of the sub-bin(s) that hold the middle rank(s)
     u64 m_bef64[3];
     int m_mode[3], m_b1[3], m_b2[3];
-    double ebox[6];                           // AABB of the whole entity
+    double ebox[6];                           // value range of the entity per axis (exact, or its outward float32 box)
+    unsigned ebk[6];                          // union of the cell boxes as order-preserving keys
     unsigned char member[E2_CELL_MAX];
     unsigned short front[2][E2_CELL_MAX];
     unsigned short rest[E2_CELL_MAX];
@@ -84,15 +90,6 @@ struct CellSmem {
     double lo[3], inv_c, scale, d2max, t_lo, t_hi, r_lo, r_hi, seedp[3];
 };
 
-__device__ __forceinline__ unsigned f32_ord(float f)
-{
-    unsigned u = __float_as_uint(f);
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-__device__ __forceinline__ float ord_f32(unsigned u)
-{
-    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
-}
 __device__ __forceinline__ double next_down(double v) { return v > 0.0 ? __longlong_as_double(__double_as_longlong(v) - 1) : 0.0; }
 __device__ __forceinline__ double next_up(double v) { return __longlong_as_double(__double_as_longlong(v) + 1); }
 
@@ -190,25 +187,26 @@ __device__ __forceinline__ double cell_block_max(CellSmem &s, int slot, double v
 
 // One warp finds the bin holding 0-based rank k of a weighted histogram (cumulative weight > k). Returns
 // E2_CELL_BINS - 1 when the rank lies beyond the total (cannot happen: the weights sum to the pair count).
-template <class T>
+template <class T, int NB = E2_CELL_BINS>
 __device__ __forceinline__ int cell_rank_bin(const T *h, u64 k, u64 *before_out = nullptr)
 {
     const int lane = threadIdx.x & 31;
-    const int per = E2_CELL_BINS / 32;
+    const int per = NB / 32;
     u64 mine = 0;
-    for (int j = 0; j < per; ++j) mine += h[lane * per + j];
+#pragma unroll 8
+    for (int j = 0; j < per; ++j) mine += h[E2_CELL_HPAD(lane * per + j)];
     u64 incl = mine;
     for (int o = 1; o < 32; o <<= 1) { u64 t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
     const unsigned has = __ballot_sync(0xffffffffu, incl > k);
-    int bin = E2_CELL_BINS - 1;
+    int bin = NB - 1;
     if (has) {
         const int L = __ffs(has) - 1;
         const u64 before = __shfl_sync(0xffffffffu, incl - mine, L);
         if (lane == L) {
             u64 acc = before;
             for (int j = 0; j < per; ++j) {
-                acc += h[lane * per + j];
-                if (acc > k) { bin = lane * per + j; acc -= h[lane * per + j]; break; }
+                acc += h[E2_CELL_HPAD(lane * per + j)];
+                if (acc > k) { bin = lane * per + j; acc -= h[E2_CELL_HPAD(lane * per + j)]; break; }
             }
             if (before_out) *before_out = acc;          // weight strictly before the bin (written by one lane)
         }
@@ -217,6 +215,14 @@ __device__ __forceinline__ int cell_rank_bin(const T *h, u64 k, u64 *before_out 
     return bin;
 }
 
+
+// -DE2_CELL_PROFILE: thread 0 of every CTA adds the clock ticks of each phase to g_cell_prof (tools/cell_profile.py)
+#ifdef E2_CELL_PROFILE
+__device__ unsigned long long g_cell_prof[16];
+#define CELL_TICK(slot) do { if (threadIdx.x == 0) { const long long t_ = clock64(); atomicAdd(&g_cell_prof[slot], (unsigned long long)(t_ - prof_t)); prof_t = t_; } } while (0)
+#else
+#define CELL_TICK(slot) do { } while (0)
+#endif
 
 __device__ __forceinline__ int median_bin(double v, double lo, double scale)
 {
@@ -235,12 +241,20 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double *A[3] = {X, Y, Z};
+#ifdef E2_CELL_PROFILE
+    long long prof_t = clock64();
+#endif
     {
+        // the value range of every axis: the outward-rounded float32 box seg_emit_kernel left behind (Dev::ent_box), or a
+        // pass over the points when the entity came another way
+        const unsigned *eb = d.ent_box ? d.ent_box + (size_t)blockIdx.x * 6 : nullptr;
         double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
-        for (int i = tid; i < n; i += E2_CELL_THREADS)
-            for (int a = 0; a < 3; ++a) { const double v = A[a][i]; mn[a] = fmin(mn[a], v); mx[a] = fmax(mx[a], v); }
+        if (!eb)
+            for (int i = tid; i < n; i += E2_CELL_THREADS)
+                for (int a = 0; a < 3; ++a) { const double v = A[a][i]; mn[a] = fmin(mn[a], v); mx[a] = fmax(mx[a], v); }
         for (int a = 0; a < 3; ++a) {
-            const double l = cell_block_min(s, a, mn[a]), h = cell_block_max(s, 3 + a, mx[a]);
+            const double l = eb ? (double)ord_f32(eb[a]) : cell_block_min(s, a, mn[a]);
+            const double h = eb ? (double)ord_f32(eb[3 + a]) : cell_block_max(s, 3 + a, mx[a]);
             if (tid == 0) {
                 s.ebox[a] = l; s.ebox[3 + a] = h;
                 s.m_lo[a] = l; s.m_hi[a] = h; s.m_below[a] = 0;
@@ -250,8 +264,12 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
         }
     }
     __syncthreads();
+    CELL_TICK(9);
     const unsigned k2 = (unsigned)(n / 2), k1 = (n & 1) ? k2 : k2 - 1;
     for (int round = 0; round < 64; ++round) {
+#ifdef E2_CELL_PROFILE
+        if (tid == 0 && round > 0) atomicAdd(&g_cell_prof[15], 1ull);
+#endif
         int mode[3];
         double lo[3], hi[3], sc[3];
         for (int a = 0; a < 3; ++a) { mode[a] = s.m_mode[a]; lo[a] = s.m_lo[a]; hi[a] = s.m_hi[a]; sc[a] = s.m_scale[a]; }
@@ -259,7 +277,7 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
             for (int a = 0; a < 3; ++a) med[a] = (n & 1) ? s.m_a[a] : (s.m_a[a] + s.m_b[a]) / 2.0;     // numpy: mean of the two middle values
             return true;
         }
-        for (int i = tid; i < 3 * E2_CELL_BINS; i += E2_CELL_THREADS) (&s.mhist[0][0])[i] = 0;
+        for (int i = tid; i < 3 * E2_CELL_HSIZE; i += E2_CELL_THREADS) (&s.mhist[0][0])[i] = 0;
         if (tid < 3) s.m_ccnt[tid] = 0;
         __syncthreads();
         // ---- pass H: histograms (one shared atomic per distinct bin of a warp) ----------------------------------
@@ -273,11 +291,12 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
                 if (mode[a] != E2_M_HIST) continue;
-                if (i0 < n && v0[a] >= lo[a] && v0[a] <= hi[a]) atomicAdd(&s.mhist[a][median_bin(v0[a], lo[a], sc[a])], 1u);
-                if (i1 < n && v1[a] >= lo[a] && v1[a] <= hi[a]) atomicAdd(&s.mhist[a][median_bin(v1[a], lo[a], sc[a])], 1u);
+                if (i0 < n && v0[a] >= lo[a] && v0[a] <= hi[a]) { const int b = median_bin(v0[a], lo[a], sc[a]); atomicAdd(&s.mhist[a][E2_CELL_HPAD(b)], 1u); }
+                if (i1 < n && v1[a] >= lo[a] && v1[a] <= hi[a]) { const int b = median_bin(v1[a], lo[a], sc[a]); atomicAdd(&s.mhist[a][E2_CELL_HPAD(b)], 1u); }
             }
         }
         __syncthreads();
+        CELL_TICK(10);
         if (warp < 3 && mode[warp] == E2_M_HIST) {
             const int a = warp;
             const int b1 = cell_rank_bin(s.mhist[a], (u64)(k1 - s.m_below[a]), &s.m_bef64[a]);
@@ -288,9 +307,10 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
         if (tid < 3 && mode[tid] == E2_M_HIST) {
             const int a = tid, b1 = s.m_b1[a], b2 = s.m_b2[a];
             s.m_before[a] = (unsigned)s.m_bef64[a];                 // values of the range below bin b1
-            s.m_mode[a] = (b1 != b2) ? E2_M_SPLIT : (s.mhist[a][b1] <= E2_CELL_MCAP ? E2_M_COLLECT : E2_M_REFINE);
+            s.m_mode[a] = (b1 != b2) ? E2_M_SPLIT : (s.mhist[a][E2_CELL_HPAD(b1)] <= E2_CELL_MCAP ? E2_M_COLLECT : E2_M_REFINE);
         }
         __syncthreads();
+        CELL_TICK(11);
         // ---- pass R: resolve ---------------------------------------------------------------------------------------
         double tmin[3] = {1e300, 1e300, 1e300}, tmax[3] = {-1e300, -1e300, -1e300};
         int m2[3], b1[3], b2[3];
@@ -324,20 +344,82 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
             }
         }
         __syncthreads();
+        CELL_TICK(12);
+        // ---- rank the collected values (shared memory only).  Up to E2_CELL_MSMALL of them directly; more go through 256
+        // sub-bins of the bin first -- monotone in v like the bins themselves -- and only the sub-bin(s) of the two middle
+        // ranks are ranked directly.
+        auto subbin = [&](int a, double v) {
+            const double t = ((v - lo[a]) * sc[a] - (double)b1[a]) * 256.0;
+            return t >= 255.0 ? 255 : (t > 0.0 ? (int)t : 0);
+        };
+        bool big[3], any_big = false;
+        unsigned cc[3], r1[3], r2[3];
+        for (int a = 0; a < 3; ++a) {
+            cc[a] = (m2[a] == E2_M_COLLECT) ? s.m_ccnt[a] : 0u;
+            r1[a] = k1 - s.m_below[a] - s.m_before[a];
+            r2[a] = k2 - s.m_below[a] - s.m_before[a];
+            big[a] = cc[a] > E2_CELL_MSMALL;
+            any_big |= big[a];
+        }
+        if (any_big) {                                           // uniform: everything above comes from shared memory
+            __syncthreads();                                     // the bins' histogram has been read by everybody
+            for (int a = 0; a < 3; ++a)
+                if (big[a]) for (int i = tid; i < E2_CELL_HPAD(256) + 1; i += E2_CELL_THREADS) s.mhist[a][i] = 0;
+            if (tid < 3) s.m_scnt[tid] = 0;
+            __syncthreads();
+            for (int a = 0; a < 3; ++a)
+                if (big[a]) for (unsigned t = tid; t < cc[a]; t += E2_CELL_THREADS) atomicAdd(&s.mhist[a][E2_CELL_HPAD(subbin(a, s.mcand[a][t]))], 1u);
+            __syncthreads();
+            if (warp < 3 && big[warp]) {
+                const int a = warp;
+                u64 bef1 = 0, bef2 = 0;
+                const int sb1 = cell_rank_bin<unsigned, 256>(s.mhist[a], (u64)r1[a], &s.m_bef64[a]);
+                __syncwarp();
+                bef1 = s.m_bef64[a];
+                __syncwarp();
+                const int sb2 = cell_rank_bin<unsigned, 256>(s.mhist[a], (u64)r2[a], &s.m_bef64[a]);
+                __syncwarp();
+                bef2 = s.m_bef64[a];
+                if (lane == 0) { s.m_sb[a][0] = sb1; s.m_sb[a][1] = sb2; s.m_sbef[a][0] = (unsigned)bef1; s.m_sbef[a][1] = (unsigned)bef2; }
+            }
+            __syncthreads();
+            for (int a = 0; a < 3; ++a)
+                if (big[a]) for (unsigned t = tid; t < cc[a]; t += E2_CELL_THREADS) {
+                    const double v = s.mcand[a][t];
+                    const int sb = subbin(a, v);
+                    if (sb == s.m_sb[a][0] || sb == s.m_sb[a][1]) {
+                        const unsigned q = atomicAdd(&s.m_scnt[a], 1u);
+                        if (q < E2_CELL_MSMALL) s.msmall[a][q] = v;
+                    }
+                }
+            __syncthreads();
+        }
         for (int a = 0; a < 3; ++a) {
             if (m2[a] != E2_M_COLLECT) continue;
-            const unsigned c = s.m_ccnt[a];
-            const unsigned r1 = k1 - s.m_below[a] - s.m_before[a], r2 = k2 - s.m_below[a] - s.m_before[a];
-            for (unsigned t = tid; t < c; t += E2_CELL_THREADS) {
-                const double v = s.mcand[a][t];
-                unsigned rank = 0;
-                for (unsigned j = 0; j < c; ++j) { const double w = s.mcand[a][j]; rank += (w < v) || (w == v && j < t); }
-                if (rank == r1) s.m_a[a] = v;
-                if (rank == r2) s.m_b[a] = v;
+            const unsigned c = cc[a];
+            if (big[a] && s.m_scnt[a] <= E2_CELL_MSMALL) {
+                const unsigned cs = s.m_scnt[a];
+                for (unsigned t = tid; t < cs; t += E2_CELL_THREADS) {
+                    const double v = s.msmall[a][t];
+                    const int sb = subbin(a, v);
+                    unsigned rank = s.m_sbef[a][sb == s.m_sb[a][0] ? 0 : 1];
+                    for (unsigned j = 0; j < cs; ++j) { const double w = s.msmall[a][j]; rank += (subbin(a, w) == sb) && ((w < v) || (w == v && j < t)); }
+                    if (rank == r1[a]) s.m_a[a] = v;
+                    if (rank == r2[a]) s.m_b[a] = v;
+                }
+            } else {
+                for (unsigned t = tid; t < c; t += E2_CELL_THREADS) {
+                    const double v = s.mcand[a][t];
+                    unsigned rank = 0;
+                    for (unsigned j = 0; j < c; ++j) { const double w = s.mcand[a][j]; rank += (w < v) || (w == v && j < t); }
+                    if (rank == r1[a]) s.m_a[a] = v;
+                    if (rank == r2[a]) s.m_b[a] = v;
+                }
             }
             if (tid == 0) s.m_mode[a] = E2_M_DONE;
         }
         __syncthreads();
+        CELL_TICK(13);
     }
     if (tid == 0) atomicExch(d.error, E2SEC_ERR_STATE);
     return false;
@@ -384,6 +466,7 @@ __device__ __forceinline__ void cell_settle(CellSmem &s, const double *X, const 
 
 extern __shared__ __align__(16) unsigned char cell_smem_raw[];
 
+
 // grid F*K CTAs of E2_CELL_THREADS. Needs d.med (axis_median_kernel). Writes, for every filtered entity that it can
 // decide: seed_pos, flist, n_list, aabb, mean, rad_lo / rad_hi, amb = 0; for the others amb = 1 (exact path follows).
 // Entities that are not stored or have <= 3 points are finished here too (raw cloud, :1543-1546).
@@ -411,6 +494,9 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
     unsigned *flist = d.flist + pb;
     unsigned short *pcell = d.pcell + pb;
     const bool filtered = entity_filtered(d, fe, n);               // :1520
+#ifdef E2_CELL_PROFILE
+    long long prof_t = clock64();
+#endif
 
     if (FINISH) {
         // the cell closure of the first visit + the candidate points, settled at the exact float32 radius (pyx:35)
@@ -428,6 +514,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         double med[3];
         if (!cell_axis_medians(s, d, X, Y, Z, n, med)) return;
         if (tid < 3) d.med[(size_t)fe * 3 + tid] = med[tid];
+        CELL_TICK(0);
         const double cx = med[0], cy = med[1], cz = med[2];
         float bd = 50000.0f;
         int bi = 0x7fffffff;
@@ -448,11 +535,9 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; }
         }
         if (lane == 0) { s.best_d[warp] = bd; s.best_i[warp] = bi; }
-        double ext2 = 0.0, half[3];
+        double half[3];
         for (int k = 0; k < 3; ++k) {
             const double a = cell_block_sum(s, k, ad[k]);
-            const double l = s.ebox[k], h = s.ebox[3 + k];
-            ext2 += (h - l) * (h - l);
             half[k] = 3.5 * (a / (double)n);
         }
         if (tid == 0) {
@@ -463,21 +548,22 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             if (!(c > 1e-300) || !(c < 1e300)) c = 1.0;          // degenerate cloud: one cell
             s.inv_c = 1.0 / c;
             s.lo[0] = cx - half[0]; s.lo[1] = cy - half[1]; s.lo[2] = cz - half[2];
-            double top = ext2 * 1.000001;                        // d2 of any pair <= squared AABB diagonal (+ slack)
-            if (!(top > 0.0) || !(top < 1e300)) top = 1.0;
-            s.d2max = top;
-            s.scale = (double)E2_CELL_BINS / top;
+            for (int k = 0; k < 3; ++k) { s.ebk[k] = 0xffffffffu; s.ebk[3 + k] = 0u; }
             s.m = 0; s.overflow = 0; s.amb = 0;
         }
         for (int i = tid; i < E2_CELL_HASH; i += E2_CELL_THREADS) s.keys[i] = E2_CELL_EMPTY;
         __syncthreads();
 
+        CELL_TICK(1);
         // ---- B1: insert the cell ids ------------------------------------------------------------------------------
-        const double l0 = s.lo[0], l1 = s.lo[1], l2 = s.lo[2], inv_c = s.inv_c;
+        // (which cell a point lands in is free -- the boxes are built from the points themselves -- so the grid coordinate
+        // is float32 arithmetic: a third of the instructions of the float64 floor / clamp)
+        const double l0 = s.lo[0], l1 = s.lo[1], l2 = s.lo[2];
+        const float inv_cf = (float)s.inv_c;
         for (int i = tid; i < n; i += E2_CELL_THREADS) {
-            const double tx = fmin(fmax(floor((X[i] - l0) * inv_c), -1.0), (double)E2_CELL_G);
-            const double ty = fmin(fmax(floor((Y[i] - l1) * inv_c), -1.0), (double)E2_CELL_G);
-            const double tz = fmin(fmax(floor((Z[i] - l2) * inv_c), -1.0), (double)E2_CELL_G);
+            const float tx = fminf(fmaxf(floorf((float)(X[i] - l0) * inv_cf), -1.0f), (float)E2_CELL_G);
+            const float ty = fminf(fmaxf(floorf((float)(Y[i] - l1) * inv_cf), -1.0f), (float)E2_CELL_G);
+            const float tz = fminf(fmaxf(floorf((float)(Z[i] - l2) * inv_cf), -1.0f), (float)E2_CELL_G);
             const unsigned id = ((unsigned)((int)tx + 1) << 10) | ((unsigned)((int)ty + 1) << 5) | (unsigned)((int)tz + 1);
             unsigned slot = (id * 2654435761u) >> 20;
             int probes = 0;
@@ -516,44 +602,45 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
 
     bool decided = true;
     if (!FINISH && filtered && !s.overflow) {
-        // ---- B3: per-cell count and outward-rounded float box (warp-aggregated shared atomics) -----------------
-        for (int i = tid; i < 2 * E2_CELL_BINS; i += E2_CELL_THREADS) (&s.hist[0][0])[i] = 0;      // keys are dead now
-        for (int base = 0; base < n; base += E2_CELL_THREADS) {
-            const int i = base + tid;
-            const bool live = i < n;
-            unsigned c = 0xffffffffu;
-            unsigned v[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
-            if (live) {
-                c = s.cidx[pcell[i]];
-                pcell[i] = (unsigned short)c;
-                const double x = X[i], y = Y[i], z = Z[i];
-                v[0] = f32_ord(__double2float_rd(x)); v[1] = f32_ord(__double2float_rd(y)); v[2] = f32_ord(__double2float_rd(z));
-                v[3] = f32_ord(__double2float_ru(x)); v[4] = f32_ord(__double2float_ru(y)); v[5] = f32_ord(__double2float_ru(z));
-            }
-            unsigned todo = __ballot_sync(0xffffffffu, live);
-            while (todo) {
-                const int leader = __ffs(todo) - 1;
-                const unsigned cl = __shfl_sync(0xffffffffu, c, leader);
-                const unsigned mask = __ballot_sync(0xffffffffu, live && c == cl);
-                if (live && c == cl) {
-                    unsigned r[6];
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) { r[k] = __reduce_min_sync(mask, v[k]); r[3 + k] = __reduce_max_sync(mask, v[3 + k]); }
-                    if (lane == leader) {
-                        atomicAdd(&s.cnt[cl], (unsigned)__popc(mask));
-#pragma unroll
-                        for (int k = 0; k < 3; ++k) { atomicMin(&s.box[k][cl], r[k]); atomicMax(&s.box[3 + k][cl], r[3 + k]); }
-                    }
-                }
-                todo &= ~mask;
-            }
+        CELL_TICK(2);
+        // ---- B3: per-cell count and outward-rounded float box ----------------------------------------------------
+        for (int i = tid; i < 2 * E2_CELL_HSIZE; i += E2_CELL_THREADS) (&s.hist[0][0])[i] = 0;     // keys are dead now
+        // one native shared atomic per quantity and point: the points of a warp (raster neighbours) fall into ~8 cells, a
+        // 4-way conflict costs far fewer issue slots than the match / reduce loop it replaces (21 % of the kernel before)
+        for (int i = tid; i < n; i += E2_CELL_THREADS) {
+            const unsigned c = s.cidx[pcell[i]];
+            pcell[i] = (unsigned short)c;
+            const double x = X[i], y = Y[i], z = Z[i];
+            atomicAdd(&s.cnt[c], 1u);
+            atomicMin(&s.box[0][c], f32_ord(__double2float_rd(x)));
+            atomicMin(&s.box[1][c], f32_ord(__double2float_rd(y)));
+            atomicMin(&s.box[2][c], f32_ord(__double2float_rd(z)));
+            atomicMax(&s.box[3][c], f32_ord(__double2float_ru(x)));
+            atomicMax(&s.box[4][c], f32_ord(__double2float_ru(y)));
+            atomicMax(&s.box[5][c], f32_ord(__double2float_ru(z)));
         }
         __syncthreads();
         const int m = (int)s.m;
+        // (the union of the cell boxes = the entity's outward float32 box: the same numbers whichever way the entity got
+        // here, so the bounds below do not depend on the segmentation path)
         for (int i = tid; i < m; i += E2_CELL_THREADS)
-            for (int k = 0; k < 6; ++k) s.box[k][i] = __float_as_uint(ord_f32(s.box[k][i]));
+            for (int k = 0; k < 6; ++k) {
+                const unsigned o = s.box[k][i];
+                if (k < 3) atomicMin(&s.ebk[k], o); else atomicMax(&s.ebk[k], o);
+                s.box[k][i] = __float_as_uint(ord_f32(o));
+            }
+        __syncthreads();
+        if (tid == 0) {
+            double ext2 = 0.0;
+            for (int k = 0; k < 3; ++k) { const double e = (double)ord_f32(s.ebk[3 + k]) - (double)ord_f32(s.ebk[k]); ext2 += e * e; }
+            double top = ext2 * 1.000001;                        // d2 of any pair <= squared AABB diagonal (+ slack)
+            if (!(top > 0.0) || !(top < 1e300)) top = 1.0;
+            s.d2max = top;
+            s.scale = (double)E2_CELL_BINS / top;
+        }
         __syncthreads();
 
+        CELL_TICK(3);
         // ---- C: cell-pair histograms over d^2 ----------------------------------------------------------------------
         // Weights are pair counts: while the entity has fewer than 2^32 pairs the bins are 32-bit words (native shared
         // atomics; a 64-bit shared atomicAdd is a compare-and-swap loop and collapses under the contention of the
@@ -571,17 +658,18 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
                 if (a == b) dmin2 = 0.0;
                 if (w) {
                     const int b0 = cell_bin(dmin2, scale), b1 = cell_bin(dmax2, scale);
-                    if (small) { atomicAdd(&h32[b0], (unsigned)w); atomicAdd(&h32[E2_CELL_BINS + b1], (unsigned)w); }
-                    else { atomicAdd(&s.hist[0][b0], w); atomicAdd(&s.hist[1][b1], w); }
+                    if (small) { atomicAdd(&h32[E2_CELL_HPAD(b0)], (unsigned)w); atomicAdd(&h32[E2_CELL_HSIZE + E2_CELL_HPAD(b1)], (unsigned)w); }
+                    else { atomicAdd(&s.hist[0][E2_CELL_HPAD(b0)], w); atomicAdd(&s.hist[1][E2_CELL_HPAD(b1)], w); }
                 }
             }
         }
         __syncthreads();
 
+        CELL_TICK(4);
         // ---- D: lo <= median <= hi ---------------------------------------------------------------------------------
         if (warp < 2) {
             const u64 k2 = P / 2, k1 = (P & 1) ? k2 : k2 - 1;
-            const int B = small ? cell_rank_bin(h32 + warp * E2_CELL_BINS, warp == 0 ? k1 : k2)
+            const int B = small ? cell_rank_bin(h32 + warp * E2_CELL_HSIZE, warp == 0 ? k1 : k2)
                                 : cell_rank_bin(s.hist[warp], warp == 0 ? k1 : k2);
             if (lane == 0) {
                 if (warp == 0) {
@@ -607,6 +695,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         if (tid == 64) { s.seedp[0] = X[s.seed]; s.seedp[1] = Y[s.seed]; s.seedp[2] = Z[s.seed]; s.n_front = 0; s.n_new = 0; s.n_cand = 0; }
         __syncthreads();
 
+        CELL_TICK(5);
         // ---- E: cell closure at r_lo ---------------------------------------------------------------------------------
         const double t_lo = s.t_lo, t_hi = s.t_hi;
         const float t_lo32 = __double2float_rd(t_lo), t_hi32 = __double2float_ru(t_hi);     // conservative float32 copies of the thresholds
@@ -640,6 +729,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             cur ^= 1;
             __syncthreads();
         }
+        CELL_TICK(6);
         // ---- F: can anything else be reached at r_hi? --------------------------------------------------------------
         // Candidate cells: non-members within r_hi of a member or of another candidate (transitively).  Cells that are
         // not candidates cannot be reached at any radius <= r_hi, whatever happens to the candidates.
@@ -678,6 +768,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
                 if (!s.joined[u] && s.udist[u] <= t_hi) s.amb = 4;      // reachable at r_hi but not at r_lo
         }
         __syncthreads();
+        CELL_TICK(7);
         decided = !s.amb;
     } else if (!FINISH && filtered) {
         decided = false;                                           // too many cells for the table
@@ -704,16 +795,26 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
     }
 
     // ---- G: stable compaction of the members + AABB / mean / count (unfiltered clouds: every point) ------------
+    // Every warp owns a contiguous run of the entity's points: count its members, one block-wide exchange of the twelve
+    // counts, then place them from the warp's own offset -- no barrier per 384 points.
     double sum[3] = {0.0, 0.0, 0.0}, mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
-    unsigned run = 0;
-    for (int base = 0; base < n; base += E2_CELL_THREADS) {
-        const int i = base + tid;
-        const bool mem = (i < n) && (!filtered || s.member[pcell[i]]);
+    const int chunk = ((n + E2_CELL_WARPS - 1) / E2_CELL_WARPS + 31) & ~31;
+    const int c0 = min(n, warp * chunk), c1 = min(n, c0 + chunk);
+    unsigned mine = (unsigned)(c1 - c0);
+    if (filtered) {
+        mine = 0;
+        for (int i = c0 + lane; i < c1; i += 32) mine += s.member[pcell[i]] ? 1u : 0u;
+        mine = __reduce_add_sync(0xffffffffu, mine);
+    }
+    __syncthreads();                                   // s.wcnt may still be read by phase B2 of a slow warp
+    if (lane == 0) s.wcnt[warp] = mine;
+    __syncthreads();
+    unsigned run = 0, before = 0;
+    for (int w = 0; w < E2_CELL_WARPS; ++w) { const unsigned c = s.wcnt[w]; if (w < warp) before += c; run += c; }
+    for (int base = c0; base < c1; base += 32) {
+        const int i = base + lane;
+        const bool mem = (i < c1) && (!filtered || s.member[pcell[i]]);
         const unsigned bal = __ballot_sync(0xffffffffu, mem);
-        if (lane == 0) s.wcnt[warp] = __popc(bal);
-        __syncthreads();
-        unsigned before = run, tot = 0;
-        for (int w = 0; w < E2_CELL_WARPS; ++w) { const unsigned c = s.wcnt[w]; if (w < warp) before += c; tot += c; }
         if (mem) {
             flist[before + __popc(bal & ((1u << lane) - 1u))] = (unsigned)i;
             const double x = X[i], y = Y[i], z = Z[i];
@@ -722,16 +823,23 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             mn[1] = fmin(mn[1], y); mx[1] = fmax(mx[1], y);
             mn[2] = fmin(mn[2], z); mx[2] = fmax(mx[2], z);
         }
-        run += tot;
-        __syncthreads();
+        before += __popc(bal);
     }
-    double tot[3], l[3], h[3];
+    // nine block reductions behind ONE barrier: warp partials to shared memory, thread 0 folds them in warp order
     for (int k = 0; k < 3; ++k) {
-        tot[k] = cell_block_sum(s, k, sum[k]);
-        l[k] = cell_block_min(s, 3 + k, mn[k]);
-        h[k] = cell_block_max(s, 6 + k, mx[k]);
+        double v = sum[k];
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        const double lo_k = warp_min_d(mn[k]), hi_k = warp_max_d(mx[k]);
+        if (lane == 0) { s.red[k][warp] = v; s.red[3 + k][warp] = lo_k; s.red[6 + k][warp] = hi_k; }
     }
+    __syncthreads();
+    CELL_TICK(8);
     if (tid == 0) {
+        double tot[3], l[3], h[3];
+        for (int k = 0; k < 3; ++k) {
+            tot[k] = 0.0; l[k] = 1e300; h[k] = -1e300;
+            for (int w = 0; w < E2_CELL_WARPS; ++w) { tot[k] += s.red[k][w]; l[k] = fmin(l[k], s.red[3 + k][w]); h[k] = fmax(h[k], s.red[6 + k][w]); }
+        }
         d.n_list[fe] = (int)run;
         d.seed_pos[fe] = filtered ? s.seed : -1;
         double cntp = (double)run;

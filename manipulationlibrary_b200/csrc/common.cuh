@@ -60,6 +60,9 @@ struct Dev {
     const int *frame_ids;             // F
     // segmentation
     unsigned *seg_cnt;                // F x S x K   valid points of entity e in segment s (becomes offsets)
+    unsigned *ent_box;                // F x K x 6   float32 box of every entity's TRANSFORMED points rounded outward, as order-
+                                      //             preserving keys (min x,y,z, max x,y,z): written by seg_emit_kernel, null when
+                                      //             the entities were produced another way
     int *ent_raw;                     // F x K       valid points per entity
     int *ent_off;                     // F x K       offset of the entity's points in the frame's storage (-1: not stored)
     int *flags;                       // F           E2SEC_FLAG_*
@@ -137,6 +140,17 @@ __device__ __forceinline__ double dist2(double ax, double ay, double az, double 
 {
     double dx = ax - bx, dy = ay - by, dz = az - bz;
     return (dx * dx + dy * dy) + dz * dz;
+}
+
+// order-preserving 32-bit key of a float32 and back
+__device__ __forceinline__ unsigned f32_ord(float f)
+{
+    unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord_f32(unsigned u)
+{
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
 
 // total order key of a float64 for radix selection

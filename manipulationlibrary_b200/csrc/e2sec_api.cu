@@ -53,7 +53,7 @@ struct e2sec_ctx {
     DevBuf xyz_stage, lab_stage, rowmap, colmap, lut, frame_ids, seg_cnt, ent_raw, ent_off, flags, px, py, pz,
         pidx, med, radius, rs, hist, cand, cand_n, seed_pos, member, front_a, front_b, flist, n_list, aabb, mean,
         gx, gy, gz, pair_key, cross_key, records, error, plan_off, plan_total, below_acc, min_above, single_count,
-        frame_used, prev_slot, prev_id, halo_info, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next, ct_map, seg_list, seg_len, seg_next;
+        frame_used, prev_slot, prev_id, halo_info, ent_box, pcell, rad_lo, rad_hi, amb, ct_cnt, ct_off, ct_next, ct_map, seg_list, seg_len, seg_next;
     int map_cfg[4] = {0, 0, 0, 0};
     int64_t launches = 0;
     cudaEvent_t ev[10];            // [0..7] stage boundaries, [8] / [9] around the streaming segmentation kernel
@@ -155,7 +155,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
                  &ctx->gz, &ctx->pair_key, &ctx->records, &ctx->error, &ctx->plan_off, &ctx->plan_total,
                  &ctx->below_acc, &ctx->min_above, &ctx->single_count, &ctx->cross_key, &ctx->frame_used, &ctx->prev_slot,
-                 &ctx->prev_id, &ctx->halo_info, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->ct_map, &ctx->seg_list, &ctx->seg_len, &ctx->seg_next,
+                 &ctx->prev_id, &ctx->halo_info, &ctx->ent_box, &ctx->pcell, &ctx->rad_lo, &ctx->rad_hi, &ctx->amb, &ctx->ct_cnt, &ctx->ct_off, &ctx->ct_next, &ctx->ct_map, &ctx->seg_list, &ctx->seg_len, &ctx->seg_next,
                  &ctx->ds_codes, &ctx->ds_off, &ctx->ds_ncols, &ctx->ds_packed, &ctx->ds_counts, &ctx->ds_D};
     *out = ctx;
     return E2SEC_OK;
@@ -221,6 +221,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     if ((rc = ensure(ctx, ctx->frame_ids, F * sizeof(int)))) return rc;
     if ((rc = ensure(ctx, ctx->seg_cnt, (size_t)F * S * K * sizeof(unsigned)))) return rc;
     if ((rc = ensure(ctx, ctx->ent_raw, FK * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->ent_box, FK * 6 * sizeof(unsigned)))) return rc;
     if ((rc = ensure(ctx, ctx->ent_off, FK * sizeof(int)))) return rc;
     if ((rc = ensure(ctx, ctx->flags, F * sizeof(int)))) return rc;
     if ((rc = ensure(ctx, ctx->px, cap * sizeof(double)))) return rc;
@@ -636,8 +637,10 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labe
     // single-pass cluster kernel when the bulk copies can be issued (16-byte aligned frames), else the two-pass kernels
     const bool fused = !ctx->force_two_pass && (N % 4 == 0) && ((uintptr_t)d.xyz % 16 == 0) && ((uintptr_t)d.labels % 16 == 0) &&
                        (upscale || d.label_size % 4 == 0) && N <= (1 << 26);
+    d.ent_box = nullptr;
     if (fused && !ctx->seg_cluster) {
         // unit stream: persistent warps pull 2048-point units, then a per-frame scan and one warp per unit to emit
+        d.ent_box = (unsigned *)ctx->ent_box.p;
         Dev du = d;
         du.S = (N + E2_SS_UNIT - 1) / E2_SS_UNIT;
         unsigned *next = (unsigned *)ctx->seg_next.p;
@@ -1212,3 +1215,14 @@ extern "C" int e2sec_phase2_bindings(e2sec_phase2 *q, int32_t labels[3], int32_t
 }
 
 extern "C" void *e2sec_phase2_stream(e2sec_phase2 *q) { return q ? (void *)q->stream : nullptr; }
+
+#ifdef E2_CELL_PROFILE
+// debugging aid (not in e2sec.h): clock ticks per phase of cell_filter_kernel summed over CTAs; reset != 0 clears them
+extern "C" int e2sec_debug_cell_profile(unsigned long long out[16], int reset)
+{
+    cudaDeviceSynchronize();
+    if (out && cudaMemcpyFromSymbol(out, g_cell_prof, sizeof(unsigned long long) * 16) != cudaSuccess) return E2SEC_ERR_CUDA;
+    if (reset) { unsigned long long z[16] = {0}; if (cudaMemcpyToSymbol(g_cell_prof, z, sizeof(z)) != cudaSuccess) return E2SEC_ERR_CUDA; }
+    return E2SEC_OK;
+}
+#endif

@@ -68,6 +68,9 @@ __global__ void __launch_bounds__(E2_SS_THREADS, E2_SS_CTAS) seg_stream_kernel(D
         const int e = raw < E2SEC_LABEL_LUT ? __ldg(d.lut + raw) : -1;
         s.lut8[raw] = (unsigned char)(e < 0 ? 0u : e == 0 ? E2_SF_ZERO : e == gi ? E2_SF_GROUND : (unsigned)e);
     }
+    if (d.ent_box)                                             // the boxes seg_emit_kernel accumulates: min keys up, max keys down
+        for (size_t i = (size_t)blockIdx.x * E2_SS_THREADS + tid; i < (size_t)d.F * K * 6; i += (size_t)gridDim.x * E2_SS_THREADS)
+            d.ent_box[i] = (i % 6 < 3) ? 0xffffffffu : 0u;
     __syncthreads();
 
     unsigned phase = 0;                                        // tiles this warp has consumed so far (ring position / parity)
@@ -262,8 +265,10 @@ __global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned
         __syncwarp();
         if (e >= 0 && lane == __ffs(peers) - 1) wc[warp][e] += __popc(peers);
         __syncwarp();
-        if (e >= 0 && pos < (unsigned)d.cap) {
-            double X = (double)__uint_as_float(rec.x), Y = (double)__uint_as_float(rec.y), Z = (double)__uint_as_float(rec.z);
+        const bool place = e >= 0 && pos < (unsigned)d.cap;
+        double X = 0.0, Y = 0.0, Z = 0.0;
+        if (place) {
+            X = (double)__uint_as_float(rec.x); Y = (double)__uint_as_float(rec.y); Z = (double)__uint_as_float(rec.z);
             if (((rec.x & 0x7fffffffu) == 0x7f800000u) | ((rec.y & 0x7fffffffu) == 0x7f800000u) | ((rec.z & 0x7fffffffu) == 0x7f800000u)) {
                 X = widen(__uint_as_float(rec.x)); Y = widen(__uint_as_float(rec.y)); Z = widen(__uint_as_float(rec.z));   // +-inf -> +-DBL_MAX (:1445), rare
             }
@@ -278,6 +283,30 @@ __global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned
             d.py[fb + pos] = Y;
             d.pz[fb + pos] = Z;
             d.pidx[fb + pos] = rec.w >> 6;
+        }
+        if (d.ent_box) {
+            // float32 box of the entity, rounded outward: the value range cell_filter_kernel's median selection starts from
+            // (saves it a pass over the points).  One reduction per entity present in the row, six fire-and-forget atomics.
+            unsigned k[6];
+            k[0] = f32_ord(__double2float_rd(X)); k[1] = f32_ord(__double2float_rd(Y)); k[2] = f32_ord(__double2float_rd(Z));
+            k[3] = f32_ord(__double2float_ru(X)); k[4] = f32_ord(__double2float_ru(Y)); k[5] = f32_ord(__double2float_ru(Z));
+            unsigned todo = __ballot_sync(0xffffffffu, place);
+            while (todo) {
+                const int leader = __ffs(todo) - 1;
+                const int el = __shfl_sync(0xffffffffu, e, leader);
+                const unsigned mask = __ballot_sync(0xffffffffu, place && e == el);
+                if (place && e == el) {
+                    unsigned r[6];
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) { r[q] = __reduce_min_sync(mask, k[q]); r[3 + q] = __reduce_max_sync(mask, k[3 + q]); }
+                    if (lane == leader) {
+                        unsigned *b = d.ent_box + ((size_t)f * K + el) * 6;
+#pragma unroll
+                        for (int q = 0; q < 3; ++q) { atomicMin(b + q, r[q]); atomicMax(b + 3 + q, r[3 + q]); }
+                    }
+                }
+                todo &= ~mask;
+            }
         }
     }
 }

@@ -2,6 +2,7 @@
 
     python oracle/gen_records_golden.py            # tests/golden/pushing06_records_<mode>.npz
     python oracle/gen_records_golden.py --synth    # tests/golden/synth_records_closure.npz (16 frames, 640x480x10)
+    python oracle/gen_records_golden.py --large    # tests/golden/synth_records_config{2,4,5}.npz (full-size frames of configs 4 / 5)
 
 Pushing_06: oracle.records.RecordOracle over the 75 processed frames of tests/golden/pushing06_frames.npz with the
 frame-0 fixture; the O(n^2) np.median(pdist()) values are the ones the reference's own run passed to
@@ -61,8 +62,31 @@ def synth(first=28, count=16):
                         first=np.int64(first), count=np.int64(count))
 
 
+def large(cfg):
+    """BASELINE configs 4 / 5 at FULL frame size (1280x720 / 20 objects, 2000x1000 / 30 objects): two consecutive frames
+    (the second one carries the cross table), and config 2 deep inside the benchmark's range (frames 777, 778)."""
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    import time
+    w, h, n_obj, first = {4: (1280, 720, 20, 30), 5: (2000, 1000, 30, 30), 2: (640, 480, 10, 777)}[cfg]
+    s = SyntheticStream(width=w, height=h, n_objects=n_obj, config=cfg, near_thresh=(cfg == 4))
+    orc = eo.E2SecOracle(s.ground_label, s.hand_label, None, s.thresh, s.translation, s.roll, s.ground,
+                         s.total_unique_labels, filter_mode="closure", seed=SEED)
+    ro = RecordOracle(orc)
+    recs = []
+    for f in range(first, first + 2):
+        t0 = time.time()
+        xyz, lab = s.frame(f)
+        recs.append(ro.frame_record(f, xyz, lab))
+        print("config", cfg, "frame", f, "%.1f s" % (time.time() - t0), flush=True)
+    np.savez_compressed(os.path.join(GOLD, "synth_records_config%d.npz" % cfg), records=np.array(recs),
+                        first=np.int64(first), count=np.int64(2), shape=np.array([w, h, n_obj, cfg], np.int64))
+
+
 if __name__ == "__main__":
-    if "--synth" in sys.argv:
+    if "--large" in sys.argv:
+        for c in (2, 4, 5):
+            large(c)
+    elif "--synth" in sys.argv:
         synth()
     else:
         for m in ("closure", "reference_seeded"):

@@ -390,6 +390,24 @@ def test_large_configs_bounded_equals_exact(engine, shape):
                 assert (a[7:10] <= a[4:7] + 1.0).all()
 
 
+@pytest.mark.parametrize("cfg", [2, 4, 5])
+def test_full_size_configs_equal_oracle_golden(engine, cfg):
+    """BASELINE configs 4 and 5 at FULL frame size (and config 2 deep inside the benchmark's frame range) against records
+    the CPU oracle produced (oracle/gen_records_golden.py --large; minutes of pdist per frame, hence committed): two
+    consecutive frames, so the second one carries the cross table against the first.  Both radius modes."""
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    z = load_golden("synth_records_config%d" % cfg)
+    w, h, n_obj, c = (int(v) for v in z["shape"])
+    assert c == cfg
+    s = SyntheticStream(width=w, height=h, n_objects=n_obj, config=cfg, near_thresh=(cfg == 4))
+    ids = np.arange(int(z["first"]), int(z["first"]) + int(z["count"]))
+    recs, _, _ = _records_both_modes(engine, s, ids, len(ids))
+    K = len(s.total_unique_labels)
+    st = compare_records(recs["exact"], z["records"], K, s.thresh)
+    assert st["filtered"] == len(ids) * (n_obj + 1)
+    compare_records(recs["bounded"], z["records"], K, s.thresh, radius_exact=False)
+
+
 # ---- the drop-in Python surface ---------------------------------------------------------------------
 def _write_sequence(tmp, frames, every=3):
     """Pushing_06 fixture frames as files named like the MANIAC recordings: <stem>_pc.pcd (binary PCD) and
