@@ -68,6 +68,7 @@ struct CellSmem {
     // M: state of the three selections
     double m_lo[3], m_hi[3], m_scale[3], m_a[3], m_b[3];
     unsigned m_below[3], m_before[3], m_ccnt[3], m_scnt[3], m_sbef[3][2];
+    int m_fb[3];                              // round-0 bin an axis was refined into (-1: none): its values are the only live ones
     int m_sb[3][2];
     double msmall[3][E2_CELL_MSMALL];         // M: values of the sub-bin(s) that hold the middle rank(s)
     u64 m_bef64[3];
@@ -192,29 +193,25 @@ __device__ __forceinline__ int cell_rank_bin(const T *h, u64 k, u64 *before_out 
 {
     const int lane = threadIdx.x & 31;
     const int per = NB / 32;
+    static_assert(per <= 32, "one lane per bin in the second level");
     u64 mine = 0;
 #pragma unroll 8
     for (int j = 0; j < per; ++j) mine += h[E2_CELL_HPAD(lane * per + j)];
     u64 incl = mine;
     for (int o = 1; o < 32; o <<= 1) { u64 t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
     const unsigned has = __ballot_sync(0xffffffffu, incl > k);
-    int bin = NB - 1;
-    if (has) {
-        const int L = __ffs(has) - 1;
-        const u64 before = __shfl_sync(0xffffffffu, incl - mine, L);
-        if (lane == L) {
-            u64 acc = before;
-            for (int j = 0; j < per; ++j) {
-                acc += h[E2_CELL_HPAD(lane * per + j)];
-                if (acc > k) { bin = lane * per + j; acc -= h[E2_CELL_HPAD(lane * per + j)]; break; }
-            }
-            if (before_out) *before_out = acc;          // weight strictly before the bin (written by one lane)
-        }
-        bin = __shfl_sync(0xffffffffu, bin, L);
-    }
-    return bin;
+    if (!has) return NB - 1;
+    // second level: the bins of the first lane whose running total passes k, one bin per lane
+    const int L = __ffs(has) - 1;
+    const u64 before = __shfl_sync(0xffffffffu, incl - mine, L);
+    const u64 w = lane < per ? (u64)h[E2_CELL_HPAD(L * per + lane)] : 0ull;
+    u64 inc2 = w;
+    for (int o = 1; o < 32; o <<= 1) { u64 t = __shfl_up_sync(0xffffffffu, inc2, o); if (lane >= o) inc2 += t; }
+    const unsigned has2 = __ballot_sync(0xffffffffu, lane < per && before + inc2 > k);
+    const int J = has2 ? __ffs(has2) - 1 : per - 1;
+    if (before_out && lane == J) *before_out = before + inc2 - w;      // weight strictly before the bin (written by one lane)
+    return L * per + J;
 }
-
 
 // -DE2_CELL_PROFILE: thread 0 of every CTA adds the clock ticks of each phase to g_cell_prof (tools/cell_profile.py)
 #ifdef E2_CELL_PROFILE
@@ -237,7 +234,9 @@ __device__ __forceinline__ int median_bin(double v, double lo, double scale)
 // Two passes over the points per round; planar clouds (one axis with a tiny spread next to far outliers) take two
 // rounds on that axis, everything else one.  Also leaves the entity's AABB in s.ebox.  Returns false (after raising
 // the device error flag) if a selection does not converge -- only non-finite coordinate spans can do that.
-__device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, const double *Y, const double *Z, int n, double med[3])
+// pbin: one scratch word per point.  Round 0 leaves every point's three bins there (10 bits each); the resolve pass and any
+// later round read that word first and touch a coordinate only where its bin is the one in question.
+__device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, const double *Y, const double *Z, unsigned *pbin, int n, double med[3])
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double *A[3] = {X, Y, Z};
@@ -257,7 +256,7 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
             const double h = eb ? (double)ord_f32(eb[3 + a]) : cell_block_max(s, 3 + a, mx[a]);
             if (tid == 0) {
                 s.ebox[a] = l; s.ebox[3 + a] = h;
-                s.m_lo[a] = l; s.m_hi[a] = h; s.m_below[a] = 0;
+                s.m_lo[a] = l; s.m_hi[a] = h; s.m_below[a] = 0; s.m_fb[a] = -1;
                 if (h > l) { s.m_scale[a] = (double)E2_CELL_BINS / (h - l); s.m_mode[a] = E2_M_HIST; }
                 else { s.m_a[a] = s.m_b[a] = l; s.m_mode[a] = E2_M_DONE; }
             }
@@ -283,16 +282,34 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
         // ---- pass H: histograms (one shared atomic per distinct bin of a warp) ----------------------------------
         // (values spread over 1024 bins: plain shared atomics beat a match_any aggregation; the three loads of a point are
         // issued together, two points per thread in flight)
-        for (int base = 0; base < n; base += 2 * E2_CELL_THREADS) {
-            const int i0 = base + tid, i1 = i0 + E2_CELL_THREADS;
-            double v0[3], v1[3];
+        int fb[3];
+        for (int a = 0; a < 3; ++a) fb[a] = s.m_fb[a];
+        if (round == 0) {
+            for (int base = 0; base < n; base += 2 * E2_CELL_THREADS) {
+                const int i0 = base + tid, i1 = i0 + E2_CELL_THREADS;
+                double v0[3], v1[3];
 #pragma unroll
-            for (int a = 0; a < 3; ++a) { v0[a] = (i0 < n) ? A[a][i0] : 0.0; v1[a] = (i1 < n) ? A[a][i1] : 0.0; }
+                for (int a = 0; a < 3; ++a) { v0[a] = (i0 < n) ? A[a][i0] : 0.0; v1[a] = (i1 < n) ? A[a][i1] : 0.0; }
+                unsigned p0 = 0, p1 = 0;
 #pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                if (mode[a] != E2_M_HIST) continue;
-                if (i0 < n && v0[a] >= lo[a] && v0[a] <= hi[a]) { const int b = median_bin(v0[a], lo[a], sc[a]); atomicAdd(&s.mhist[a][E2_CELL_HPAD(b)], 1u); }
-                if (i1 < n && v1[a] >= lo[a] && v1[a] <= hi[a]) { const int b = median_bin(v1[a], lo[a], sc[a]); atomicAdd(&s.mhist[a][E2_CELL_HPAD(b)], 1u); }
+                for (int a = 0; a < 3; ++a) {
+                    if (mode[a] != E2_M_HIST) continue;             // a degenerate axis: bin 0 everywhere, never asked for
+                    // (the range is the entity's own box: every value lies inside)
+                    if (i0 < n) { const int b = median_bin(v0[a], lo[a], sc[a]); atomicAdd(&s.mhist[a][E2_CELL_HPAD(b)], 1u); p0 |= (unsigned)b << (10 * a); }
+                    if (i1 < n) { const int b = median_bin(v1[a], lo[a], sc[a]); atomicAdd(&s.mhist[a][E2_CELL_HPAD(b)], 1u); p1 |= (unsigned)b << (10 * a); }
+                }
+                if (i0 < n) pbin[i0] = p0;
+                if (i1 < n) pbin[i1] = p1;
+            }
+        } else {
+            for (int i = tid; i < n; i += E2_CELL_THREADS) {
+                const unsigned pk = pbin[i];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    if (mode[a] != E2_M_HIST || (int)((pk >> (10 * a)) & 1023u) != fb[a]) continue;
+                    const double v = A[a][i];
+                    if (v >= lo[a] && v <= hi[a]) { const int b = median_bin(v, lo[a], sc[a]); atomicAdd(&s.mhist[a][E2_CELL_HPAD(b)], 1u); }
+                }
             }
         }
         __syncthreads();
@@ -316,16 +333,35 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
         int m2[3], b1[3], b2[3];
         for (int a = 0; a < 3; ++a) { m2[a] = (mode[a] == E2_M_HIST) ? s.m_mode[a] : E2_M_DONE; b1[a] = s.m_b1[a]; b2[a] = s.m_b2[a]; }
         for (int i = tid; i < n; i += E2_CELL_THREADS) {
-            double vv[3];
-#pragma unroll
-            for (int a = 0; a < 3; ++a) vv[a] = A[a][i];
+            const unsigned pk = pbin[i];
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
                 if (m2[a] == E2_M_DONE) continue;
-                const double v = vv[a];
-                if (!(v >= lo[a] && v <= hi[a])) continue;
-                const int bin = median_bin(v, lo[a], sc[a]);
-                if (m2[a] == E2_M_COLLECT) { if (bin == b1[a]) s.mcand[a][atomicAdd(&s.m_ccnt[a], 1u)] = v; }
+                const int bin0 = (int)((pk >> (10 * a)) & 1023u);
+                int bin;
+                double v;
+                if (round == 0) {                                 // the cached bins are this round's bins
+                    if (bin0 != b1[a] && !(m2[a] == E2_M_SPLIT && bin0 == b2[a])) continue;
+                    bin = bin0;
+                    v = A[a][i];
+                } else {
+                    if (bin0 != fb[a]) continue;                  // outside the refined bin: outside [lo, hi]
+                    v = A[a][i];
+                    if (!(v >= lo[a] && v <= hi[a])) continue;
+                    bin = median_bin(v, lo[a], sc[a]);
+                }
+                if (m2[a] == E2_M_COLLECT) {
+                    // one counter bump per warp and axis: the middle bin of a flat face holds hundreds of raster neighbours,
+                    // and a returning atomic on ONE shared word serialises them across the whole CTA
+                    if (bin == b1[a]) {
+                        const unsigned peers = __activemask();
+                        const int leader = __ffs(peers) - 1;
+                        unsigned base = 0;
+                        if (lane == leader) base = atomicAdd(&s.m_ccnt[a], (unsigned)__popc(peers));
+                        base = __shfl_sync(peers, base, leader);
+                        s.mcand[a][base + __popc(peers & ((1u << lane) - 1u))] = v;
+                    }
+                }
                 else if (m2[a] == E2_M_REFINE) { if (bin == b1[a]) { tmin[a] = fmin(tmin[a], v); tmax[a] = fmax(tmax[a], v); } }
                 else { if (bin == b1[a]) tmax[a] = fmax(tmax[a], v); else if (bin == b2[a]) tmin[a] = fmin(tmin[a], v); }
             }
@@ -336,6 +372,7 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
             if (tid == 0) {
                 if (m2[a] == E2_M_SPLIT) { s.m_a[a] = h; s.m_b[a] = l; s.m_mode[a] = E2_M_DONE; }
                 else {
+                    if (round == 0) s.m_fb[a] = b1[a];
                     s.m_below[a] += s.m_before[a];
                     s.m_lo[a] = l; s.m_hi[a] = h;
                     if (h > l && (double)E2_CELL_BINS / (h - l) < 1e300) { s.m_scale[a] = (double)E2_CELL_BINS / (h - l); s.m_mode[a] = E2_M_HIST; }
@@ -512,7 +549,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         // ---- A: seed, mean absolute deviation, AABB ------------------------------------------------------------
         // ---- M: per-axis medians = the seed target (:1523) -----------------------------------------------------------
         double med[3];
-        if (!cell_axis_medians(s, d, X, Y, Z, n, med)) return;
+        if (!cell_axis_medians(s, d, X, Y, Z, flist, n, med)) return;      // flist is free until phase G
         if (tid < 3) d.med[(size_t)fe * 3 + tid] = med[tid];
         CELL_TICK(0);
         const double cx = med[0], cy = med[1], cz = med[2];
@@ -568,8 +605,11 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             unsigned slot = (id * 2654435761u) >> 20;
             int probes = 0;
             for (;;) {
-                const unsigned prev = atomicCAS(&s.keys[slot], E2_CELL_EMPTY, id);
-                if (prev == E2_CELL_EMPTY || prev == id) break;
+                // a plain look first: almost every point finds its cell already there, and compare-and-swaps of a whole
+                // face on one word would queue up
+                unsigned cur = ((volatile unsigned *)s.keys)[slot];
+                if (cur == E2_CELL_EMPTY) cur = atomicCAS(&s.keys[slot], E2_CELL_EMPTY, id);
+                if (cur == E2_CELL_EMPTY || cur == id) break;
                 slot = (slot + 1) & (E2_CELL_HASH - 1);
                 if (++probes >= E2_CELL_HASH) { s.overflow = 1; break; }
             }
