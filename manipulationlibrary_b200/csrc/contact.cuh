@@ -89,7 +89,7 @@ __global__ void contact_plan_kernel(Dev d, ContactPlan plan)
             const double lim2 = d.thresh * d.thresh * 1.000001 + 1e-300;
             const double gap2 = box_box_d2(ba, bb);
             init = d2key(fmax(gap2, d.thresh * d.thresh));
-            if (!(gap2 > lim2)) items = (unsigned)((na + E2_CT_CHUNK - 1) / E2_CT_CHUNK);
+            if (!(gap2 > lim2)) items = 1u;          // one work item per pair: its chunks of A run one after the other
         }
     }
     *s.out = init;
@@ -256,10 +256,6 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
             }
         const int f = lo / plan.slots;
         const ContactSlot cs = contact_decode(d, f, lo - f * plan.slots);
-        const int chunk = (int)(item - plan.off[lo]);
-        if (tid == 0) s.skip = cs.cross && *((volatile u64 *)cs.out) == 0ull;   // another item already found a witness
-        __syncthreads();
-        if (s.skip) continue;
         const int offa = d.ent_off[cs.fa * K + cs.a], na = d.n_list[cs.fa * K + cs.a];
         const size_t pa = (size_t)cs.fa * d.cap + offa;
         const double *AX = d.px + pa, *AY = d.py + pa, *AZ = d.pz + pa;
@@ -281,7 +277,14 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
             nb = d.n_list[f * K + cs.b];
             for (int k = 0; k < 6; ++k) bb[k] = d.aabb[(size_t)(f * K + cs.b) * 6 + k];
         }
-        // ---- A chunk: points within thresh of B's box, and their own tight box ---------------------------------
+        // The chunks of A (1024 consecutive points of its raster order) run one after the other, LAST chunk first, and share
+        // the minimum found so far: only points closer to B's box than that minimum can still improve it.  The last rows of an
+        // object in the image are the ones next to what it stands on, so the first chunk usually finds (almost) the minimum
+        // and the others are skimmed -- an (object, table) pair costs one sweep instead of one per chunk.
+        double best = lim2;                                      // block-uniform at every tile and chunk boundary
+        for (int chunk = (na + E2_CT_CHUNK - 1) / E2_CT_CHUNK - 1; chunk >= 0; --chunk) {
+        // ---- A chunk: points within `best` of B's box, and their own tight box ---------------------------------
+        __syncthreads();                                         // the previous chunk's staging is consumed
         unsigned nA = 0;
         double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
         {
@@ -297,7 +300,7 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const int i = chunk * E2_CT_CHUNK + k * E2_CT_THREADS + tid;
-                take[k] = (i < na) && point_box_d2(x[k], y[k], z[k], bb) <= lim2;
+                take[k] = (i < na) && point_box_d2(x[k], y[k], z[k], bb) <= best;
                 if (take[k]) {
                     mn[0] = fmin(mn[0], x[k]); mx[0] = fmax(mx[0], x[k]);
                     mn[1] = fmin(mn[1], y[k]); mx[1] = fmax(mx[1], y[k]);
@@ -345,7 +348,6 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
             }
         }
         const double c0 = 4.0 * e * sqrt(lim2) + 12.0 * e * e;
-        double best = lim2;                                      // block-uniform at every tile boundary
         float guard = contact_guard(best, c0);
         // ---- B tiles -----------------------------------------------------------------------------------------------
         // Ground (Morton order, one tight box per run of E2_CT_SUB points): warp 0 lists the runs that lie within thresh
@@ -406,6 +408,8 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
             guard = contact_guard(best, c0);
             if (cs.cross && sqrt(best) < d.thresh) break;        // a witness is enough for a cross pair (best is uniform)
         }
+        if (cs.cross && sqrt(best) < d.thresh) break;
+        }                                                        // chunks of A
         if (tid == 0) {
             if (cs.cross) { if (sqrt(best) < d.thresh) atomicMin(cs.out, 0ull); }     // contact flag: 0.0 = closer than thresh
             else if (best < lim2) atomicMin(cs.out, d2key(best));
