@@ -280,25 +280,32 @@ def run_b200(args):
         saved_stdout = os.dup(1)
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
-    # rank r holds stream frames [r * pool, (r + 1) * pool); local frame j of a block has the content of pool frame j % pool.
-    # One more frame in front (a copy of the pool's last frame) so that a batch can be handed over together with the frame
-    # before it (its halo) as one contiguous block even where the pool wraps.
-    hx, hl = generate_pool(stream, rank * pool, pool)
-    hx = np.concatenate([hx[-1:], hx])
-    hl = np.concatenate([hl[-1:], hl])
+    # One sequence of world * K batches of B frames, dealt round-robin: global batch g runs on rank g % world as that rank's
+    # step g // world, behind a one-frame halo (the last frame of batch g - 1).  Rank r holds `pool` distinct stream frames
+    # [r * pool, (r + 1) * pool) as pool / B blocks of B frames; step j of a block of the run has the content of pool block
+    # j % (pool / B).  Every block is stored with its halo frame in front -- the last frame of the pool block the
+    # predecessor batch uses on ITS rank -- so a batch and its halo are one contiguous region.
+    nb = pool // B
+
+    def pred_block(r, b):
+        """(rank, pool block) of the batch in front of rank r's pool block b"""
+        return (r - 1, b) if r > 0 else (world - 1, (b - 1) % nb)
+
+    hx = np.empty((nb, B + 1, N, 3), np.float32)
+    hl = np.empty((nb, B + 1, N), np.int32)
+    gx_, gl_ = generate_pool(stream, rank * pool, pool)
+    hx[:, 1:] = gx_.reshape(nb, B, N, 3)
+    hl[:, 1:] = gl_.reshape(nb, B, N)
+    del gx_, gl_
+    for b_ in range(nb):
+        pr, pb = pred_block(rank, b_)
+        hx[b_, 0], hl[b_, 0] = stream.frame(pr * pool + pb * B + B - 1)
     hx_t = torch.from_numpy(hx).pin_memory()
     hl_t = torch.from_numpy(hl).pin_memory()
     lab8 = args.e2e_labels == "u8" and not args.no_e2e and int(hl.max()) < 256 and int(hl.min()) >= 0
     hl8_t = torch.from_numpy(hl.astype(np.uint8)).pin_memory() if lab8 else None     # what a uint8 label reader hands over
     dx = hx_t.to(dev, non_blocking=True)
     dl = hl_t.to(dev, non_blocking=True)
-    # the frame in front of this rank's block = the last frame of the previous rank's block (the shard's halo)
-    if rank > 0:
-        px_, pl_ = stream.frame((rank - 1) * pool + (seq - 1) % pool)
-        sx_t = torch.from_numpy(px_[None].copy()).pin_memory()
-        sl_t = torch.from_numpy(pl_[None].astype(np.int32)).pin_memory()
-        sl8_t = torch.from_numpy(pl_[None].astype(np.uint8)).pin_memory()
-        sdx, sdl = sx_t.to(dev), sl_t.to(dev)
     torch.cuda.synchronize()
 
     p, keep = nat.make_params(**stream.params(filter_mode=args.filter_mode, filter_seed=20261104,
@@ -312,22 +319,24 @@ def run_b200(args):
     ests = [torch.cuda.ExternalStream(e.stream, device=dev) for e in engs]
     rec_w = nat.record_doubles(int(p.n_entities))
     p2 = Phase2(eng, max_columns=seq + 8)
-    shard_rec = torch.empty((seq, rec_w), dtype=torch.float64, device=dev) if world > 1 else None
     # e2e / host phase 2 / verification: the records of a block on the host, batch i in rows [i, 1:] (row [i, 0]: its halo frame)
     rec_host = torch.empty((K, B + 1, rec_w), dtype=torch.float64).pin_memory()
     rec3 = rec_host.numpy()
-    g0 = rank * seq                                # global index of this rank's first frame inside the block's sequence
-    ids_block = np.arange(g0 - 1, g0 + seq, dtype=np.int32)       # [0] = the halo frame's id
     state_t = torch.zeros(nat.PHASE2_STATE_BYTES, dtype=torch.uint8, device=dev)
     from concurrent.futures import ThreadPoolExecutor
     follower = ThreadPoolExecutor(max_workers=1)
+    LAG = max(1, C - 1)                            # batches queued on the GPU while the host hands the phase-2 state on
 
-    def inputs(on_device, first_local, halo):
-        """pointers to local frame first_local (minus one with its halo): pool position + 1 because of the leading copy"""
-        s = first_local % pool + (0 if halo else 1)
+    def ids_of(j, halo):
+        """frame ids (= global frame indices of the sequence) of this rank's step j, with its halo frame's in front"""
+        g = j * world + rank
+        return np.arange(g * B - (1 if halo else 0), (g + 1) * B, dtype=np.int32)
+
+    def inputs(on_device, j, halo):
+        blk, o = j % nb, (0 if halo else 1)
         if on_device:
-            return dx[s].data_ptr(), dl[s].data_ptr()
-        return hx_t[s].data_ptr(), (hl8_t if lab8 else hl_t)[s].data_ptr()
+            return dx[blk, o].data_ptr(), dl[blk, o].data_ptr()
+        return hx_t[blk, o].data_ptr(), (hl8_t if lab8 else hl_t)[blk, o].data_ptr()
 
     def queue(e, px, pl, n, ids, out, on_device):
         if on_device:
@@ -335,80 +344,61 @@ def run_b200(args):
         else:
             e.process_batch_device_async(px, pl, n, ids, N, records=out, on_device=False, labels8=lab8)
 
-    def step(i, on_device, want_host, phase2_dev):
-        """Batch i of the block (local frames i*B .. (i+1)*B-1) on context i % C.  With one context the batches follow each
-        other on its stream.  With several, every batch is its own little sequence on its context: the frame before it goes
-        in front as the halo (its record is dropped) -- the same one-frame halo the frame sharding across GPUs uses.  The
-        first batch of a shard (rank > 0) runs behind the previous rank's last frame."""
-        c = i % C
-        e = engs[c]
-        skip = 0
-        if i == 0 or C > 1:
+    def step(j, on_device, want_host):
+        """Phase 1 of this rank's step j on context j % C.  Every batch is its own little sequence on its context: the frame
+        before it goes in front as the halo (its record is dropped) -- except the very first batch of the sequence, and
+        except with one context on one GPU, where the batches simply follow each other on the stream."""
+        e = engs[j % C]
+        g = j * world + rank
+        halo = g > 0 and not (C == 1 and world == 1)
+        if halo or g == 0:
             e.reset_sequence()
-        if i == 0:
-            if rank > 0:
-                if on_device:
-                    queue(e, sdx.data_ptr(), sdl.data_ptr(), 1, ids_block[:1], None, True)
-                else:
-                    queue(e, sx_t.data_ptr(), (sl8_t if lab8 else sl_t).data_ptr(), 1, ids_block[:1], None, False)
-            px, pl = inputs(on_device, 0, False)
-            queue(e, px, pl, B, ids_block[1: 1 + B], rec3[i, 1:] if want_host else None, on_device)
-        elif C == 1:
-            px, pl = inputs(on_device, i * B, False)
-            queue(e, px, pl, B, ids_block[1 + i * B: 1 + (i + 1) * B], rec3[i, 1:] if want_host else None, on_device)
-        else:
-            px, pl = inputs(on_device, i * B, True)
-            queue(e, px, pl, B + 1, ids_block[i * B: 1 + (i + 1) * B], rec3[i] if want_host else None, on_device)
-            skip = 1
-        if phase2_dev:
-            if world == 1:
-                p2.run_engine_batch(e, B + skip, skip=skip)         # the classifier follows the batch on its own stream
-            else:
-                e.copy_records(shard_rec[i * B].data_ptr(), skip, B)  # the shard keeps its records for the chained phase 2
-        return c
+        px, pl = inputs(on_device, j, halo)
+        out = (rec3[j] if halo else rec3[j, 1:]) if want_host else None
+        queue(e, px, pl, B + (1 if halo else 0), ids_of(j, halo), out, on_device)
+        return e, (1 if halo else 0)
+
+    def phase2_step(j, e, skip):
+        """The relation classifiers of step j behind everything before it in the sequence: the state (512 bytes) arrives
+        from the rank that ran the batch in front, and goes on to the rank that runs the next one."""
+        g = j * world + rank
+        if world > 1 and g > 0:
+            dist.recv(state_t, src=(rank - 1) % world)
+            torch.cuda.current_stream().synchronize()
+            p2.state_set(state_t.data_ptr())
+        p2.run_engine_batch(e, B + skip, skip=skip)
+        if world > 1 and g < world * K - 1:
+            p2.state_get(state_t.data_ptr())
+            dist.send(state_t, dst=(rank + 1) % world)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def finish_device(out):
-        """End of a block with the device classifier: one GPU just waits for it; several chain the phase-2 state through
-        the shards in rank order (512 bytes each way) and gather the emitted columns on rank 0 -- the one collective."""
-        for e in engs:
-            e.sync()                                   # raises device-side errors of the queued batches
+    cap_cols = seq + 8
+    exp_t = torch.zeros(16 + 36 * cap_cols, dtype=torch.uint8, device=dev)
+    exp_all = [torch.empty_like(exp_t) for _ in range(world)] if (world > 1 and rank == 0) else None
+
+    def gather_columns(out):
+        """The one collective: the emitted columns (32 code bytes + frame id each) of every rank on rank 0, in frame order."""
+        n = p2.sync()                                  # raises phase-2 errors (records out of order, too many columns)
         if world == 1:
-            n = p2.sync()
             if out is not None:
                 out["columns"], out["frames"] = p2.fetch()
             return n
-        if rank > 0:
-            dist.recv(state_t, src=rank - 1)
-            torch.cuda.current_stream().synchronize()
-            p2.state_set(state_t.data_ptr())
-        p2.run(shard_rec.data_ptr(), seq)
-        p2.state_get(state_t.data_ptr())
-        if rank < world - 1:
-            dist.send(state_t, dst=rank + 1)
-        cols, frames = p2.fetch()
-        cnt = torch.tensor([len(frames)], dtype=torch.int32, device=dev)
-        counts = torch.empty(world, dtype=torch.int32, device=dev)
-        dist.all_gather_into_tensor(counts, cnt)
-        counts = counts.cpu().numpy()
-        width = nat.PHASE2_COLUMN_BYTES + 4
-        pad = torch.zeros((max(int(counts.max()), 1), width), dtype=torch.uint8, device=dev)
-        if len(frames):
-            packed = np.concatenate([cols, frames.view(np.uint8).reshape(-1, 4)], axis=1)
-            pad[: len(frames)] = torch.from_numpy(packed).to(dev)
-        parts = [torch.empty_like(pad) for _ in range(world)] if rank == 0 else None
-        dist.gather(pad, parts, dst=0)
+        p2.export(exp_t.data_ptr(), cap_cols)
+        dist.gather(exp_t, exp_all, dst=0)
         if rank != 0:
             return 0
-        allp = np.concatenate([parts[r][: int(counts[r])].cpu().numpy() for r in range(world)])
+        host = torch.stack(exp_all).cpu().numpy()
+        parts = [Phase2.parse_export(host[r], cap_cols) for r in range(world)]
+        cols = np.concatenate([c for c, _ in parts])
+        fr = np.concatenate([f for _, f in parts])
+        order = np.argsort(fr, kind="stable")
         if out is not None:
-            out["columns"] = np.ascontiguousarray(allp[:, : nat.PHASE2_COLUMN_BYTES])
-            out["frames"] = np.ascontiguousarray(allp[:, nat.PHASE2_COLUMN_BYTES:]).view(np.int32).reshape(-1)
-        return len(allp)
+            out["columns"], out["frames"] = np.ascontiguousarray(cols[order]), fr[order]
+        return len(fr)
 
     def block(on_device, want_host=False, out=None):
         """One timed block = one sequence of world * K * B frames.  -> (device ms, wall ms, launches, columns)"""
@@ -422,9 +412,16 @@ def run_b200(args):
         with torch.cuda.stream(est):
             ev0.record()                    # every stream is idle here (barrier)
         if dev_p2:
-            for i in range(K):
-                step(i, on_device, want_host, True)
-            cols = finish_device(out)
+            pend = []
+            for j in range(K):
+                pend.append((j,) + step(j, on_device, want_host))
+                if len(pend) > LAG:
+                    phase2_step(*pend.pop(0))
+            while pend:
+                phase2_step(*pend.pop(0))
+            for e in engs:
+                e.sync()                                   # raises device-side errors of the queued batches
+            cols = gather_columns(out)
         else:
             # the C++ resolver follows the GPU on its own thread, in frame order
             res = Resolver(p, keep)
@@ -435,8 +432,8 @@ def run_b200(args):
                 res.feed(rec3[i, 1:])
 
             for i in range(K):
-                c = step(i, on_device, True, False)
-                with torch.cuda.stream(ests[c]):
+                step(i, on_device, True)
+                with torch.cuda.stream(ests[i % C]):
                     e = torch.cuda.Event()
                     e.record()
                 futs.append(follower.submit(follow, i, e))
@@ -519,8 +516,8 @@ def run_b200(args):
     # timed region the stages of different batches overlap) -- three back to back, the last one's events are read
     eng.reset_sequence()
     for i in range(3):
-        px, pl = inputs(True, (i % (pool // B)) * B, False)
-        queue(eng, px, pl, B, ids_block[1 + (i % K) * B: 1 + (i % K + 1) * B], None, True)
+        px, pl = inputs(True, i, False)
+        queue(eng, px, pl, B, ids_of(i, False), None, True)
     eng.sync()
     stages = eng.stage_ms()
 
@@ -561,8 +558,9 @@ def run_b200(args):
                        "frames_timed": frames, "pool_frames_per_gpu": pool, "filter_mode": args.filter_mode,
                        "radius_mode": args.radius_mode, "filtered_entities": n_filtered, "exact_path_entities": n_exact,
                        "l2": "inputs larger than L2 (one step reads %d MB)" % (alg // 2 ** 20),
-                       "parallelism": ("one sequence of %d frames, frame-sharded x%d in contiguous blocks behind a one-frame halo; "
-                                       "phase-2 state chained through the shards, one gather of the emitted columns" % (frames, world))
+                       "parallelism": ("one sequence of %d frames, frame-sharded x%d: blocks of %d frames dealt round-robin, each behind a "
+                                       "one-frame halo; the phase-2 state (512 B) follows the blocks around the ring of GPUs, one "
+                                       "gather of the emitted columns at the end" % (frames, world, B))
                        if world > 1 else "one GPU",
                        "phase2": args.phase2, "contexts_per_gpu": C},
             "timed_blocks": {"blocks": len(runs), "steps_per_block": K, "median_ms": ms, "best_ms": ms_all[0],

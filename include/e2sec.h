@@ -98,6 +98,7 @@ size_t e2sec_record_doubles(int32_t n_entities);
 
 /* ---- context ----------------------------------------------------------------------------------- */
 int e2sec_abi_version(void);
+int e2sec_device_count(void);        /* CUDA devices visible to the process (0: none -- and no CPU fallback) */
 int e2sec_create(int device, e2sec_ctx **out);
 void e2sec_destroy(e2sec_ctx *ctx);
 const char *e2sec_last_error(const e2sec_ctx *ctx);
@@ -237,6 +238,9 @@ int e2sec_phase2_sync(e2sec_phase2 *p2, int32_t *n_columns);
 /* The packed columns (n x E2SEC_PHASE2_COLUMN_BYTES relation codes as csrc/relations.h numbers them, rows 0..10*relations-1
  * used) and the frame id of each, to the host; and their device addresses for a gather between GPUs.                      */
 int e2sec_phase2_fetch(e2sec_phase2 *p2, uint8_t *columns, int32_t *frames, int32_t capacity, int32_t *n_columns);
+/* The same in ONE fixed-size buffer (host or device) for a gather between GPUs: [int32 n][12 bytes unused][capacity x
+ * E2SEC_PHASE2_COLUMN_BYTES codes][capacity x int32 frame ids] = 16 + 36 * capacity bytes.  Waits for the object's stream. */
+int e2sec_phase2_export(e2sec_phase2 *p2, void *dst, int32_t capacity);
 int e2sec_phase2_columns_dev(e2sec_phase2 *p2, const uint8_t **columns_dev, const int32_t **frames_dev, const int32_t **n_dev);
 /* o1/o2/o3 entity indices (-1 while unassigned) and the sticky absent flags, like e2sec_resolver_state */
 int e2sec_phase2_bindings(e2sec_phase2 *p2, int32_t labels[3], int32_t absent[3]);

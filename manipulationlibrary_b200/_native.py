@@ -47,6 +47,7 @@ def _load():
     sig = {
         "e2sec_abi_version": (C.c_int, []),
         "e2sec_record_doubles": (C.c_size_t, [i32]),
+        "e2sec_device_count": (C.c_int, []),
         "e2sec_create": (C.c_int, [C.c_int, C.POINTER(vp)]),
         "e2sec_destroy": (None, [vp]),
         "e2sec_last_error": (C.c_char_p, [vp]),
@@ -86,6 +87,7 @@ def _load():
         "e2sec_phase2_state_set": (C.c_int, [vp, vp]),
         "e2sec_phase2_sync": (C.c_int, [vp, vp]),
         "e2sec_phase2_fetch": (C.c_int, [vp, vp, vp, i32, vp]),
+        "e2sec_phase2_export": (C.c_int, [vp, vp, i32]),
         "e2sec_phase2_columns_dev": (C.c_int, [vp, vp, vp, vp]),
         "e2sec_phase2_bindings": (C.c_int, [vp, vp, vp]),
         "e2sec_phase2_stream": (vp, [vp]),

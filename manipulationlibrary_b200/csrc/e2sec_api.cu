@@ -95,6 +95,12 @@ static int ensure(e2sec_ctx *ctx, DevBuf &b, size_t bytes)
 
 extern "C" int e2sec_abi_version(void) { return E2SEC_ABI_VERSION; }
 
+extern "C" int e2sec_device_count(void)
+{
+    int count = 0;
+    return cudaGetDeviceCount(&count) == cudaSuccess ? count : 0;
+}
+
 extern "C" size_t e2sec_record_doubles(int32_t K)
 {
     return (size_t)E2SEC_REC_HEADER + (size_t)E2SEC_REC_ENTITY * K + (size_t)(K + 1) * (K + 1) + (size_t)K * K + (size_t)2 * K;
@@ -1186,6 +1192,22 @@ extern "C" int e2sec_phase2_fetch(e2sec_phase2 *q, uint8_t *columns, int32_t *fr
     if (n > capacity) return fail(ctx, E2SEC_ERR_CAPACITY, "e2sec_phase2_fetch: capacity too small");
     if (n && columns) CU(cudaMemcpyAsync(columns, q->cols.p, (size_t)n * E2_P2_COL, cudaMemcpyDeviceToHost, q->stream));
     if (n && frames) CU(cudaMemcpyAsync(frames, q->col_frame.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, q->stream));
+    CU(cudaStreamSynchronize(q->stream));
+    return E2SEC_OK;
+}
+
+// everything a gather between GPUs needs, in ONE fixed-size device (or host) buffer: [int32 n][12 bytes unused]
+// [capacity x E2SEC_PHASE2_COLUMN_BYTES codes][capacity x int32 frame ids]; waits for the object's stream
+extern "C" int e2sec_phase2_export(e2sec_phase2 *q, void *dst, int32_t capacity)
+{
+    if (!q || !dst || capacity < 1) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    const int cap = capacity < q->a.max_columns ? capacity : q->a.max_columns;
+    char *o = (char *)dst;
+    CU(cudaMemcpyAsync(o, q->n_cols.p, sizeof(int), cudaMemcpyDefault, q->stream));
+    CU(cudaMemcpyAsync(o + 16, q->cols.p, (size_t)cap * E2_P2_COL, cudaMemcpyDefault, q->stream));
+    CU(cudaMemcpyAsync(o + 16 + (size_t)capacity * E2_P2_COL, q->col_frame.p, (size_t)cap * sizeof(int), cudaMemcpyDefault, q->stream));
     CU(cudaStreamSynchronize(q->stream));
     return E2SEC_OK;
 }

@@ -355,6 +355,19 @@ class Phase2:
         self._check(lib.e2sec_phase2_fetch(self._h, ptr(cols), ptr(fr), max(n, 1), C.byref(got)), "e2sec_phase2_fetch")
         return cols[:got.value], fr[:got.value]
 
+    def export(self, dst_ptr, capacity):
+        """Columns, frame ids and their count into one fixed-size buffer (16 + 36 * capacity bytes, host or device)."""
+        self._check(lib.e2sec_phase2_export(self._h, C.c_void_p(int(dst_ptr)), int(capacity)), "e2sec_phase2_export")
+
+    @staticmethod
+    def parse_export(buf, capacity):
+        """The buffer export() filled (uint8 array) -> (columns (n, 32) uint8, frames (n,) int32)."""
+        buf = np.ascontiguousarray(buf, np.uint8).reshape(-1)
+        n = int(buf[:4].view(np.int32)[0])
+        cols = buf[16: 16 + capacity * nat.PHASE2_COLUMN_BYTES].reshape(capacity, nat.PHASE2_COLUMN_BYTES)[:n]
+        fr = buf[16 + capacity * nat.PHASE2_COLUMN_BYTES: 16 + capacity * (nat.PHASE2_COLUMN_BYTES + 4)].view(np.int32)[:n]
+        return cols.copy(), fr.copy()
+
     def columns_dev(self):
         c, f, n = C.c_void_p(), C.c_void_p(), C.c_void_p()
         self._check(lib.e2sec_phase2_columns_dev(self._h, C.byref(c), C.byref(f), C.byref(n)), "e2sec_phase2_columns_dev")

@@ -9,6 +9,8 @@ sequential o1/o2/o3 + relation logic is the library's host resolver.  There is n
 fallback: without a CUDA device the first call raises.
 
 Scope notes:
+  * several GPUs: analyse_maniac_manipulation deals batches of BATCH_FRAMES frames to every visible device in turn, each
+    behind its one-frame halo, while reader threads decode the files ahead; one resolver consumes the records in order.
   * frame-0 setup (_getGroundiNewNew :278-361, _getTranslation :212-276) is random in the reference and outside
     this path; its products are INPUTS here: call set_frame0(translation, roll, ground) before the first frame.
   * icp=True (:1677-1738) is not implemented: it raises NotImplementedError.  relations = 1, 2, 3 are.
@@ -20,6 +22,7 @@ State lives in module globals like the reference's (:32-59): one sequence at a t
 import json
 import os
 import shutil
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -27,7 +30,8 @@ from . import _native as nat
 from .engine import Engine, Resolver, esec_to_e2sec_native, rec_entity
 
 IMAGE_SHAPE = (480, 640)            # :1390, :1433
-BATCH_FRAMES = 25
+BATCH_FRAMES = 25                   # frames per GPU batch (E2SEC_BATCH_FRAMES overrides)
+READ_THREADS = 4                    # file decode runs ahead of the GPUs on this many threads
 
 final_columns = []
 column_frames = []                  # frame id of every raw eSEC column (-1: the initial '-' column), all relation modes
@@ -93,7 +97,7 @@ def _check_args(relations, icp, cython):
 
 
 def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
-                    thresh, max_frames, filter_mode, filter_seed, relations=3):
+                    thresh, max_frames, filter_mode, filter_seed, relations=3, n_devices=1):
     global _state, total_unique_labels, hand_label_inarray, final_columns
     if _frame0 is None:
         raise NotImplementedError("frame-0 setup (_getGroundiNewNew / _getTranslation) is outside this path: call "
@@ -106,11 +110,17 @@ def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old
     p, keep = nat.make_params(tul, hand_label, ground_label, support_hand, thresh, T, R, ground, replace=replace,
                               old=old, new=new, filter_mode=filter_mode, filter_seed=filter_seed, relations=relations)
     if _state is not None:
-        _state["engine"].close()
+        for e in _state["engines"]:
+            e.close()
         _state["resolver"].close()
-    eng = Engine(0)
-    eng.configure(p, max_frames, IMAGE_SHAPE[0] * IMAGE_SHAPE[1], keep)
-    _state = dict(engine=eng, resolver=Resolver(p, keep), params=p, keep=keep, K=len(tul), records={})
+    # every visible GPU takes batches of the sequence in turn (E2SEC_DEVICES limits how many); _process, frame by frame, uses one
+    n_dev = max(1, min(int(nat.lib.e2sec_device_count()), int(os.environ.get("E2SEC_DEVICES", "64")), n_devices))
+    engines = []
+    for dev in range(n_dev):
+        eng = Engine(dev)
+        eng.configure(p, max_frames + 1, IMAGE_SHAPE[0] * IMAGE_SHAPE[1], keep)      # + the halo frame in front of a batch
+        engines.append(eng)
+    _state = dict(engine=engines[0], engines=engines, resolver=Resolver(p, keep), params=p, keep=keep, K=len(tul), records={})
     final_columns = []
 
 
@@ -194,21 +204,68 @@ def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, 
     step = int(30 / fps)                                                 # :2266-2268
     files = sorted(os.listdir(pcl_path))
     todo = [(i, f) for i, f in enumerate(files) if i % step == 0]
-    started = False
-    for s in range(0, len(todo), BATCH_FRAMES):
-        chunk = todo[s: s + BATCH_FRAMES]
-        xs, ls, ids = [], [], []
+    batch = max(1, int(os.environ.get("E2SEC_BATCH_FRAMES", BATCH_FRAMES)))
+    chunks = [todo[s: s + batch] for s in range(0, len(todo), batch)]
+
+    def read_chunk(chunk):
+        xs, ls, ids, lshape = [], [], [], None
         for i, f in chunk:
             xyz, label = read_frame(pcl_path + f[0:-7] + "_pc.pcd", label_path + f[0:-7] + "_left-labels.dat")
-            if not started:
-                _start_sequence(label, ground_label, hand_label, support_hand, replace, old, new, ignored_labels,
-                                cut_labels, thresh, BATCH_FRAMES, filter_mode, filter_seed, relations)
-                started = True
             xs.append(xyz)
             ls.append(label.reshape(-1).astype(np.int32))
             ids.append(i)
             lshape = label.shape
-        _run_batch(np.array(ids, np.int32), np.stack(xs), np.stack(ls), lshape)
+        return np.stack(xs), np.stack(ls), np.array(ids, np.int32), lshape
+
+    def run_on(dev, xyz, lab, ids, lshape, halo):
+        """One batch as its own little sequence on GPU `dev`: the frame in front of it (halo = (xyz, labels, id) of the last
+        frame of the batch before) goes first and its record is dropped -- the one-frame halo of the frame sharding."""
+        eng = _state["engines"][dev]
+        kw = dict(label_shape=lshape, image_shape=IMAGE_SHAPE) if lab.shape[1] != xyz.shape[1] else {}
+        eng.reset_sequence()
+        if halo is None:
+            return None, eng.process_batch(xyz, lab, ids, **kw)
+        rec = eng.process_batch(np.concatenate([halo[0][None], xyz]), np.concatenate([halo[1][None], lab]),
+                                np.concatenate([[halo[2]], ids]).astype(np.int32), **kw)
+        return rec[0], rec[1:]
+
+    KEPT = nat.FLAG_HAND_LABEL | nat.FLAG_HAND_POINTS
+    last_kept = None                     # (xyz, labels, id) of the last kept frame fed to the resolver so far
+    with ThreadPoolExecutor(max_workers=READ_THREADS) as readers:
+        ahead = [readers.submit(read_chunk, c) for c in chunks[: 2]]
+        first = ahead[0].result() if ahead else None
+        if first is not None:
+            _start_sequence(first[1][0].reshape(first[3]), ground_label, hand_label, support_hand, replace, old, new,
+                            ignored_labels, cut_labels, thresh, batch, filter_mode, filter_seed, relations, n_devices=64)
+        D = len(_state["engines"]) if first is not None else 1
+        workers = [ThreadPoolExecutor(max_workers=1) for _ in range(D)]
+        window = 2 * D + 2                                               # chunks read ahead / in flight
+        ahead += [readers.submit(read_chunk, c) for c in chunks[2: window]]
+        jobs = []                                                        # (data, future of (halo record, records))
+        prev_last = None                                                 # last frame of the chunk in front (speculative halo)
+        for c in range(len(chunks)):
+            data = ahead[c].result()
+            if c + window < len(chunks):
+                ahead.append(readers.submit(read_chunk, chunks[c + window]))
+            xyz, lab, ids, lshape = data
+            jobs.append((data, prev_last, workers[c % D].submit(run_on, c % D, xyz, lab, ids, lshape, prev_last)))
+            prev_last = (xyz[-1], lab[-1], int(ids[-1]))
+            while jobs and (len(jobs) > D or c == len(chunks) - 1):      # collect in order, D batches stay in flight
+                (xyz0, lab0, ids0, lshape0), halo, fut = jobs.pop(0)
+                hrec, rec = fut.result()
+                want = last_kept[2] if last_kept is not None else -1
+                if halo is not None and (int(hrec[1]) != KEPT or halo[2] != want):
+                    # the frame in front was not a kept frame (no hand in it): redo the batch behind the real one
+                    _, rec = workers[0].submit(run_on, 0, xyz0, lab0, ids0, lshape0, last_kept).result()
+                _state["resolver"].feed(rec)
+                for f, r in zip(ids0, rec):
+                    _state["records"][int(f)] = r
+                kept = np.nonzero(rec[:, 1].astype(np.int64) == KEPT)[0]
+                if len(kept):
+                    k = int(kept[-1])
+                    last_kept = (xyz0[k], lab0[k], int(ids0[k]))
+        for w in workers:
+            w.shutdown()
     table = _table_from_resolver(relations)
     raw_columns = list(column_frames)
     if debug:

@@ -462,6 +462,49 @@ def test_dropin_analyse_maniac_manipulation(tmp_path, monkeypatch):
         ma.analyse_maniac_manipulation(pcl, lab, 2, 11, None, 3, False, [], [], [255], 0.07, icp=True)
 
 
+@pytest.mark.parametrize("want_relations", [1, 2, 3])
+def test_dropin_scripted_scene_relations_and_batches(tmp_path, monkeypatch, want_relations):
+    """analyse_maniac_manipulation on a scripted scene of tests/golden/relation_kats.npz (the outputs of the reference's
+    own analyse_maniac_manipulation): relations 1, 2 and 3, the hand-as-lowest-label scene among them, batches of 4 frames
+    dealt to the device(s) behind their one-frame halo with the file reads running ahead."""
+    from manipulationlibrary_b200 import manipulation_analyser as ma
+    from oracle.gen_relation_kats import ROLL, THRESH, scene_from_golden
+    z = load_golden("relation_kats")
+    z = {k: z[k] for k in z.files}
+    picked = [k for k in range(int(z["b_count"])) if int(z["b%d_params" % k][4]) == want_relations][:2]
+    if want_relations == 3:
+        picked += [k for k in range(int(z["b_count"])) if int(z["b%d_params" % k][1]) == 1][:1]      # the hand is label 1
+    assert picked
+    monkeypatch.setenv("E2SEC_BATCH_FRAMES", "4")
+    head = ("# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\nCOUNT 1 1 1\n"
+            "WIDTH 640\nHEIGHT 480\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS 307200\nDATA binary\n").encode()
+    for k in picked:
+        sc, exp = scene_from_golden(z, k)
+        d = tmp_path / ("scene%d" % k)
+        pcl, lab = d / "pcl", d / "lab"
+        pcl.mkdir(parents=True)
+        lab.mkdir()
+        for i in range(len(sc.frames) * 3):
+            stem = "%05d" % i
+            if i % 3:
+                (pcl / (stem + "_pc.pcd")).write_bytes(b"")
+                continue
+            xyz, labels = sc.dense(i // 3)
+            with open(pcl / (stem + "_pc.pcd"), "wb") as f:
+                f.write(head)
+                f.write(np.ascontiguousarray(xyz, "<f4").tobytes())
+            np.savetxt(lab / (stem + "_left-labels.dat"), labels, fmt="%d")
+        monkeypatch.chdir(d)
+        ma.set_frame0(np.eye(4), ROLL, sc.ground_final)
+        ma.analyse_maniac_manipulation(str(pcl) + "/", str(lab) + "/", sc.ground_label, sc.hand_label, sc.support, sc.relations,
+                                       False, [], [], [], THRESH, cut_labels=[], icp=False, savename="kat")
+        e2 = np.load(d / "e2sec_kat.npy")
+        assert e2.shape == exp["e2sec"].shape and (e2.astype("U5") == exp["e2sec"]).all(), k
+        if sc.relations == 3:
+            assert list(ma.final_columns) == list(exp["final_columns"]), k
+        assert list(np.asarray(ma.total_unique_labels, np.float64)) == list(exp["total_unique_labels"]), k
+
+
 def test_dropin_process_frame_by_frame(tmp_path, monkeypatch):
     """_process called per frame like the reference's loop (:2271-2281) builds the same raw eSEC table."""
     from manipulationlibrary_b200 import manipulation_analyser as ma
