@@ -322,10 +322,16 @@ def run_b200(args):
     # e2e / host phase 2 / verification: the records of a block on the host, batch i in rows [i, 1:] (row [i, 0]: its halo frame)
     rec_host = torch.empty((K, B + 1, rec_w), dtype=torch.float64).pin_memory()
     rec3 = rec_host.numpy()
-    state_t = torch.zeros(nat.PHASE2_STATE_BYTES, dtype=torch.uint8, device=dev)
+    serial = [0]                                   # blocks run so far (tickets of the ring never repeat)
+    if world > 1:
+        # every rank's phase-2 mailbox is opened by the rank in front of it as peer memory (CUDA IPC, NVLink): the state of
+        # the sequence then travels from kernel to kernel without the host
+        mine = torch.from_numpy(p2.mailbox_handle()).to(dev)
+        handles = torch.empty((world, nat.IPC_HANDLE_BYTES), dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(handles, mine)
+        p2.connect(handles[(rank + 1) % world].cpu().numpy())
     from concurrent.futures import ThreadPoolExecutor
     follower = ThreadPoolExecutor(max_workers=1)
-    LAG = max(1, C - 1)                            # batches queued on the GPU while the host hands the phase-2 state on
 
     def ids_of(j, halo):
         """frame ids (= global frame indices of the sequence) of this rank's step j, with its halo frame's in front"""
@@ -359,17 +365,15 @@ def run_b200(args):
         return e, (1 if halo else 0)
 
     def phase2_step(j, e, skip):
-        """The relation classifiers of step j behind everything before it in the sequence: the state (512 bytes) arrives
-        from the rank that ran the batch in front, and goes on to the rank that runs the next one."""
+        """The relation classifiers of step j behind everything before it in the sequence.  With several GPUs the kernel
+        itself waits for the state (512 bytes) in this rank's mailbox, where the kernel of the batch in front -- on the
+        previous rank of the ring -- has put it over NVLink, and posts its own state into the next rank's mailbox."""
         g = j * world + rank
-        if world > 1 and g > 0:
-            dist.recv(state_t, src=(rank - 1) % world)
-            torch.cuda.current_stream().synchronize()
-            p2.state_set(state_t.data_ptr())
-        p2.run_engine_batch(e, B + skip, skip=skip)
-        if world > 1 and g < world * K - 1:
-            p2.state_get(state_t.data_ptr())
-            dist.send(state_t, dst=(rank + 1) % world)
+        if world == 1:
+            p2.run_engine_batch(e, B + skip, skip=skip)
+            return
+        base = serial[0] * world * K + 1
+        p2.run_ring_engine_batch(e, B + skip, skip, base + g if g > 0 else 0, base + g + 1 if g < world * K - 1 else 0)
 
     def barrier():
         if world > 1:
@@ -412,13 +416,10 @@ def run_b200(args):
         with torch.cuda.stream(est):
             ev0.record()                    # every stream is idle here (barrier)
         if dev_p2:
-            pend = []
             for j in range(K):
-                pend.append((j,) + step(j, on_device, want_host))
-                if len(pend) > LAG:
-                    phase2_step(*pend.pop(0))
-            while pend:
-                phase2_step(*pend.pop(0))
+                e, skip = step(j, on_device, want_host)
+                phase2_step(j, e, skip)
+            serial[0] += 1
             for e in engs:
                 e.sync()                                   # raises device-side errors of the queued batches
             cols = gather_columns(out)
@@ -463,10 +464,32 @@ def run_b200(args):
         os.dup2(saved_stdout, 1)
         os.close(saved_stdout)
     uuid = str(torch.cuda.get_device_properties(dev).uuid)
-    sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if rank == 0 else None
+    debug = bool(os.environ.get("E2SEC_BENCH_DEBUG"))
+    sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if (rank == 0 or debug) else None
     time.sleep(0.3 if sampler else 0.0)
     runs = [block(True) for _ in range(max(1, args.blocks))]
+    if os.environ.get("E2SEC_BENCH_DEBUG"):            # per-rank view of the timed blocks (stderr): own device time, clocks
+        own = []
+        for _ in range(5):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            t_ = time.perf_counter()
+            for j in range(K):
+                step(j, True, False)
+            for e in engs:
+                e.sync()
+            own.append((time.perf_counter() - t_) * 1e3)
+        try:
+            q = subprocess.run(["nvidia-smi", "-i", str(local), "--query-gpu=clocks.sm,power.draw,temperature.gpu,clocks_event_reasons.active",
+                                "--format=csv,noheader"], capture_output=True, text=True).stdout.strip()
+        except Exception:
+            q = "?"
+        print("[rank %d] phase 1 only, K steps, no ring: %s ms; idle-after-run smi: %s" % (rank, ["%.2f" % v for v in own], q), file=sys.stderr, flush=True)
     clocks = sampler.stop(runs[0][4][0], runs[-1][4][1]) if sampler else None
+    if debug:
+        print("[rank %d] clocks under load: %s; block ms (max over ranks): median %.2f" % (rank, clocks, statistics.median(r[0] for r in runs)),
+              file=sys.stderr, flush=True)
     ms_all = sorted(r[0] for r in runs)
     ms = statistics.median(ms_all)
     wall_ms = statistics.median(r[1] for r in runs)
@@ -559,8 +582,8 @@ def run_b200(args):
                        "radius_mode": args.radius_mode, "filtered_entities": n_filtered, "exact_path_entities": n_exact,
                        "l2": "inputs larger than L2 (one step reads %d MB)" % (alg // 2 ** 20),
                        "parallelism": ("one sequence of %d frames, frame-sharded x%d: blocks of %d frames dealt round-robin, each behind a "
-                                       "one-frame halo; the phase-2 state (512 B) follows the blocks around the ring of GPUs, one "
-                                       "gather of the emitted columns at the end" % (frames, world, B))
+                                       "one-frame halo; the phase-2 state (512 B) goes from kernel to kernel around the ring of GPUs "
+                                       "through peer memory (NVLink), one gather of the emitted columns at the end" % (frames, world, B))
                        if world > 1 else "one GPU",
                        "phase2": args.phase2, "contexts_per_gpu": C},
             "timed_blocks": {"blocks": len(runs), "steps_per_block": K, "median_ms": ms, "best_ms": ms_all[0],

@@ -232,6 +232,21 @@ int e2sec_phase2_run(e2sec_phase2 *p2, e2sec_ctx *src, const double *records_dev
  * host or device memory, e.g. the buffer of an NCCL send / recv).  Both wait for the object's stream.                     */
 int e2sec_phase2_state_get(e2sec_phase2 *p2, void *dst);
 int e2sec_phase2_state_set(e2sec_phase2 *p2, const void *src);
+/* The same handing-over WITHOUT the host, for one process per GPU on one box: every object owns a mailbox in device memory;
+ * e2sec_phase2_mailbox_handle gives its CUDA IPC handle (E2SEC_IPC_HANDLE_BYTES, exchanged once between the processes),
+ * e2sec_phase2_connect opens the mailbox of the rank that runs the NEXT frames as peer memory (NVLink / NVSwitch).
+ * e2sec_phase2_run_ring is e2sec_phase2_run whose kernel first waits -- on the device -- until the state posted under
+ * wait_ticket has arrived in its own mailbox (0: start from the object's own state), and at the end writes its state and
+ * then post_ticket straight into the next rank's mailbox (0: post nothing).  Tickets are any non-zero numbers that differ
+ * from hop to hop, e.g. 1 + the running index of the batch in the sequence.  A ticket that does not arrive within 20 s
+ * is reported by e2sec_phase2_sync as E2SEC_ERR_STATE.                                                                    */
+#define E2SEC_IPC_HANDLE_BYTES 64
+int e2sec_phase2_mailbox_handle(e2sec_phase2 *p2, void *handle);
+int e2sec_phase2_connect(e2sec_phase2 *p2, const void *next_handle);
+/* the same for two objects of ONE process (several GPUs driven by one process, or two objects on one GPU) */
+int e2sec_phase2_connect_local(e2sec_phase2 *p2, e2sec_phase2 *next);
+int e2sec_phase2_run_ring(e2sec_phase2 *p2, e2sec_ctx *src, const double *records_dev, int32_t n_frames,
+                          uint32_t wait_ticket, uint32_t post_ticket);
 /* Waits; reports device-side errors (records out of order, more than max_columns columns); n_columns (may be NULL) = the
  * columns this object holds.                                                                                              */
 int e2sec_phase2_sync(e2sec_phase2 *p2, int32_t *n_columns);

@@ -16,6 +16,7 @@ FLAG_HAND_LABEL = 1
 FLAG_HAND_POINTS = 2
 PHASE2_STATE_BYTES = 512
 PHASE2_COLUMN_BYTES = 32
+IPC_HANDLE_BYTES = 64
 FILTER_CLOSURE = 0
 FILTER_REFERENCE_SEEDED = 1
 FILTER_MODES = {"closure": FILTER_CLOSURE, "reference_seeded": FILTER_REFERENCE_SEEDED}
@@ -83,6 +84,10 @@ def _load():
         "e2sec_phase2_destroy": (None, [vp]),
         "e2sec_phase2_reset": (C.c_int, [vp]),
         "e2sec_phase2_run": (C.c_int, [vp, vp, vp, i32]),
+        "e2sec_phase2_mailbox_handle": (C.c_int, [vp, vp]),
+        "e2sec_phase2_connect": (C.c_int, [vp, vp]),
+        "e2sec_phase2_connect_local": (C.c_int, [vp, vp]),
+        "e2sec_phase2_run_ring": (C.c_int, [vp, vp, vp, i32, C.c_uint32, C.c_uint32]),
         "e2sec_phase2_state_get": (C.c_int, [vp, vp]),
         "e2sec_phase2_state_set": (C.c_int, [vp, vp]),
         "e2sec_phase2_sync": (C.c_int, [vp, vp]),

@@ -1037,7 +1037,9 @@ struct e2sec_phase2 {
     cudaStream_t stream = nullptr;
     cudaEvent_t ready = nullptr, done = nullptr;
     Phase2Dev a;
-    DevBuf state, cols, col_frame, n_cols;
+    DevBuf state, cols, col_frame, n_cols, mailbox;
+    void *peer_mailbox = nullptr;               // the next rank's mailbox, opened from its IPC handle ...
+    bool peer_is_ipc = false;                   // ... or an object of this very process (e2sec_phase2_connect_local)
 };
 
 static void phase2_initial_state(Phase2State &s)
@@ -1085,12 +1087,15 @@ extern "C" int e2sec_phase2_create(e2sec_ctx *ctx, int32_t max_columns, e2sec_ph
               cudaEventCreateWithFlags(&q->ready, cudaEventDisableTiming) == cudaSuccess &&
               cudaEventCreateWithFlags(&q->done, cudaEventDisableTiming) == cudaSuccess;
     ok = ok && !ensure(ctx, q->state, sizeof(Phase2State)) && !ensure(ctx, q->cols, (size_t)max_columns * E2_P2_COL) &&
-         !ensure(ctx, q->col_frame, (size_t)max_columns * sizeof(int)) && !ensure(ctx, q->n_cols, sizeof(int));
+         !ensure(ctx, q->col_frame, (size_t)max_columns * sizeof(int)) && !ensure(ctx, q->n_cols, sizeof(int)) &&
+         !ensure(ctx, q->mailbox, sizeof(Phase2Mailbox)) && cudaMemset(q->mailbox.p, 0, sizeof(Phase2Mailbox)) == cudaSuccess;
     if (!ok) { e2sec_phase2_destroy(q); return fail(ctx, E2SEC_ERR_CUDA, "e2sec_phase2_create: cannot allocate"); }
     a.state = (Phase2State *)q->state.p;
     a.cols = (unsigned char *)q->cols.p;
     a.col_frame = (int *)q->col_frame.p;
     a.n_cols = (int *)q->n_cols.p;
+    a.inbox = (Phase2Mailbox *)q->mailbox.p;
+    a.timeout_ns = 20000000000ull;
     *out = q;
     return e2sec_phase2_reset(q);
 }
@@ -1100,7 +1105,8 @@ extern "C" void e2sec_phase2_destroy(e2sec_phase2 *q)
     if (!q) return;
     cudaSetDevice(q->ctx->device);
     if (q->stream) cudaStreamSynchronize(q->stream);
-    for (DevBuf *b : {&q->state, &q->cols, &q->col_frame, &q->n_cols})
+    if (q->peer_mailbox && q->peer_is_ipc) cudaIpcCloseMemHandle(q->peer_mailbox);
+    for (DevBuf *b : {&q->state, &q->cols, &q->col_frame, &q->n_cols, &q->mailbox})
         if (b->p) cudaFree(b->p);
     if (q->ready) cudaEventDestroy(q->ready);
     if (q->done) cudaEventDestroy(q->done);
@@ -1121,12 +1127,77 @@ extern "C" int e2sec_phase2_reset(e2sec_phase2 *q)
     return E2SEC_OK;
 }
 
+static_assert(sizeof(cudaIpcMemHandle_t) <= E2SEC_IPC_HANDLE_BYTES, "IPC handle size");
+
+extern "C" int e2sec_phase2_mailbox_handle(e2sec_phase2 *q, void *handle)
+{
+    if (!q || !handle) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, q->mailbox.p));
+    memset(handle, 0, E2SEC_IPC_HANDLE_BYTES);
+    memcpy(handle, &h, sizeof(h));
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_connect(e2sec_phase2 *q, const void *next_handle)
+{
+    if (!q || !next_handle) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    if (q->peer_mailbox && q->peer_is_ipc) cudaIpcCloseMemHandle(q->peer_mailbox);
+    q->peer_mailbox = nullptr;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, next_handle, sizeof(h));
+    CU(cudaIpcOpenMemHandle(&q->peer_mailbox, h, cudaIpcMemLazyEnablePeerAccess));
+    q->peer_is_ipc = true;
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_phase2_connect_local(e2sec_phase2 *q, e2sec_phase2 *next)
+{
+    if (!q || !next) return E2SEC_ERR_ARG;
+    e2sec_ctx *ctx = q->ctx;
+    cudaSetDevice(ctx->device);
+    if (q->peer_mailbox && q->peer_is_ipc) cudaIpcCloseMemHandle(q->peer_mailbox);
+    q->peer_mailbox = nullptr;
+    if (next->ctx->device != ctx->device) {
+        int can = 0;
+        CU(cudaDeviceCanAccessPeer(&can, ctx->device, next->ctx->device));
+        if (!can) return fail(ctx, E2SEC_ERR_CUDA, "e2sec_phase2_connect_local: no peer access between the two devices");
+        const cudaError_t e = cudaDeviceEnablePeerAccess(next->ctx->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CU(e);
+        cudaGetLastError();
+    }
+    q->peer_mailbox = next->mailbox.p;
+    q->peer_is_ipc = false;
+    return E2SEC_OK;
+}
+
+static int phase2_launch(e2sec_phase2 *q, e2sec_ctx *src, const double *records_dev, int32_t n_frames, uint32_t wait_ticket,
+                         uint32_t post_ticket);
+
 extern "C" int e2sec_phase2_run(e2sec_phase2 *q, e2sec_ctx *src, const double *records_dev, int32_t n_frames)
+{
+    return phase2_launch(q, src, records_dev, n_frames, 0u, 0u);
+}
+
+extern "C" int e2sec_phase2_run_ring(e2sec_phase2 *q, e2sec_ctx *src, const double *records_dev, int32_t n_frames,
+                                     uint32_t wait_ticket, uint32_t post_ticket)
+{
+    if (!q) return E2SEC_ERR_ARG;
+    if (post_ticket && !q->peer_mailbox) return fail(q->ctx, E2SEC_ERR_STATE, "e2sec_phase2_run_ring: e2sec_phase2_connect has not been called");
+    return phase2_launch(q, src, records_dev, n_frames, wait_ticket, post_ticket);
+}
+
+static int phase2_launch(e2sec_phase2 *q, e2sec_ctx *src, const double *records_dev, int32_t n_frames, uint32_t wait_ticket,
+                         uint32_t post_ticket)
 {
     if (!q || !records_dev || n_frames < 0) return E2SEC_ERR_ARG;
     e2sec_ctx *ctx = q->ctx;
     cudaSetDevice(ctx->device);
-    if (n_frames == 0) return E2SEC_OK;
+    if (n_frames == 0 && !wait_ticket && !post_ticket) return E2SEC_OK;
     if (src) {                                   // the records are produced on src's stream
         CU(cudaEventRecord(q->ready, src->stream));
         CU(cudaStreamWaitEvent(q->stream, q->ready, 0));
@@ -1134,6 +1205,9 @@ extern "C" int e2sec_phase2_run(e2sec_phase2 *q, e2sec_ctx *src, const double *r
     Phase2Dev a = q->a;
     a.records = records_dev;
     a.n_frames = n_frames;
+    a.wait_ticket = wait_ticket;
+    a.post_ticket = post_ticket;
+    a.outbox = (Phase2Mailbox *)q->peer_mailbox;
     phase2_kernel<<<1, E2_P2_THREADS, 0, q->stream>>>(a);
     ++ctx->launches;
     CU(cudaGetLastError());

@@ -38,6 +38,15 @@ struct Phase2State {               // POD; e2sec.h: E2SEC_PHASE2_STATE_BYTES
     unsigned char last[E2_P2_COL];
 };
 
+// A rank's inbox for the state of a frame-sharded sequence (e2sec_phase2_run_ring): the kernel of the rank that ran the
+// batch in front writes the state and then the ticket straight into this memory over NVLink (peer access through a CUDA IPC
+// handle); the kernel that needs it polls the ticket.  No host, no collective on the way.
+struct Phase2Mailbox {
+    Phase2State state;
+    unsigned ticket;
+    unsigned pad[3];
+};
+
 struct Phase2Dev {
     const double *records;
     int n_frames, rec_doubles;
@@ -49,6 +58,11 @@ struct Phase2Dev {
     int *col_frame;                // max_columns
     int *n_cols;                   // columns this object holds (a shard's own, unlike state->n_columns)
     int max_columns;
+    Phase2Mailbox *inbox;          // this rank's mailbox (local memory, written by the previous rank)
+    Phase2Mailbox *outbox;         // the next rank's mailbox (peer memory)
+    unsigned wait_ticket;          // != 0: start from the state posted under this ticket instead of *state
+    unsigned post_ticket;          // != 0: post the final state to the outbox under this ticket
+    unsigned long long timeout_ns; // give up waiting after this long (E2SEC_ERR_STATE)
 };
 
 // inclusive block scans over E2_P2_THREADS threads; `tot` (shared, 32 ints) is scratch; every thread also gets the total
@@ -79,7 +93,30 @@ __global__ void __launch_bounds__(E2_P2_THREADS) phase2_kernel(Phase2Dev a)
     auto op_max = [](int x, int y) { return x > y ? x : y; };
     auto op_or = [](int x, int y) { return x | y; };
     auto op_add = [](int x, int y) { return x + y; };
-    if (tid == 0) st = *a.state;
+    if (a.wait_ticket) {
+        // the state of everything in front of these frames comes from the rank that ran it: wait for its ticket
+        __shared__ int arrived;
+        if (tid == 0) {
+            unsigned long long t0;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+            int ok = 1;
+            while (*((volatile unsigned *)&a.inbox->ticket) != a.wait_ticket) {
+                __nanosleep(100);
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+                if (t1 - t0 > a.timeout_ns) { ok = 0; break; }
+            }
+            __threadfence_system();
+            arrived = ok;
+        }
+        __syncthreads();
+        const volatile unsigned *src = (const volatile unsigned *)&a.inbox->state;
+        unsigned *dst = (unsigned *)&st;
+        if (arrived) for (int i = tid; i < (int)(sizeof(Phase2State) / 4); i += E2_P2_THREADS) dst[i] = src[i];
+        else for (int i = tid; i < (int)(sizeof(Phase2State) / 4); i += E2_P2_THREADS) dst[i] = ((const unsigned *)a.state)[i];
+        __syncthreads();
+        if (!arrived && tid == 0) st.error = E2SEC_ERR_STATE;
+    } else if (tid == 0) st = *a.state;
     __syncthreads();
     for (int base = 0; base < a.n_frames; base += E2_P2_THREADS) {
         const int f = base + tid;
@@ -208,4 +245,14 @@ __global__ void __launch_bounds__(E2_P2_THREADS) phase2_kernel(Phase2Dev a)
         __syncthreads();
     }
     if (tid == 0) *a.state = st;
+    if (a.post_ticket) {
+        // hand the state to the rank that runs the next frames: payload, system-wide fence, then the ticket
+        __syncthreads();
+        volatile unsigned *dst = (volatile unsigned *)&a.outbox->state;
+        const unsigned *src = (const unsigned *)&st;
+        for (int i = tid; i < (int)(sizeof(Phase2State) / 4); i += E2_P2_THREADS) dst[i] = src[i];
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) { *((volatile unsigned *)&a.outbox->ticket) = a.post_ticket; __threadfence_system(); }
+    }
 }

@@ -327,6 +327,31 @@ class Phase2:
         base = lib.e2sec_records_dev(engine._h)
         self.run(base + skip * nat.record_doubles(self.K) * 8, n_frames - skip, src=engine)
 
+    def mailbox_handle(self):
+        """CUDA IPC handle (64 bytes) of this object's mailbox, for the rank that runs the frames in front."""
+        h = np.zeros(nat.IPC_HANDLE_BYTES, np.uint8)
+        self._check(lib.e2sec_phase2_mailbox_handle(self._h, ptr(h)), "e2sec_phase2_mailbox_handle")
+        return h
+
+    def connect(self, next_handle):
+        """Opens the mailbox of the rank that runs the NEXT frames (peer memory over NVLink)."""
+        h = np.ascontiguousarray(next_handle, np.uint8)
+        self._check(lib.e2sec_phase2_connect(self._h, ptr(h)), "e2sec_phase2_connect")
+
+    def connect_local(self, nxt):
+        """The same for a Phase2 object of this very process."""
+        self._check(lib.e2sec_phase2_connect_local(self._h, nxt._h), "e2sec_phase2_connect_local")
+
+    def run_ring(self, records_dev_ptr, n_frames, wait_ticket, post_ticket, src=None):
+        self._check(lib.e2sec_phase2_run_ring(self._h, src._h if src is not None else None, C.c_void_p(int(records_dev_ptr)),
+                                              int(n_frames), int(wait_ticket), int(post_ticket)), "e2sec_phase2_run_ring")
+
+    def run_ring_engine_batch(self, engine, n_frames, skip, wait_ticket, post_ticket):
+        """run_engine_batch whose kernel takes the state from its mailbox (wait_ticket) and posts it on (post_ticket)."""
+        base = lib.e2sec_records_dev(engine._h)
+        self._check(lib.e2sec_phase2_run_ring(self._h, engine._h, C.c_void_p(base + skip * nat.record_doubles(self.K) * 8),
+                                              int(n_frames - skip), int(wait_ticket), int(post_ticket)), "e2sec_phase2_run_ring")
+
     def state_get(self, dst_ptr=None):
         if dst_ptr is None:
             buf = np.zeros(nat.PHASE2_STATE_BYTES, np.uint8)

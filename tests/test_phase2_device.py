@@ -179,3 +179,39 @@ def test_phase2_reports_out_of_order_records(engine):
     with pytest.raises(E2SecError):
         p2.sync()
     p2.close()
+
+
+def test_phase2_ring_through_mailboxes(engine):
+    """The state handed from kernel to kernel through mailboxes (e2sec_phase2_run_ring): pieces of one sequence dealt in
+    turn to three Phase2 objects whose kernels wait for / post tickets on the device -- the columns, merged by frame id,
+    equal the single object's.  (Across processes the mailbox is opened through its CUDA IPC handle; bench.py does that.)"""
+    from manipulationlibrary_b200.engine import Phase2, Resolver, columns_table
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    s = SyntheticStream(width=160, height=120, n_objects=3, config=98, cycle=16)
+    ids = np.arange(0, 96, dtype=np.int32)
+    p, keep, rec = _stream_records(engine, s, ids)
+    r = Resolver(p, keep)
+    r.feed(rec)
+    table, fc = r.table()
+    t = _dev(rec)
+    width = rec.shape[1] * 8
+    ring = [Phase2(engine, max_columns=128) for _ in range(3)]
+    for i, q in enumerate(ring):
+        q.connect_local(ring[(i + 1) % 3])
+    edges = list(range(0, 96, 8)) + [96]
+    n = len(edges) - 1
+    for g in range(n):
+        ring[g % 3].run_ring(t.data_ptr() + edges[g] * width, edges[g + 1] - edges[g], 100 + g if g else 0, 101 + g if g < n - 1 else 0)
+    cols, frames = [], []
+    for q in ring:
+        c, f = q.fetch()
+        cols.append(c)
+        frames.append(f)
+    cols, frames = np.concatenate(cols), np.concatenate(frames)
+    order = np.argsort(frames, kind="stable")
+    t3, fc3 = columns_table(cols[order], frames[order], 3)
+    assert (t3 == table).all() and fc3 == fc
+    assert ring[(n - 1) % 3].state() == r.state()
+    for q in ring:
+        q.close()
+    r.close()
