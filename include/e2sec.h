@@ -141,6 +141,25 @@ int e2sec_process_batch_labels8(e2sec_ctx *ctx, const float *xyz, const uint8_t 
 int e2sec_process_batch_labels8_async(e2sec_ctx *ctx, const float *xyz, const uint8_t *labels, int32_t n_frames,
                                       int32_t label_w, int32_t label_h, int32_t width, int32_t height,
                                       const int32_t *frame_ids, int on_device, double *records);
+/* The same pass with the FILES as input (input decode on the device): what the reference reads with
+ * o3d.io.read_point_cloud (:1441) and pd.read_csv (:1391).  pcd_files holds the n_frames PCD v0.7 files back to back, file f
+ * at [pcd_offsets[f], pcd_offsets[f + 1]); they must be DATA binary_compressed with float32 x, y, z as their first three
+ * fields and width * height = n_points points (any other cloud: e2sec_read_pcd_xyz + e2sec_process_batch).  label_files
+ * likewise holds the label files -- label_h lines of label_w whitespace-separated non-negative integers each.  Headers are
+ * read on the host (a few hundred bytes per file); the compressed payloads and the text are uploaded as they are, LZF-decoded
+ * and parsed on the device (csrc/lzf.cuh) on the context's copy stream, under the kernels of the batch before.  Host memory
+ * (pinned for the _async form, and untouched until e2sec_sync); records as in e2sec_process_batch.                         */
+int e2sec_process_batch_pcd(e2sec_ctx *ctx, const uint8_t *pcd_files, const int64_t *pcd_offsets, const uint8_t *label_files,
+                            const int64_t *label_offsets, int32_t n_frames, int32_t label_w, int32_t label_h, int32_t width,
+                            int32_t height, const int32_t *frame_ids, double *records);
+int e2sec_process_batch_pcd_async(e2sec_ctx *ctx, const uint8_t *pcd_files, const int64_t *pcd_offsets, const uint8_t *label_files,
+                                  const int64_t *label_offsets, int32_t n_frames, int32_t label_w, int32_t label_h, int32_t width,
+                                  int32_t height, const int32_t *frame_ids, double *records);
+/* device addresses of the decoded inputs of the batch queued last from host memory or files: xyz n_frames x n_points x 3
+ * float32, labels n_frames x (label_w * label_h) int32 (valid until the batch after the next one is queued)              */
+int e2sec_staged_inputs_dev(e2sec_ctx *ctx, const float **xyz_dev, const int32_t **labels_dev);
+/* ... and copied to the host (waits for the context's stream): what the device decoders made of the files */
+int e2sec_copy_staged_inputs(e2sec_ctx *ctx, float *xyz, int32_t *labels, int32_t n_frames, int32_t label_size);
 const double *e2sec_records_dev(e2sec_ctx *ctx);
 /* Stream-ordered copy of records [first, first + count) of the batch queued last to dst (host or device memory): a shard
  * that keeps its records on the device for e2sec_phase2_run, minus the halo frame's.  Does not wait.                  */
@@ -280,7 +299,7 @@ int e2sec_dissimilarity(e2sec_ctx *ctx, const char *codes, const int64_t *offset
 /* device time of the two kernels of the last e2sec_dissimilarity call, in ms */
 int e2sec_dissimilarity_ms(e2sec_ctx *ctx, float *ms);
 
-/* ---- input decode (host): o3d.io.read_point_cloud :1441 and pd.read_csv :1391 -------------------- */
+/* ---- input decode on the host (any PCD v0.7 flavour; e2sec_process_batch_pcd decodes the common one on the device) ---- */
 int e2sec_read_pcd_xyz(const char *path, float *xyz, int64_t capacity_points, int32_t *width,
                        int32_t *height);
 int e2sec_read_labels(const char *path, int32_t *labels, int64_t capacity, int32_t *rows, int32_t *cols);

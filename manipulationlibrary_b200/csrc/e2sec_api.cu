@@ -21,6 +21,9 @@
 #include "contact.cuh"
 #include "dissim.cuh"
 #include "phase2.cuh"
+#include "lzf.cuh"
+
+int e2sec_pcd_locate(const unsigned char *file, size_t len, long long *payload, unsigned *comp, long long *points, int *width, int *height);   // pcd_reader.cpp
 
 #define E2_MAX_REFINE 6        // histogram rounds launched per batch (each narrows the key interval 256x)
 
@@ -47,6 +50,13 @@ struct e2sec_ctx {
     Dev d;
     std::vector<DevBuf *> bufs;
     DevBuf lab8_stage, gsub, amb_count, cell_state;
+    DevBuf pcd_stage, pcd_frames, pcd_status, ltext_stage, ltext_off;       // e2sec_process_batch_pcd: file bytes, per-frame jobs
+    struct PcdJob {                                                          // the batch e2sec_process_batch_pcd is handing over
+        const unsigned char *files = nullptr, *ltext = nullptr;
+        size_t files_bytes = 0, ltext_bytes = 0;
+        std::vector<LzfFrame> frames;
+        std::vector<long long> loff;
+    } pcd;
     DevBuf ds_codes, ds_off, ds_ncols, ds_packed, ds_counts, ds_D;     // e2sec_dissimilarity
     cudaEvent_t ds_ev[2];
     bool ds_timed = false;
@@ -155,7 +165,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
     cudaFuncSetAttribute(cell_filter_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
-    ctx->bufs = {&ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->cell_state, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
+    ctx->bufs = {&ctx->pcd_stage, &ctx->pcd_frames, &ctx->pcd_status, &ctx->ltext_stage, &ctx->ltext_off, &ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->cell_state, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
                  &ctx->radius, &ctx->rs, &ctx->hist, &ctx->cand, &ctx->cand_n, &ctx->seed_pos, &ctx->member,
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
@@ -563,6 +573,7 @@ static int check_device_error(e2sec_ctx *ctx)
     CU(cudaStreamSynchronize(ctx->stream));
     if (err == E2SEC_ERR_CAPACITY) return fail(ctx, err, "stored points exceed the frame capacity");
     if (err == E2SEC_ERR_STATE) return fail(ctx, err, "radius selection lost its rank (internal error)");
+    if (err == E2SEC_ERR_IO) return fail(ctx, err, "a compressed cloud is malformed, or a label file does not hold label_w x label_h non-negative integers");
     if (err) return fail(ctx, err, "device-side error");
     return E2SEC_OK;
 }
@@ -609,7 +620,38 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labe
     cudaEventRecord(ctx->ev[0], st);
     const size_t n_lab = (size_t)n_frames * (size_t)lsz;
     if (label_bytes == 1 && ensure(ctx, ctx->lab8_stage, (size_t)2 * ctx->maxF * N)) return E2SEC_ERR_CUDA;
-    if (on_device && label_bytes == 4) {
+    if (label_bytes == -1) {
+        // e2sec_process_batch_pcd: the FILES travel (compressed clouds, label text); the copy stream uploads them and decodes
+        // them into the staging slot while the main stream still works on the previous batch
+        const size_t slack = 4096;                  // the decoder's input ring reads whole aligned 1 KB blocks around a stream
+        const size_t fb = (ctx->pcd.files_bytes + 15) / 16 * 16 + 2 * slack, lb = (ctx->pcd.ltext_bytes + 15) / 16 * 16 + 64;
+        if (ctx->pcd_stage.bytes < 2 * fb && ensure(ctx, ctx->pcd_stage, 2 * fb + fb / 2)) return E2SEC_ERR_CUDA;
+        if (ctx->ltext_stage.bytes < 2 * lb && ensure(ctx, ctx->ltext_stage, 2 * lb + lb / 2)) return E2SEC_ERR_CUDA;
+        if (ensure(ctx, ctx->pcd_frames, (size_t)2 * ctx->maxF * sizeof(LzfFrame)) || ensure(ctx, ctx->pcd_status, (size_t)4 * ctx->maxF * sizeof(int)) ||
+            ensure(ctx, ctx->ltext_off, (size_t)2 * (ctx->maxF + 1) * sizeof(long long)))
+            return E2SEC_ERR_CUDA;
+        stage_slot = (int)(ctx->stage_idx++ & 1u);
+        float *xs = (float *)ctx->xyz_stage.p + (size_t)stage_slot * ctx->maxF * N * 3;
+        int *ls = (int *)ctx->lab_stage.p + (size_t)stage_slot * ctx->maxF * N;
+        unsigned char *fs = (unsigned char *)ctx->pcd_stage.p + (size_t)stage_slot * (ctx->pcd_stage.bytes / 2 / 16 * 16) + slack;
+        unsigned char *ts = (unsigned char *)ctx->ltext_stage.p + (size_t)stage_slot * (ctx->ltext_stage.bytes / 2 / 16 * 16);
+        LzfFrame *fj = (LzfFrame *)ctx->pcd_frames.p + (size_t)stage_slot * ctx->maxF;
+        int *stt = (int *)ctx->pcd_status.p + (size_t)stage_slot * 2 * ctx->maxF;      // [clouds][label images]
+        long long *lo = (long long *)ctx->ltext_off.p + (size_t)stage_slot * (ctx->maxF + 1);
+        cudaStream_t cs = ctx->copy_stream;
+        if (ctx->slot_used[stage_slot]) CU(cudaStreamWaitEvent(cs, ctx->slot_free[stage_slot], 0));
+        CU(cudaMemcpyAsync(fs, ctx->pcd.files, ctx->pcd.files_bytes, cudaMemcpyHostToDevice, cs));
+        CU(cudaMemcpyAsync(ts, ctx->pcd.ltext, ctx->pcd.ltext_bytes, cudaMemcpyHostToDevice, cs));
+        CU(cudaMemcpyAsync(fj, ctx->pcd.frames.data(), n_frames * sizeof(LzfFrame), cudaMemcpyHostToDevice, cs));
+        CU(cudaMemcpyAsync(lo, ctx->pcd.loff.data(), (n_frames + 1) * sizeof(long long), cudaMemcpyHostToDevice, cs));
+        lzf_decode_kernel<<<n_frames, 32, 0, cs>>>(fs, fj, xs, N, stt, (int *)ctx->error.p); LAUNCHED();
+        label_text_kernel<<<n_frames, E2_LT_THREADS, 0, cs>>>(ts, lo, ls, (int)lsz, stt + ctx->maxF, (int *)ctx->error.p); LAUNCHED();
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(ctx->copy_done[stage_slot], cs));
+        CU(cudaStreamWaitEvent(st, ctx->copy_done[stage_slot], 0));
+        d.xyz = xs;
+        d.labels = ls;
+    } else if (on_device && label_bytes == 4) {
         d.xyz = xyz;
         d.labels = (const int *)labels;
     } else {
@@ -721,6 +763,85 @@ extern "C" int e2sec_process_batch_labels8_async(e2sec_ctx *ctx, const float *xy
                                                  const int32_t *frame_ids, int on_device, double *records)
 {
     return process_batch_impl(ctx, xyz, labels, 1, n_frames, label_w, label_h, width, height, frame_ids, on_device, records, false);
+}
+
+// e2sec_process_batch_pcd: headers are read here (a few hundred bytes per file), everything else happens on the device
+static int process_batch_pcd(e2sec_ctx *ctx, const uint8_t *pcd_files, const int64_t *pcd_offsets, const uint8_t *label_files,
+                             const int64_t *label_offsets, int32_t n_frames, int32_t label_w, int32_t label_h, int32_t width,
+                             int32_t height, const int32_t *frame_ids, double *records, bool wait)
+{
+    if (!ctx) return E2SEC_ERR_ARG;
+    if (!ctx->configured) return fail(ctx, E2SEC_ERR_STATE, "e2sec_configure has not been called");
+    if (!pcd_files || !pcd_offsets || !label_files || !label_offsets || !frame_ids) return fail(ctx, E2SEC_ERR_ARG, "null input");
+    if (n_frames < 0 || n_frames > ctx->maxF) return fail(ctx, E2SEC_ERR_CAPACITY, "n_frames exceeds max_frames");
+    if (n_frames == 0) return E2SEC_OK;
+    if ((long long)width * height != ctx->N) return fail(ctx, E2SEC_ERR_ARG, "width * height must equal n_points of e2sec_configure");
+    ctx->pcd.frames.resize(n_frames);
+    ctx->pcd.loff.assign(label_offsets, label_offsets + n_frames + 1);
+    for (int f = 0; f < n_frames; ++f) {
+        const int64_t a = pcd_offsets[f], b = pcd_offsets[f + 1];
+        if (a < pcd_offsets[0] || b < a) return fail(ctx, E2SEC_ERR_ARG, "pcd_offsets must be non-decreasing");
+        long long payload = 0, points = 0;
+        unsigned comp = 0;
+        int w = 0, h = 0;
+        const int rc = e2sec_pcd_locate(pcd_files + a, (size_t)(b - a), &payload, &comp, &points, &w, &h);
+        if (rc == E2SEC_ERR_ARG)
+            return fail(ctx, rc, "cloud " + std::to_string(f) + " is not a binary_compressed PCD with float32 x, y, z as its first fields "
+                                 "(decode it with e2sec_read_pcd_xyz and use e2sec_process_batch)");
+        if (rc) return fail(ctx, rc, "cloud " + std::to_string(f) + ": malformed PCD header");
+        if (points != ctx->N) return fail(ctx, E2SEC_ERR_ARG, "cloud " + std::to_string(f) + " holds " + std::to_string(points) + " points, the context was configured for " + std::to_string(ctx->N));
+        ctx->pcd.frames[f].payload = (long long)(a - pcd_offsets[0]) + payload;
+        ctx->pcd.frames[f].comp = comp;
+        ctx->pcd.frames[f].need = (unsigned)(12ll * points);
+        if (label_offsets[f + 1] < label_offsets[f]) return fail(ctx, E2SEC_ERR_ARG, "label_offsets must be non-decreasing");
+    }
+    for (auto &v : ctx->pcd.loff) v -= label_offsets[0];
+    ctx->pcd.files = pcd_files + pcd_offsets[0];
+    ctx->pcd.files_bytes = (size_t)(pcd_offsets[n_frames] - pcd_offsets[0]);
+    ctx->pcd.ltext = label_files + label_offsets[0];
+    ctx->pcd.ltext_bytes = (size_t)(label_offsets[n_frames] - label_offsets[0]);
+    return process_batch_impl(ctx, (const float *)pcd_files, label_files, -1, n_frames, label_w, label_h, width, height, frame_ids, 0,
+                              records, wait);
+}
+
+extern "C" int e2sec_process_batch_pcd(e2sec_ctx *ctx, const uint8_t *pcd_files, const int64_t *pcd_offsets, const uint8_t *label_files,
+                                       const int64_t *label_offsets, int32_t n_frames, int32_t label_w, int32_t label_h,
+                                       int32_t width, int32_t height, const int32_t *frame_ids, double *records)
+{
+    return process_batch_pcd(ctx, pcd_files, pcd_offsets, label_files, label_offsets, n_frames, label_w, label_h, width, height,
+                             frame_ids, records, true);
+}
+
+extern "C" int e2sec_process_batch_pcd_async(e2sec_ctx *ctx, const uint8_t *pcd_files, const int64_t *pcd_offsets,
+                                             const uint8_t *label_files, const int64_t *label_offsets, int32_t n_frames,
+                                             int32_t label_w, int32_t label_h, int32_t width, int32_t height,
+                                             const int32_t *frame_ids, double *records)
+{
+    return process_batch_pcd(ctx, pcd_files, pcd_offsets, label_files, label_offsets, n_frames, label_w, label_h, width, height,
+                             frame_ids, records, false);
+}
+
+// the staged inputs of the batch queued last (device memory): what the decoders produced, for callers that want to look
+extern "C" int e2sec_staged_inputs_dev(e2sec_ctx *ctx, const float **xyz_dev, const int32_t **labels_dev)
+{
+    if (!ctx || !ctx->configured) return E2SEC_ERR_ARG;
+    const int slot = (int)((ctx->stage_idx - 1u) & 1u);
+    if (xyz_dev) *xyz_dev = (const float *)ctx->xyz_stage.p + (size_t)slot * ctx->maxF * ctx->N * 3;
+    if (labels_dev) *labels_dev = (const int32_t *)ctx->lab_stage.p + (size_t)slot * ctx->maxF * ctx->N;
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_copy_staged_inputs(e2sec_ctx *ctx, float *xyz, int32_t *labels, int32_t n_frames, int32_t label_size)
+{
+    if (!ctx || !ctx->configured || n_frames < 0 || n_frames > ctx->maxF || label_size < 0 || label_size > ctx->N) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    const float *x;
+    const int32_t *l;
+    e2sec_staged_inputs_dev(ctx, &x, &l);
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (xyz) CU(cudaMemcpy(xyz, x, (size_t)n_frames * ctx->N * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+    if (labels) CU(cudaMemcpy(labels, l, (size_t)n_frames * label_size * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    return E2SEC_OK;
 }
 
 extern "C" int e2sec_copy_records(e2sec_ctx *ctx, double *dst, int32_t first, int32_t count)

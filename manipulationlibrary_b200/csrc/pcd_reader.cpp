@@ -105,6 +105,36 @@ bool parse_header(const std::vector<unsigned char> &buf, Header &h)
 
 }   // namespace
 
+// Where the LZF stream of a binary_compressed cloud lies inside its file (for the device decoder, lzf.cuh): the header is
+// read here, nothing else.  Only the layout the device decoder handles is accepted: x, y, z as the first three fields,
+// float32 each, so that the first 12 * POINTS decoded bytes are the x, y and z planes.
+int e2sec_pcd_locate(const unsigned char *file, size_t len, long long *payload, unsigned *comp, long long *points, int *width, int *height)
+{
+    std::vector<unsigned char> head(file, file + (len < 4096 ? len : 4096));       // a header is a few hundred bytes
+    Header h;
+    if (!parse_header(head, h)) return E2SEC_ERR_IO;
+    const size_t nf = h.fields.size();
+    if (nf < 3 || h.sizes.size() != nf || h.types.size() != nf) return E2SEC_ERR_IO;
+    if (h.counts.empty()) h.counts.assign(nf, 1);
+    if (h.counts.size() != nf) return E2SEC_ERR_IO;
+    if (h.data != "binary_compressed") return E2SEC_ERR_ARG;
+    for (int a = 0; a < 3; ++a)
+        if (h.fields[a] != std::string(1, "xyz"[a]) || h.sizes[a] != 4 || h.types[a] != "F" || h.counts[a] != 1) return E2SEC_ERR_ARG;
+    if (h.points <= 0) h.points = h.width * h.height;
+    if (h.points <= 0 || h.points > (1ll << 28)) return E2SEC_ERR_IO;
+    if (h.body + 8 > len) return E2SEC_ERR_IO;
+    uint32_t c, raw;
+    memcpy(&c, file + h.body, 4);
+    memcpy(&raw, file + h.body + 4, 4);
+    if ((uint64_t)c > len - h.body - 8 || (uint64_t)raw < (uint64_t)12 * (uint64_t)h.points) return E2SEC_ERR_IO;
+    *payload = (long long)h.body + 8;
+    *comp = c;
+    *points = h.points;
+    if (width) *width = (int)h.width;
+    if (height) *height = (int)h.height;
+    return E2SEC_OK;
+}
+
 extern "C" int e2sec_read_pcd_xyz(const char *path, float *xyz, int64_t capacity_points, int32_t *width, int32_t *height)
 {
     if (!path || !xyz) return E2SEC_ERR_ARG;

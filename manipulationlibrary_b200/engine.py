@@ -66,6 +66,38 @@ class Engine:
                     "e2sec_process_batch")
         return rec
 
+    def process_batch_files(self, pcd_blob, pcd_offsets, label_blob, label_offsets, frame_ids, label_shape, image_shape,
+                            records=None, wait=True):
+        """The FILES as input: pcd_blob / label_blob are uint8 arrays holding the PCD (binary_compressed) and label files back
+        to back, *_offsets (F + 1) their boundaries.  Clouds are LZF-decoded and the label text is parsed on the device.
+        With wait=False the buffers (pinned) must stay untouched until sync() and `records` must be given (pinned)."""
+        pcd_blob = np.ascontiguousarray(pcd_blob, np.uint8).reshape(-1)
+        label_blob = np.ascontiguousarray(label_blob, np.uint8).reshape(-1)
+        po = np.ascontiguousarray(pcd_offsets, np.int64).reshape(-1)
+        lo = np.ascontiguousarray(label_offsets, np.int64).reshape(-1)
+        fid = np.ascontiguousarray(frame_ids, np.int32).reshape(-1)
+        F = len(fid)
+        if len(po) != F + 1 or len(lo) != F + 1 or po[-1] > len(pcd_blob) or lo[-1] > len(label_blob) or po[0] < 0 or lo[0] < 0:
+            raise ValueError("offsets must hold frames + 1 boundaries inside the blobs")
+        if F > self.max_frames:
+            raise ValueError("%d frames exceed max_frames=%d of configure()" % (F, self.max_frames))
+        lh, lw, h, w = int(label_shape[0]), int(label_shape[1]), int(image_shape[0]), int(image_shape[1])
+        if h * w != self.n_points:
+            raise ValueError("image_shape %r does not match the %d points per frame" % ((h, w), self.n_points))
+        rec = np.empty((F, nat.record_doubles(self.K)), np.float64) if records is None else records
+        fn = lib.e2sec_process_batch_pcd if wait else lib.e2sec_process_batch_pcd_async
+        self._check(fn(self._h, ptr(pcd_blob), ptr(po), ptr(label_blob), ptr(lo), F, lw, lh, w, h, ptr(fid), ptr(rec)),
+                    "e2sec_process_batch_pcd")
+        self._keep_files = (pcd_blob, label_blob, po, lo, fid)
+        return rec
+
+    def staged_inputs(self, n_frames, label_size):
+        """The decoded inputs of the batch queued last, copied back: xyz (F, N, 3) float32, labels (F, label_size) int32."""
+        xyz = np.empty((n_frames, self.n_points, 3), np.float32)
+        lab = np.empty((n_frames, label_size), np.int32)
+        self._check(lib.e2sec_copy_staged_inputs(self._h, ptr(xyz), ptr(lab), int(n_frames), int(label_size)), "e2sec_copy_staged_inputs")
+        return xyz, lab
+
     def process_batch_device(self, xyz_ptr, labels_ptr, n_frames, frame_ids, label_size, records=None,
                              label_shape=None, image_shape=None):
         """Device-resident inputs (raw pointers, e.g. torch tensors' data_ptr())."""

@@ -30,7 +30,35 @@ def _lzf():
         _LIB.oracle_lzf_decompress.restype = ctypes.c_long
         _LIB.oracle_lzf_decompress.argtypes = [ctypes.c_void_p, ctypes.c_size_t,
                                                ctypes.c_void_p, ctypes.c_size_t]
+        _LIB.oracle_lzf_compress.restype = ctypes.c_long
+        _LIB.oracle_lzf_compress.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t]
     return _LIB
+
+
+def lzf_compress(data):
+    """bytes -> LZF stream (oracle/lzf_dec.c: oracle_lzf_compress)."""
+    src = np.frombuffer(bytes(data), np.uint8)
+    out = np.empty(len(src) + len(src) // 16 + 64, np.uint8)
+    n = _lzf().oracle_lzf_compress(src.ctypes.data, len(src), out.ctypes.data, len(out))
+    assert n > 0
+    return out[:n].tobytes()
+
+
+def pcd_binary_compressed(xyz, width, height, rgba=True):
+    """The bytes of a PCD v0.7 binary_compressed file as PCL writes the MANIAC clouds: fields x y z (rgba), SoA payload
+    (all x, all y, all z, all rgba) compressed as ONE LZF stream behind two uint32 (compressed, uncompressed size)."""
+    xyz = np.ascontiguousarray(xyz, np.float32)
+    n = len(xyz)
+    planes = [xyz[:, 0].tobytes(), xyz[:, 1].tobytes(), xyz[:, 2].tobytes()]
+    if rgba:
+        planes.append(np.zeros(n, np.uint32).tobytes())
+    raw = b"".join(planes)
+    comp = lzf_compress(raw)
+    extra = (" rgba", " 4", " U", " 1") if rgba else ("", "", "", "")
+    head = ("# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS x y z%s\nSIZE 4 4 4%s\nTYPE F F F%s\nCOUNT 1 1 1%s\n"
+            "WIDTH %d\nHEIGHT %d\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS %d\nDATA binary_compressed\n"
+            % (extra + (width, height, n))).encode()
+    return head + np.array([len(comp), len(raw)], np.uint32).tobytes() + comp
 
 
 def lzf_decompress_py(data, out_len):
