@@ -86,6 +86,13 @@ def read_frame(pcd_file, label_file):
     return xyz, lab[: rows.value * cols.value].reshape(rows.value, cols.value)
 
 
+def _label_shape(label_file):
+    """(rows, cols) of a label file: lines and numbers per line (host look at one file; the batch is parsed on the device)"""
+    with open(label_file, "rb") as fh:
+        lines = [ln for ln in fh.read().split(b"\n") if ln.strip()]
+    return len(lines), len(lines[0].split())
+
+
 def _check_args(relations, icp, cython):
     if relations not in (1, 2, 3):
         raise ValueError("relations must be 1 (T/N), 2 (+ SSR) or 3 (+ DSR), got %r" % (relations,))
@@ -207,63 +214,92 @@ def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, 
     batch = max(1, int(os.environ.get("E2SEC_BATCH_FRAMES", BATCH_FRAMES)))
     chunks = [todo[s: s + batch] for s in range(0, len(todo), batch)]
 
-    def read_chunk(chunk):
-        xs, ls, ids, lshape = [], [], [], None
-        for i, f in chunk:
-            xyz, label = read_frame(pcl_path + f[0:-7] + "_pc.pcd", label_path + f[0:-7] + "_left-labels.dat")
-            xs.append(xyz)
-            ls.append(label.reshape(-1).astype(np.int32))
-            ids.append(i)
-            lshape = label.shape
-        return np.stack(xs), np.stack(ls), np.array(ids, np.int32), lshape
+    def paths(f):
+        return pcl_path + f[0:-7] + "_pc.pcd", label_path + f[0:-7] + "_left-labels.dat"
 
-    def run_on(dev, xyz, lab, ids, lshape, halo):
-        """One batch as its own little sequence on GPU `dev`: the frame in front of it (halo = (xyz, labels, id) of the last
-        frame of the batch before) goes first and its record is dropped -- the one-frame halo of the frame sharding."""
+    def read_chunk(chunk):
+        """The files of a chunk as they are (clouds that are PCD binary_compressed with x, y, z in front are decoded on the
+        device, csrc/lzf.cuh); any other flavour goes through the host reader frame by frame."""
+        frames = []
+        for i, f in chunk:
+            pp, lp = paths(f)
+            with open(pp, "rb") as fh:
+                pb = fh.read()
+            head = pb[:1024]
+            if b"DATA binary_compressed" in head and b"FIELDS x y z" in head:
+                with open(lp, "rb") as fh:
+                    frames.append(dict(id=i, pcd=pb, lab=fh.read(), paths=(pp, lp)))
+            else:
+                xyz, label = read_frame(pp, lp)
+                frames.append(dict(id=i, xyz=xyz, labels=label.reshape(-1).astype(np.int32), lshape=label.shape, paths=(pp, lp)))
+        if "lshape" not in frames[0]:
+            frames[0]["lshape"] = _label_shape(frames[0]["paths"][1])
+        return frames
+
+    def as_arrays(fr):
+        if "xyz" not in fr:
+            xyz, label = read_frame(*fr["paths"])
+            fr.update(xyz=xyz, labels=label.reshape(-1).astype(np.int32), lshape=label.shape)
+        return fr
+
+    def run_on(dev, frames, halo):
+        """One batch as its own little sequence on GPU `dev`: the frame in front of it (halo = the last frame of the batch
+        before) goes first and its record is dropped -- the one-frame halo of the frame sharding."""
         eng = _state["engines"][dev]
-        kw = dict(label_shape=lshape, image_shape=IMAGE_SHAPE) if lab.shape[1] != xyz.shape[1] else {}
         eng.reset_sequence()
-        if halo is None:
-            return None, eng.process_batch(xyz, lab, ids, **kw)
-        rec = eng.process_batch(np.concatenate([halo[0][None], xyz]), np.concatenate([halo[1][None], lab]),
-                                np.concatenate([[halo[2]], ids]).astype(np.int32), **kw)
-        return rec[0], rec[1:]
+        seq = ([halo] if halo is not None else []) + frames
+        ids = np.array([fr["id"] for fr in seq], np.int32)
+        lshape = frames[0].get("lshape") or _label_shape(frames[0]["paths"][1])
+        if all("pcd" in fr for fr in seq):
+            po = np.concatenate([[0], np.cumsum([len(fr["pcd"]) for fr in seq])]).astype(np.int64)
+            lo = np.concatenate([[0], np.cumsum([len(fr["lab"]) for fr in seq])]).astype(np.int64)
+            rec = eng.process_batch_files(np.frombuffer(b"".join(fr["pcd"] for fr in seq), np.uint8),
+                                          po, np.frombuffer(b"".join(fr["lab"] for fr in seq), np.uint8), lo, ids, lshape,
+                                          IMAGE_SHAPE)
+        else:
+            seq = [as_arrays(fr) for fr in seq]
+            xyz, lab = np.stack([fr["xyz"] for fr in seq]), np.stack([fr["labels"] for fr in seq])
+            kw = dict(label_shape=lshape, image_shape=IMAGE_SHAPE) if lab.shape[1] != xyz.shape[1] else {}
+            rec = eng.process_batch(xyz, lab, ids, **kw)
+        return (rec[0], rec[1:]) if halo is not None else (None, rec)
 
     KEPT = nat.FLAG_HAND_LABEL | nat.FLAG_HAND_POINTS
-    last_kept = None                     # (xyz, labels, id) of the last kept frame fed to the resolver so far
+    last_kept = None                     # the last kept frame fed to the resolver so far
     with ThreadPoolExecutor(max_workers=READ_THREADS) as readers:
         ahead = [readers.submit(read_chunk, c) for c in chunks[: 2]]
         first = ahead[0].result() if ahead else None
         if first is not None:
-            _start_sequence(first[1][0].reshape(first[3]), ground_label, hand_label, support_hand, replace, old, new,
+            rows, cols = first[0]["lshape"]
+            label0 = as_arrays(dict(first[0]))["labels"].reshape(rows, cols) if "labels" not in first[0] else \
+                first[0]["labels"].reshape(rows, cols)
+            _start_sequence(label0, ground_label, hand_label, support_hand, replace, old, new,
                             ignored_labels, cut_labels, thresh, batch, filter_mode, filter_seed, relations, n_devices=64)
         D = len(_state["engines"]) if first is not None else 1
         workers = [ThreadPoolExecutor(max_workers=1) for _ in range(D)]
         window = 2 * D + 2                                               # chunks read ahead / in flight
         ahead += [readers.submit(read_chunk, c) for c in chunks[2: window]]
-        jobs = []                                                        # (data, future of (halo record, records))
+        jobs = []                                                        # (frames, halo, future of (halo record, records))
         prev_last = None                                                 # last frame of the chunk in front (speculative halo)
         for c in range(len(chunks)):
-            data = ahead[c].result()
+            frames = ahead[c].result()
+            ahead[c] = None
             if c + window < len(chunks):
                 ahead.append(readers.submit(read_chunk, chunks[c + window]))
-            xyz, lab, ids, lshape = data
-            jobs.append((data, prev_last, workers[c % D].submit(run_on, c % D, xyz, lab, ids, lshape, prev_last)))
-            prev_last = (xyz[-1], lab[-1], int(ids[-1]))
+            jobs.append((frames, prev_last, workers[c % D].submit(run_on, c % D, frames, prev_last)))
+            prev_last = frames[-1]
             while jobs and (len(jobs) > D or c == len(chunks) - 1):      # collect in order, D batches stay in flight
-                (xyz0, lab0, ids0, lshape0), halo, fut = jobs.pop(0)
+                frames0, halo, fut = jobs.pop(0)
                 hrec, rec = fut.result()
-                want = last_kept[2] if last_kept is not None else -1
-                if halo is not None and (int(hrec[1]) != KEPT or halo[2] != want):
+                want = last_kept["id"] if last_kept is not None else -1
+                if halo is not None and (int(hrec[1]) != KEPT or halo["id"] != want):
                     # the frame in front was not a kept frame (no hand in it): redo the batch behind the real one
-                    _, rec = workers[0].submit(run_on, 0, xyz0, lab0, ids0, lshape0, last_kept).result()
+                    _, rec = workers[0].submit(run_on, 0, frames0, last_kept).result()
                 _state["resolver"].feed(rec)
-                for f, r in zip(ids0, rec):
-                    _state["records"][int(f)] = r
+                for fr, r in zip(frames0, rec):
+                    _state["records"][int(fr["id"])] = r
                 kept = np.nonzero(rec[:, 1].astype(np.int64) == KEPT)[0]
                 if len(kept):
-                    k = int(kept[-1])
-                    last_kept = (xyz0[k], lab0[k], int(ids0[k]))
+                    last_kept = frames0[int(kept[-1])]
         for w in workers:
             w.shutdown()
     table = _table_from_resolver(relations)

@@ -468,6 +468,7 @@ def test_dropin_scripted_scene_relations_and_batches(tmp_path, monkeypatch, want
     own analyse_maniac_manipulation): relations 1, 2 and 3, the hand-as-lowest-label scene among them, batches of 4 frames
     dealt to the device(s) behind their one-frame halo with the file reads running ahead."""
     from manipulationlibrary_b200 import manipulation_analyser as ma
+    from oracle import pcd_io
     from oracle.gen_relation_kats import ROLL, THRESH, scene_from_golden
     z = load_golden("relation_kats")
     z = {k: z[k] for k in z.files}
@@ -491,8 +492,11 @@ def test_dropin_scripted_scene_relations_and_batches(tmp_path, monkeypatch, want
                 continue
             xyz, labels = sc.dense(i // 3)
             with open(pcl / (stem + "_pc.pcd"), "wb") as f:
-                f.write(head)
-                f.write(np.ascontiguousarray(xyz, "<f4").tobytes())
+                if want_relations == 1:                      # DATA binary: decoded by the host reader
+                    f.write(head)
+                    f.write(np.ascontiguousarray(xyz, "<f4").tobytes())
+                else:                                        # binary_compressed like the recordings: decoded on the device
+                    f.write(pcd_io.pcd_binary_compressed(xyz, 640, 480))
             np.savetxt(lab / (stem + "_left-labels.dat"), labels, fmt="%d")
         monkeypatch.chdir(d)
         ma.set_frame0(np.eye(4), ROLL, sc.ground_final)
