@@ -189,6 +189,23 @@ int e2sec_axis_median(e2sec_ctx *ctx, const double *pts, int32_t n, double media
 int e2sec_min_distance(e2sec_ctx *ctx, const double *a, int32_t na, const double *b, int32_t nb,
                        double limit, double *dist);
 
+/* ---- frame-0 setup (csrc/frame0.cuh): the Open3D calls of _getGroundiNewNew (:278-361) and _getTranslation (:212-276) as
+ * device operators; the host side (manipulationlibrary_b200/frame0.py) strings them together deterministically.
+ * segment_plane (:353): counts[h] = number of points with |p . n_h + d_h| < threshold for m <= 64 plane hypotheses
+ * (planes: m x 4, host), and the inlier mask of one plane.                                                              */
+int e2sec_plane_inlier_counts(e2sec_ctx *ctx, const double *pts, int32_t n, const double *planes, int32_t m, double threshold,
+                              int32_t *counts);
+int e2sec_plane_inlier_mask(e2sec_ctx *ctx, const double *pts, int32_t n, const double plane[4], double threshold, uint8_t *mask);
+/* voxel_down_sample (:224, :359): one point per occupied voxel of size `voxel` = the mean of its points (summed in their
+ * order of appearance), voxels in ascending (ix, iy, iz) with origin min_bound - voxel / 2.  out: up to n x 3.            */
+int e2sec_voxel_down_sample(e2sec_ctx *ctx, const double *pts, int32_t n, double voxel, double *out, int32_t *n_out);
+/* One correspondence step of registration_icp (:260, point to point): every source point, moved by `transform` (row-major
+ * 4 x 4), is matched to its exact nearest target point if that lies within max_distance.  stats[0] = matched pairs,
+ * [1] = sum of squared distances, [2..4] / [5..7] = centroids of the matched source / target points, [8..16] = the centred
+ * cross-covariance sum (a - ca)(b - cb)^T row-major.  The 3 x 3 SVD of the update stays with the caller.                  */
+int e2sec_icp_correspondences(e2sec_ctx *ctx, const double *source, int32_t n_source, const double *target, int32_t n_target,
+                              const double transform[16], double max_distance, double stats[17]);
+
 /* ---- phase 2: the sequential part of _process (:1558-1675 selection, :363-1353 relation rows,
  * :1795-1829 / :2000-2007 column emit) over records in frame order.  Host code. -------------------- */
 typedef struct e2sec_resolver e2sec_resolver;

@@ -73,6 +73,10 @@ def _load():
         "e2sec_pairwise_median": (C.c_int, [vp, vp, i32, vp]),
         "e2sec_axis_median": (C.c_int, [vp, vp, i32, vp]),
         "e2sec_min_distance": (C.c_int, [vp, vp, i32, vp, i32, dbl, vp]),
+        "e2sec_plane_inlier_counts": (C.c_int, [vp, vp, i32, vp, i32, dbl, vp]),
+        "e2sec_plane_inlier_mask": (C.c_int, [vp, vp, i32, vp, dbl, vp]),
+        "e2sec_voxel_down_sample": (C.c_int, [vp, vp, i32, dbl, vp, vp]),
+        "e2sec_icp_correspondences": (C.c_int, [vp, vp, i32, vp, i32, vp, dbl, vp]),
         "e2sec_dissimilarity": (C.c_int, [vp, vp, vp, vp, i32, i32, dbl, vp, vp]),
         "e2sec_dissimilarity_ms": (C.c_int, [vp, vp]),
         "e2sec_resolver_create": (C.c_int, [C.POINTER(Params), C.POINTER(vp)]),

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libe2sec.so")
 SOURCES = ["e2sec_api.cu", "resolver.cpp", "pcd_reader.cpp"]
-HEADERS = ["common.cuh", "tma.cuh", "seg_fused.cuh", "seg_stream.cuh", "seg.cuh", "select.cuh", "radius.cuh", "filter.cuh", "pairs.cuh", "cells.cuh", "contact.cuh", "dissim.cuh", "relations.h",
+HEADERS = ["common.cuh", "tma.cuh", "seg_fused.cuh", "seg_stream.cuh", "seg.cuh", "select.cuh", "radius.cuh", "filter.cuh", "pairs.cuh", "cells.cuh", "contact.cuh", "dissim.cuh", "relations.h", "phase2.cuh", "lzf.cuh", "frame0.cuh",
            os.path.join("..", "..", "include", "e2sec.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 

@@ -22,6 +22,7 @@
 #include "dissim.cuh"
 #include "phase2.cuh"
 #include "lzf.cuh"
+#include "frame0.cuh"
 
 int e2sec_pcd_locate(const unsigned char *file, size_t len, long long *payload, unsigned *comp, long long *points, int *width, int *height);   // pcd_reader.cpp
 
@@ -1443,3 +1444,110 @@ extern "C" int e2sec_debug_cell_profile(unsigned long long out[16], int reset)
     return E2SEC_OK;
 }
 #endif
+
+// ---- frame-0 setup geometry (frame0.cuh) ---------------------------------------------------------------------------------
+// small scratch device buffers of the operators below
+struct F0Buf {
+    void *p = nullptr;
+    ~F0Buf() { if (p) cudaFree(p); }
+    int get(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16) == cudaSuccess ? 0 : 1; }
+};
+
+extern "C" int e2sec_plane_inlier_counts(e2sec_ctx *ctx, const double *pts, int32_t n, const double *planes, int32_t m,
+                                         double threshold, int32_t *counts)
+{
+    if (!ctx || !pts || !planes || !counts || n < 1 || m < 1 || m > E2_F0_MAXPLANES) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    F0Buf dp, dpl, dc;
+    if (dp.get(sizeof(double) * 3 * n) || dpl.get(sizeof(double) * 4 * m) || dc.get(sizeof(int) * m)) return fail(ctx, E2SEC_ERR_CUDA, "cudaMalloc failed");
+    CU(cudaMemcpyAsync(dp.p, pts, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(dpl.p, planes, sizeof(double) * 4 * m, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(dc.p, 0, sizeof(int) * m, st));
+    const int grid = std::min((n + E2_F0_THREADS - 1) / E2_F0_THREADS, ctx->sm_count * 8);
+    plane_count_kernel<<<grid, E2_F0_THREADS, 0, st>>>((const double *)dp.p, n, (const double *)dpl.p, m, threshold, (int *)dc.p); LAUNCHED();
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(counts, dc.p, sizeof(int) * m, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_plane_inlier_mask(e2sec_ctx *ctx, const double *pts, int32_t n, const double plane[4], double threshold, uint8_t *mask)
+{
+    if (!ctx || !pts || !plane || !mask || n < 1) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    F0Buf dp, dm;
+    if (dp.get(sizeof(double) * 3 * n) || dm.get(n)) return fail(ctx, E2SEC_ERR_CUDA, "cudaMalloc failed");
+    CU(cudaMemcpyAsync(dp.p, pts, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, st));
+    plane_mask_kernel<<<(n + 255) / 256, 256, 0, st>>>((const double *)dp.p, n, plane[0], plane[1], plane[2], plane[3], threshold, (unsigned char *)dm.p); LAUNCHED();
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(mask, dm.p, n, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_voxel_down_sample(e2sec_ctx *ctx, const double *pts, int32_t n, double voxel, double *out, int32_t *n_out)
+{
+    if (!ctx || !pts || !out || !n_out || n < 1 || !(voxel > 0.0)) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    double lo[3] = {pts[0], pts[1], pts[2]}, hi[3] = {pts[0], pts[1], pts[2]};
+    for (int i = 1; i < n; ++i)
+        for (int a = 0; a < 3; ++a) { const double v = pts[3 * (size_t)i + a]; if (v < lo[a]) lo[a] = v; if (v > hi[a]) hi[a] = v; }
+    double org[3];
+    long long dim[3];
+    for (int a = 0; a < 3; ++a) {
+        if (!std::isfinite(lo[a]) || !std::isfinite(hi[a])) return fail(ctx, E2SEC_ERR_ARG, "e2sec_voxel_down_sample: non-finite coordinates");
+        org[a] = lo[a] - voxel * 0.5;                         // Open3D: voxel_min_bound = min_bound - voxel_size * 0.5
+        dim[a] = (long long)std::floor((hi[a] - org[a]) / voxel) + 2;
+    }
+    if ((double)dim[0] * (double)dim[1] * (double)dim[2] > 9e18) return fail(ctx, E2SEC_ERR_CAPACITY, "e2sec_voxel_down_sample: voxel grid too large");
+    F0Buf dp, dk, di, ds, dout;
+    if (dp.get(sizeof(double) * 3 * n) || dk.get(sizeof(unsigned long long) * n) || di.get(sizeof(int) * n) || ds.get(sizeof(int) * (n + 1)) ||
+        dout.get(sizeof(double) * 3 * n))
+        return fail(ctx, E2SEC_ERR_CUDA, "cudaMalloc failed");
+    CU(cudaMemcpyAsync(dp.p, pts, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, st));
+    const int grid = (n + 255) / 256;
+    voxel_key_kernel<<<grid, 256, 0, st>>>((const double *)dp.p, n, org[0], org[1], org[2], voxel, dim[1], dim[2], (unsigned long long *)dk.p, (int *)di.p); LAUNCHED();
+    thrust::device_ptr<unsigned long long> k((unsigned long long *)dk.p);
+    thrust::device_ptr<int> ix((int *)di.p), start((int *)ds.p);
+    thrust::stable_sort_by_key(thrust::cuda::par.on(st), k, k + n, ix);
+    voxel_start_kernel<<<grid, 256, 0, st>>>((const unsigned long long *)dk.p, n, (int *)ds.p); LAUNCHED();
+    int last_flag = 0, last_excl = 0;
+    CU(cudaMemcpyAsync(&last_flag, (int *)ds.p + (n - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+    thrust::exclusive_scan(thrust::cuda::par.on(st), start, start + n, start);
+    CU(cudaMemcpyAsync(&last_excl, (int *)ds.p + (n - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+    voxel_mean_kernel<<<grid, 256, 0, st>>>((const double *)dp.p, n, (const unsigned long long *)dk.p, (const int *)di.p, (double *)dout.p, (int *)ds.p); LAUNCHED();
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(st));
+    const int m = last_excl + last_flag;
+    CU(cudaMemcpy(out, dout.p, sizeof(double) * 3 * m, cudaMemcpyDeviceToHost));
+    *n_out = m;
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_icp_correspondences(e2sec_ctx *ctx, const double *source, int32_t n_source, const double *target, int32_t n_target,
+                                         const double transform[16], double max_distance, double stats[17])
+{
+    if (!ctx || !source || !target || !transform || !stats || n_source < 1 || n_target < 1 || !(max_distance > 0.0)) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaStream_t st = ctx->stream;
+    F0Buf dsrc, dtgt, dnn, dd2, dmv, dst;
+    if (dsrc.get(sizeof(double) * 3 * n_source) || dtgt.get(sizeof(double) * 3 * n_target) || dnn.get(sizeof(int) * n_source) ||
+        dd2.get(sizeof(double) * n_source) || dmv.get(sizeof(double) * 3 * n_source) || dst.get(sizeof(double) * 17))
+        return fail(ctx, E2SEC_ERR_CUDA, "cudaMalloc failed");
+    CU(cudaMemcpyAsync(dsrc.p, source, sizeof(double) * 3 * n_source, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(dtgt.p, target, sizeof(double) * 3 * n_target, cudaMemcpyHostToDevice, st));
+    IcpParams p;
+    memcpy(p.T, transform, sizeof(p.T));
+    p.max_d2 = max_distance * max_distance;
+    const long long threads = (long long)n_source * 32;
+    icp_nn_kernel<<<(unsigned)((threads + E2_F0_THREADS - 1) / E2_F0_THREADS), E2_F0_THREADS, 0, st>>>((const double *)dsrc.p, n_source, (const double *)dtgt.p, n_target, p,
+                                                                                                     (int *)dnn.p, (double *)dd2.p, (double *)dmv.p); LAUNCHED();
+    icp_accumulate_kernel<<<1, 1024, 0, st>>>((const double *)dmv.p, (const double *)dtgt.p, (const int *)dnn.p, (const double *)dd2.p, n_source, (double *)dst.p); LAUNCHED();
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(stats, dst.p, sizeof(double) * 17, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return E2SEC_OK;
+}

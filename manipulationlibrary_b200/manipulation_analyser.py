@@ -11,8 +11,9 @@ fallback: without a CUDA device the first call raises.
 Scope notes:
   * several GPUs: analyse_maniac_manipulation deals batches of BATCH_FRAMES frames to every visible device in turn, each
     behind its one-frame halo, while reader threads decode the files ahead; one resolver consumes the records in order.
-  * frame-0 setup (_getGroundiNewNew :278-361, _getTranslation :212-276) is random in the reference and outside
-    this path; its products are INPUTS here: call set_frame0(translation, roll, ground) before the first frame.
+  * frame-0 setup (_getGroundiNewNew :278-361, _getTranslation :212-276) runs on the device (frame0.py, csrc/frame0.cuh),
+    seeded and therefore repeatable (the reference draws unseeded random numbers); set_frame0(translation, roll, ground)
+    supplies the products instead, clear_frame0() goes back to computing them.
   * icp=True (:1677-1738) is not implemented: it raises NotImplementedError.  relations = 1, 2, 3 are.
   * debug=True writes the data behind the reference's debug PNGs (:1830-1998) as
     debug_images/<savename>/<frame>.json (AABBs, centres, relation codes) and prunes them to final_columns like
@@ -37,15 +38,28 @@ final_columns = []
 column_frames = []                  # frame id of every raw eSEC column (-1: the initial '-' column), all relation modes
 total_unique_labels = 0
 hand_label_inarray = -1
-_frame0 = None
+_frame0 = None                      # (translation, roll, ground) in use
+_frame0_given = False               # set by set_frame0: kept for every following sequence until clear_frame0()
 _state = None                       # per-sequence: engine, resolver, params
 
 
 def set_frame0(translation, roll, ground):
     """The frame-0 products the reference computes at :1397-1404 (4x4, 4x4, (G,3) ground cloud already transformed)."""
-    global _frame0
+    global _frame0, _frame0_given
+    _frame0_given = True
     _frame0 = (np.asarray(translation, np.float64).reshape(4, 4), np.asarray(roll, np.float64).reshape(4, 4),
                np.ascontiguousarray(ground, np.float64).reshape(-1, 3))
+
+
+def clear_frame0():
+    """Forget the products given with set_frame0: the next sequence computes them from its frame 0 on the device."""
+    global _frame0, _frame0_given
+    _frame0, _frame0_given = None, False
+
+
+def frame0_products():
+    """(translation, roll, ground) of the current sequence (given, or computed from frame 0)."""
+    return _frame0
 
 
 def _total_unique_labels(label0, hand_label, replace, old, ignored_labels, cut_labels):
@@ -104,11 +118,19 @@ def _check_args(relations, icp, cython):
 
 
 def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
-                    thresh, max_frames, filter_mode, filter_seed, relations=3, n_devices=1):
-    global _state, total_unique_labels, hand_label_inarray, final_columns
-    if _frame0 is None:
-        raise NotImplementedError("frame-0 setup (_getGroundiNewNew / _getTranslation) is outside this path: call "
-                                  "manipulation_analyser.set_frame0(translation, roll, ground) first")
+                    thresh, max_frames, filter_mode, filter_seed, relations=3, n_devices=1, xyz0=None, frame0_seed=None):
+    global _state, total_unique_labels, hand_label_inarray, final_columns, _frame0
+    if not _frame0_given:
+        # the frame-0 branch of _process (:1397-1404) on the device: RANSAC ground plane, voxel grids, levelling ICP
+        # (frame0.py; deterministic, seeded -- the reference draws unseeded random numbers here)
+        if xyz0 is None:
+            raise ValueError("frame-0 setup needs the cloud of frame 0")
+        from . import frame0 as f0
+        tmp = Engine(0)
+        try:
+            _frame0 = f0.frame0_setup(tmp, xyz0, label0, ground_label, f0.DEFAULT_SEED if frame0_seed is None else frame0_seed)
+        finally:
+            tmp.close()
     tul = _total_unique_labels(label0, hand_label, replace, old, ignored_labels, cut_labels)
     total_unique_labels = tul
     hand_label_inarray = int(np.where(tul == hand_label)[0][0])      # IndexError like :1520 when absent
@@ -158,13 +180,13 @@ def _run_batch(frames, xyz, labels, label_shape):
 
 def _process(pcd_file, label_file, ground_label, hand_label, support_hand, translation, roll, frame, ESEC_table,
              relations, replace=False, old=[], new=[], ignored_labels=[], cut_labels=[], thresh=0.1, debug=False,
-             cython=True, icp=True, savename="", filter_mode="closure", filter_seed=0):
+             cython=True, icp=True, savename="", filter_mode="closure", filter_seed=0, frame0_seed=None):
     """One frame of the sequence (the reference's per-frame entry point, :1355-1357)."""
     _check_args(relations, icp, cython)
     xyz, label = read_frame(pcd_file, label_file)
     if frame == 0 or _state is None:
         _start_sequence(label, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
-                        thresh, 1, filter_mode, filter_seed, relations)
+                        thresh, 1, filter_mode, filter_seed, relations, xyz0=xyz, frame0_seed=frame0_seed)
     _run_batch(np.array([frame], np.int32), xyz[None], label.reshape(1, -1).astype(np.int32), label.shape)
     T, R, _ = _frame0
     return T, R, _table_from_resolver(relations)
@@ -198,8 +220,10 @@ def _clean_debug_images(final_columns, savename):
 
 def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, support_hand, relations, replace, old,
                                 new, ignored_labels, thresh, cut_labels=[], debug=False, cython=True, icp=True,
-                                savename="", filter_mode="closure", filter_seed=0):
-    """:2184-2291.  Extra keyword arguments (additions): filter_mode 'closure' | 'reference_seeded', filter_seed."""
+                                savename="", filter_mode="closure", filter_seed=0, frame0_seed=None):
+    """:2184-2291.  Extra keyword arguments (additions): filter_mode 'closure' | 'reference_seeded', filter_seed, and
+    frame0_seed for the frame-0 setup (RANSAC samples, synthetic plane), which runs on the device unless set_frame0 gave
+    its products."""
     global final_columns
     _check_args(relations, icp, cython)
     if debug:
@@ -270,10 +294,11 @@ def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, 
         first = ahead[0].result() if ahead else None
         if first is not None:
             rows, cols = first[0]["lshape"]
-            label0 = as_arrays(dict(first[0]))["labels"].reshape(rows, cols) if "labels" not in first[0] else \
-                first[0]["labels"].reshape(rows, cols)
+            fr0 = as_arrays(dict(first[0]))
+            label0 = fr0["labels"].reshape(rows, cols)
             _start_sequence(label0, ground_label, hand_label, support_hand, replace, old, new,
-                            ignored_labels, cut_labels, thresh, batch, filter_mode, filter_seed, relations, n_devices=64)
+                            ignored_labels, cut_labels, thresh, batch, filter_mode, filter_seed, relations, n_devices=64,
+                            xyz0=fr0["xyz"], frame0_seed=frame0_seed)
         D = len(_state["engines"]) if first is not None else 1
         workers = [ThreadPoolExecutor(max_workers=1) for _ in range(D)]
         window = 2 * D + 2                                               # chunks read ahead / in flight

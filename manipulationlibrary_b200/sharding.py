@@ -65,3 +65,47 @@ def gather_records(local, n_frames, world, device=None):
         a, b = shard_range(n_frames, r, world)
         parts.append(full[r, : b - a])
     return np.concatenate(parts)
+
+
+# ---- one sequence dealt over the GPUs batch by batch (bench.py) ------------------------------------------------
+def batch_owner(g, world):
+    """Global batch g of the sequence runs on rank g % world as that rank's step g // world, behind a one-frame halo."""
+    return g % world, g // world
+
+
+def ring_tickets(g, n_batches, serial=0):
+    """(wait, post) tickets of batch g for e2sec_phase2_run_ring: the kernel of batch g waits for the state the kernel of
+    batch g - 1 posted, and posts its own for batch g + 1; 0 = nothing to wait for / post.  `serial` numbers the sequences
+    run so far so that tickets never repeat."""
+    base = serial * n_batches + 1
+    return (base + g if g > 0 else 0), (base + g + 1 if g < n_batches - 1 else 0)
+
+
+def gather_columns(columns, frames, world, device=None):
+    """The one collective of the sharded run: every rank's emitted columns ((n, 32) uint8 relation codes + (n,) int32 frame
+    ids) on rank 0, merged into frame order.  Other ranks get (None, None)."""
+    import torch
+    import torch.distributed as dist
+    columns = np.ascontiguousarray(columns, np.uint8).reshape(-1, nat.PHASE2_COLUMN_BYTES)
+    frames = np.ascontiguousarray(frames, np.int32).reshape(-1)
+    if world == 1:
+        order = np.argsort(frames, kind="stable")
+        return columns[order], frames[order]
+    rank = dist.get_rank()
+    cnt = torch.tensor([len(frames)], dtype=torch.int64, device=device)
+    counts = [torch.zeros_like(cnt) for _ in range(world)]
+    dist.all_gather(counts, cnt)
+    counts = [int(c.item()) for c in counts]
+    width = nat.PHASE2_COLUMN_BYTES + 4
+    pad = torch.zeros((max(max(counts), 1), width), dtype=torch.uint8, device=device)
+    if len(frames):
+        packed = np.concatenate([columns, frames.view(np.uint8).reshape(-1, 4)], axis=1)
+        pad[: len(frames)] = torch.from_numpy(packed).to(pad.device)
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad)
+    if rank != 0:
+        return None, None
+    allp = np.concatenate([parts[r][: counts[r]].cpu().numpy() for r in range(world)])
+    fr = np.ascontiguousarray(allp[:, nat.PHASE2_COLUMN_BYTES:]).view(np.int32).reshape(-1)
+    order = np.argsort(fr, kind="stable")
+    return np.ascontiguousarray(allp[order, : nat.PHASE2_COLUMN_BYTES]), fr[order]

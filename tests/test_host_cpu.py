@@ -175,6 +175,23 @@ if rank == 0:
     e2, fc2 = esec_to_e2sec_native(table, 3, fc)
     assert (e2.astype("U5") == gold["e2sec"]).all()
     assert fc2 == list(gold["final_columns"])
+# the sharded run's one collective: columns emitted by batches dealt round-robin come back merged in frame order
+from manipulationlibrary_b200.sharding import batch_owner, gather_columns, ring_tickets
+from manipulationlibrary_b200.engine import columns_table
+n_batches, B = 7, 10
+rng = np.random.default_rng(5)
+all_frames = np.sort(rng.choice(n_batches * B, size=23, replace=False)).astype(np.int32)
+all_cols = rng.integers(1, 19, size=(len(all_frames), 32)).astype(np.uint8)
+mine = [i for i, f in enumerate(all_frames) if batch_owner(int(f) // B, world)[0] == rank]
+cols, frames = gather_columns(all_cols[mine], all_frames[mine], world)
+if rank == 0:
+    assert (frames == all_frames).all() and (cols == all_cols).all()
+    t, fc = columns_table(cols, frames, 3)
+    assert t.shape == (30, len(all_frames)) and fc == all_frames.tolist()
+else:
+    assert cols is None
+tk = [ring_tickets(g, n_batches, serial=2) for g in range(n_batches)]
+assert tk[0][0] == 0 and tk[-1][1] == 0 and all(tk[g][1] == tk[g + 1][0] != 0 for g in range(n_batches - 1))
 dist.barrier()
 dist.destroy_process_group()
 print("rank", rank, "ok")
