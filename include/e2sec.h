@@ -160,6 +160,12 @@ int e2sec_process_batch_pcd_async(e2sec_ctx *ctx, const uint8_t *pcd_files, cons
 int e2sec_staged_inputs_dev(e2sec_ctx *ctx, const float **xyz_dev, const int32_t **labels_dev);
 /* ... and copied to the host (waits for the context's stream): what the device decoders made of the files */
 int e2sec_copy_staged_inputs(e2sec_ctx *ctx, float *xyz, int32_t *labels, int32_t n_frames, int32_t label_size);
+/* The clouds behind a record of the batch processed last, for callers that track rigid models (icp=True, :1677-1738):
+ * entity (index into total_unique_labels) of frame (position in the batch).  which = 0: every valid point of the label,
+ * transformed = pcd[i] (:1516); which = 1: filtered_pcd_voxel[i] (:1519-1546; the seed point first -- it is in the
+ * reference's cloud twice, pyx:48 --, then the kept points in raster order).  out: capacity x 3 (may be NULL to ask for
+ * the size); entities that are never stored (index 0 unless it is the hand, the ground label) give 0 points.            */
+int e2sec_entity_cloud(e2sec_ctx *ctx, int32_t frame, int32_t entity, int32_t which, double *out, int32_t capacity, int32_t *n_out);
 const double *e2sec_records_dev(e2sec_ctx *ctx);
 /* Stream-ordered copy of records [first, first + count) of the batch queued last to dst (host or device memory): a shard
  * that keeps its records on the device for e2sec_phase2_run, minus the halo frame's.  Does not wait.                  */

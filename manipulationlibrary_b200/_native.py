@@ -63,6 +63,7 @@ def _load():
         "e2sec_process_batch_pcd_async": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]),
         "e2sec_staged_inputs_dev": (C.c_int, [vp, vp, vp]),
         "e2sec_copy_staged_inputs": (C.c_int, [vp, vp, vp, i32, i32]),
+        "e2sec_entity_cloud": (C.c_int, [vp, i32, i32, i32, vp, i32, vp]),
         "e2sec_records_dev": (vp, [vp]),
         "e2sec_copy_records": (C.c_int, [vp, vp, i32, i32]),
         "e2sec_sync": (C.c_int, [vp]),

@@ -845,6 +845,45 @@ extern "C" int e2sec_copy_staged_inputs(e2sec_ctx *ctx, float *xyz, int32_t *lab
     return E2SEC_OK;
 }
 
+// The clouds behind a record (for callers that track rigid models, icp=True :1677-1738): entity `entity` of frame `frame` of
+// the batch processed last.  which = 0: every valid point of the label, transformed (pcd[i], :1516); 1: the filtered cloud
+// (filtered_pcd_voxel[i], :1519-1546: the seed point first -- it counts twice, pyx:48 -- then the kept points in raster order).
+extern "C" int e2sec_entity_cloud(e2sec_ctx *ctx, int32_t frame, int32_t entity, int32_t which, double *out, int32_t capacity, int32_t *n_out)
+{
+    if (!ctx || !ctx->configured || !n_out || frame < 0 || frame >= ctx->maxF || (which != 0 && which != 1)) return E2SEC_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    const Dev &d = ctx->d;
+    const int K = ctx->d.K, e = entity + d.ent_shift;
+    if (entity < 0 || e >= K) return fail(ctx, E2SEC_ERR_ARG, "e2sec_entity_cloud: entity out of range");
+    CU(cudaStreamSynchronize(ctx->stream));
+    int off = -1, raw = 0, nl = 0, seed = -1;
+    const size_t fe = (size_t)frame * K + e;
+    CU(cudaMemcpy(&off, d.ent_off + fe, sizeof(int), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(&raw, d.ent_raw + fe, sizeof(int), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(&nl, d.n_list + fe, sizeof(int), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(&seed, d.seed_pos + fe, sizeof(int), cudaMemcpyDeviceToHost));
+    if (off < 0) { *n_out = 0; return E2SEC_OK; }                 // index 0 / the ground label: never stored
+    const int n = which == 0 ? raw : nl + (seed >= 0 ? 1 : 0);
+    *n_out = n;
+    if (!out || n == 0) return E2SEC_OK;
+    if (n > capacity) return fail(ctx, E2SEC_ERR_CAPACITY, "e2sec_entity_cloud: capacity too small");
+    const size_t pb = (size_t)frame * ctx->N + off;
+    std::vector<double> x(raw), y(raw), z(raw);
+    CU(cudaMemcpy(x.data(), d.px + pb, sizeof(double) * raw, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(y.data(), d.py + pb, sizeof(double) * raw, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(z.data(), d.pz + pb, sizeof(double) * raw, cudaMemcpyDeviceToHost));
+    if (which == 0) {
+        for (int i = 0; i < raw; ++i) { out[3 * (size_t)i] = x[i]; out[3 * (size_t)i + 1] = y[i]; out[3 * (size_t)i + 2] = z[i]; }
+        return E2SEC_OK;
+    }
+    std::vector<unsigned> fl(nl > 0 ? nl : 1);
+    if (nl) CU(cudaMemcpy(fl.data(), d.flist + pb, sizeof(unsigned) * nl, cudaMemcpyDeviceToHost));
+    size_t o = 0;
+    if (seed >= 0) { out[0] = x[seed]; out[1] = y[seed]; out[2] = z[seed]; o = 1; }
+    for (int i = 0; i < nl; ++i, ++o) { const unsigned q = fl[i]; out[3 * o] = x[q]; out[3 * o + 1] = y[q]; out[3 * o + 2] = z[q]; }
+    return E2SEC_OK;
+}
+
 extern "C" int e2sec_copy_records(e2sec_ctx *ctx, double *dst, int32_t first, int32_t count)
 {
     if (!ctx || !dst || first < 0 || count < 0) return E2SEC_ERR_ARG;

@@ -149,6 +149,16 @@ class Engine:
             return label_size, 1, self.n_points, 1
         return lw, lh, w, h
 
+    def entity_cloud(self, frame, entity, filtered):
+        """(n, 3) float64: entity's cloud of frame `frame` of the batch processed last -- pcd[i] or filtered_pcd_voxel[i]."""
+        n = C.c_int32()
+        self._check(lib.e2sec_entity_cloud(self._h, int(frame), int(entity), 1 if filtered else 0, None, 0, C.byref(n)), "e2sec_entity_cloud")
+        out = np.empty((n.value, 3), np.float64)
+        if n.value:
+            self._check(lib.e2sec_entity_cloud(self._h, int(frame), int(entity), 1 if filtered else 0, ptr(out), n.value, C.byref(n)),
+                        "e2sec_entity_cloud")
+        return out
+
     def copy_records(self, dst_ptr, first, count):
         """Stream-ordered copy of records [first, first + count) of the batch queued last to host or device memory."""
         self._check(lib.e2sec_copy_records(self._h, C.c_void_p(int(dst_ptr)), int(first), int(count)), "e2sec_copy_records")

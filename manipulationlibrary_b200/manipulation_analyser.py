@@ -14,7 +14,8 @@ Scope notes:
   * frame-0 setup (_getGroundiNewNew :278-361, _getTranslation :212-276) runs on the device (frame0.py, csrc/frame0.cuh),
     seeded and therefore repeatable (the reference draws unseeded random numbers); set_frame0(translation, roll, ground)
     supplies the products instead, clear_frame0() goes back to computing them.
-  * icp=True (:1677-1738) is not implemented: it raises NotImplementedError.  relations = 1, 2, 3 are.
+  * icp=True (:1677-1738, rigid-model tracking) runs frame by frame (tracking.py): the models are registered with ICP steps
+    on the device.  relations = 1, 2, 3 are all there.
   * debug=True writes the data behind the reference's debug PNGs (:1830-1998) as
     debug_images/<savename>/<frame>.json (AABBs, centres, relation codes) and prunes them to final_columns like
     _clean_debug_images (:160-173); matplotlib rendering is unavailable on this box.
@@ -110,15 +111,13 @@ def _label_shape(label_file):
 def _check_args(relations, icp, cython):
     if relations not in (1, 2, 3):
         raise ValueError("relations must be 1 (T/N), 2 (+ SSR) or 3 (+ DSR), got %r" % (relations,))
-    if icp:
-        raise NotImplementedError("icp=True (rigid-model tracking, manipulation_analyser.py:1677-1738) is outside this "
-                                  "path; call with icp=False")
     if not cython:
         raise NotImplementedError("cython=False selects Open3D's statistical outlier branch (:1534-1541), not built")
 
 
 def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
-                    thresh, max_frames, filter_mode, filter_seed, relations=3, n_devices=1, xyz0=None, frame0_seed=None):
+                    thresh, max_frames, filter_mode, filter_seed, relations=3, n_devices=1, xyz0=None, frame0_seed=None,
+                    icp=False):
     global _state, total_unique_labels, hand_label_inarray, final_columns, _frame0
     if not _frame0_given:
         # the frame-0 branch of _process (:1397-1404) on the device: RANSAC ground plane, voxel grids, levelling ICP
@@ -143,13 +142,19 @@ def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old
             e.close()
         _state["resolver"].close()
     # every visible GPU takes batches of the sequence in turn (E2SEC_DEVICES limits how many); _process, frame by frame, uses one
-    n_dev = max(1, min(int(nat.lib.e2sec_device_count()), int(os.environ.get("E2SEC_DEVICES", "64")), n_devices))
+    n_dev = max(1, min(int(nat.lib.e2sec_device_count()), int(os.environ.get("E2SEC_DEVICES", "64")), 1 if icp else n_devices))
     engines = []
     for dev in range(n_dev):
         eng = Engine(dev)
         eng.configure(p, max_frames + 1, IMAGE_SHAPE[0] * IMAGE_SHAPE[1], keep)      # + the halo frame in front of a batch
         engines.append(eng)
-    _state = dict(engine=engines[0], engines=engines, resolver=Resolver(p, keep), params=p, keep=keep, K=len(tul), records={})
+    _state = dict(engine=engines[0], engines=engines, resolver=Resolver(p, keep), params=p, keep=keep, K=len(tul), records={},
+                  tracker=None)
+    if icp:
+        # rigid-model tracking (:1677-1738) makes the frames depend on each other through whole clouds: tracking.py walks
+        # them one by one over the same device operators
+        from .tracking import Tracker
+        _state["tracker"] = Tracker(engines[0], tul, hand_label, ground_label, support_hand, thresh, relations, ground)
     final_columns = []
 
 
@@ -157,7 +162,7 @@ def _table_from_resolver(relations):
     """The raw eSEC table so far.  final_columns follows the reference: frame ids of the columns with relations == 3
     (:1813-1829), left empty with relations 1 / 2 (those branches never append, :1744-1794); column_frames has them always."""
     global final_columns, column_frames
-    table, fc = _state["resolver"].table()
+    table, fc = (_state["tracker"] or _state["resolver"]).table()
     column_frames = list(fc)
     final_columns = list(fc) if relations == 3 else []
     if table.shape[1] == 0:
@@ -173,7 +178,11 @@ def _run_batch(frames, xyz, labels, label_shape):
     if labels.shape[1] != xyz.shape[1]:
         kw = dict(label_shape=label_shape, image_shape=IMAGE_SHAPE)
     rec = eng.process_batch(xyz, labels, frames, **kw)
-    _state["resolver"].feed(rec)
+    if _state["tracker"] is not None:
+        for slot, (f, r) in enumerate(zip(frames, rec)):
+            _state["tracker"].frame(int(f), slot, r)
+    else:
+        _state["resolver"].feed(rec)
     for f, r in zip(frames, rec):
         _state["records"][int(f)] = r
 
@@ -186,7 +195,7 @@ def _process(pcd_file, label_file, ground_label, hand_label, support_hand, trans
     xyz, label = read_frame(pcd_file, label_file)
     if frame == 0 or _state is None:
         _start_sequence(label, ground_label, hand_label, support_hand, replace, old, new, ignored_labels, cut_labels,
-                        thresh, 1, filter_mode, filter_seed, relations, xyz0=xyz, frame0_seed=frame0_seed)
+                        thresh, 1, filter_mode, filter_seed, relations, xyz0=xyz, frame0_seed=frame0_seed, icp=icp)
     _run_batch(np.array([frame], np.int32), xyz[None], label.reshape(1, -1).astype(np.int32), label.shape)
     T, R, _ = _frame0
     return T, R, _table_from_resolver(relations)
@@ -298,7 +307,7 @@ def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, 
             label0 = fr0["labels"].reshape(rows, cols)
             _start_sequence(label0, ground_label, hand_label, support_hand, replace, old, new,
                             ignored_labels, cut_labels, thresh, batch, filter_mode, filter_seed, relations, n_devices=64,
-                            xyz0=fr0["xyz"], frame0_seed=frame0_seed)
+                            xyz0=fr0["xyz"], frame0_seed=frame0_seed, icp=icp)
         D = len(_state["engines"]) if first is not None else 1
         workers = [ThreadPoolExecutor(max_workers=1) for _ in range(D)]
         window = 2 * D + 2                                               # chunks read ahead / in flight
@@ -312,14 +321,22 @@ def analyse_maniac_manipulation(pcl_path, label_path, ground_label, hand_label, 
                 ahead.append(readers.submit(read_chunk, chunks[c + window]))
             jobs.append((frames, prev_last, workers[c % D].submit(run_on, c % D, frames, prev_last)))
             prev_last = frames[-1]
-            while jobs and (len(jobs) > D or c == len(chunks) - 1):      # collect in order, D batches stay in flight
+            in_flight = 0 if _state["tracker"] is not None else D        # model tracking reads the batch's clouds back: no overlap
+            while jobs and (len(jobs) > in_flight or c == len(chunks) - 1):   # collect in order, D batches stay in flight
                 frames0, halo, fut = jobs.pop(0)
                 hrec, rec = fut.result()
                 want = last_kept["id"] if last_kept is not None else -1
                 if halo is not None and (int(hrec[1]) != KEPT or halo["id"] != want):
                     # the frame in front was not a kept frame (no hand in it): redo the batch behind the real one
                     _, rec = workers[0].submit(run_on, 0, frames0, last_kept).result()
-                _state["resolver"].feed(rec)
+                    halo = last_kept
+                if _state["tracker"] is not None:
+                    # (one device, D == 1: the batch's clouds are still in the engine's buffers; a halo'd batch holds them
+                    # one slot further back)
+                    for slot, (fr, r) in enumerate(zip(frames0, rec)):
+                        _state["tracker"].frame(int(fr["id"]), slot + (1 if halo is not None else 0), r)
+                else:
+                    _state["resolver"].feed(rec)
                 for fr, r in zip(frames0, rec):
                     _state["records"][int(fr["id"])] = r
                 kept = np.nonzero(rec[:, 1].astype(np.int64) == KEPT)[0]

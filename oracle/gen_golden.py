@@ -235,7 +235,25 @@ def run_reference_capture(mode, pcl, lab, savename, work, tr):
     return out, fixture, ref
 
 
-if __name__ == "__main__" and "--frames" not in sys.argv:
+def main_icp():
+    """icp=True (rigid-model tracking, :1677-1738 -- the notebook's default): the reference's own code on Pushing_06 with
+    the same seeds -> tests/golden/pushing06_icp_closure.npz (e2sec, final_columns, per-frame raw columns and bindings)."""
+    import tempfile
+    ARGS["icp"] = True
+    pcl = os.path.join(REF, "example", "Pushing_06") + "/"
+    lab = os.path.join(REF, "example", "Pushing_06_labels") + "/"
+    work = tempfile.mkdtemp(prefix="e2sec_gold_icp_")
+    tr = {}
+    out, fixture, ref = run_reference_capture("closure", pcl, lab, "Pushing_06_icp", work, tr)
+    np.savez_compressed(os.path.join(GOLD, "pushing06_icp_closure.npz"), e2sec=out["e2sec"], final_columns=out["final_columns"],
+                        columns=out["columns"], raw_columns=out["raw_columns"])
+    print("icp e2sec", out["e2sec"].shape, "final_columns", out["final_columns"])
+    print(out["e2sec"])
+
+
+if __name__ == "__main__" and "--icp" in sys.argv:
+    main_icp()
+elif __name__ == "__main__" and "--frames" not in sys.argv:
     main()
 
 

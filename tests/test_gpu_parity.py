@@ -458,8 +458,23 @@ def test_dropin_analyse_maniac_manipulation(tmp_path, monkeypatch):
     assert list(ma.final_columns) == list(gold["final_columns"])
     kept = sorted(int(p.name.split(".")[0]) for p in (tmp_path / "debug_images" / "Pushing_06").iterdir())
     assert kept == sorted(set(int(c) for c in gold["final_columns"]))
-    with pytest.raises(NotImplementedError):
-        ma.analyse_maniac_manipulation(pcl, lab, 2, 11, None, 3, False, [], [], [255], 0.07, icp=True)
+
+
+def test_dropin_icp_model_tracking(tmp_path, monkeypatch):
+    """icp=True, the notebook's default (:1677-1738): o1 / o2 / o3 are rigid models registered onto every frame.  The saved
+    matrix equals the one the reference's own code produced with icp=True (oracle/gen_golden.py --icp)."""
+    from manipulationlibrary_b200 import manipulation_analyser as ma
+    frames = Pushing06Frames()
+    fx = load_golden("pushing06_fixture")
+    gold = load_golden("pushing06_icp_closure")
+    pcl, lab = _write_sequence(tmp_path, frames)
+    monkeypatch.chdir(tmp_path)
+    ma.set_frame0(fx["translation"], fx["roll"], fx["ground"])
+    ma.analyse_maniac_manipulation(pcl, lab, 2, 11, None, 3, False, [], [], [255], 0.07, icp=True, savename="icp")
+    e2 = np.load(tmp_path / "e2sec_icp.npy")
+    assert e2.shape == gold["e2sec"].shape, (e2.shape, gold["e2sec"].shape, ma.final_columns, gold["final_columns"])
+    assert (e2.astype("U5") == gold["e2sec"]).all()
+    assert list(ma.final_columns) == list(gold["final_columns"])
 
 
 @pytest.mark.parametrize("want_relations", [1, 2, 3])
