@@ -34,8 +34,13 @@
 #define E2_CELL_CTAS 3              // resident CTAs per SM the register budget is cut for
 #endif
 #define E2_CELL_WARPS (E2_CELL_THREADS / 32)
+#ifndef E2_CELL_MAX
 #define E2_CELL_MAX 1024          // occupied cells per entity
-#define E2_CELL_HASH 4096         // hash slots (power of two)
+#endif
+#ifndef E2_CELL_HASH_LOG
+#define E2_CELL_HASH_LOG 12
+#endif
+#define E2_CELL_HASH (1 << E2_CELL_HASH_LOG)   // hash slots
 #ifndef E2_CELL_G
 #define E2_CELL_G 24              // cells along the largest robust extent; ids use 5 bits per axis
 #endif
@@ -43,7 +48,7 @@
 #define E2_CELL_EMPTY 0xffffffffu
 #define E2_CELL_JOIN (E2_CELL_MAX - 1)   // virtual cell of candidate points that were settled as members one by one
 #define E2_CELL_UMAX 256          // candidate points settled at point level before giving up
-#define E2_CELL_MCAP 1024         // median selection: values ranked in shared memory once the middle bin holds no more than this
+#define E2_CELL_MCAP (E2_CELL_MAX < 1024 ? E2_CELL_MAX : 1024)   // median selection: values ranked in shared memory once the middle bin holds no more than this
 #define E2_CELL_MSMALL 64         // ... directly once a sub-bin of it holds no more than this
 #define E2_CELL_HPAD(b) ((b) + ((b) >> 5))   // histogram slot of bin b: a lane that walks 32 consecutive bins meets 32 banks
 #define E2_CELL_HSIZE (E2_CELL_BINS + E2_CELL_BINS / 32)
@@ -602,7 +607,7 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             const float ty = fminf(fmaxf(floorf((float)(Y[i] - l1) * inv_cf), -1.0f), (float)E2_CELL_G);
             const float tz = fminf(fmaxf(floorf((float)(Z[i] - l2) * inv_cf), -1.0f), (float)E2_CELL_G);
             const unsigned id = ((unsigned)((int)tx + 1) << 10) | ((unsigned)((int)ty + 1) << 5) | (unsigned)((int)tz + 1);
-            unsigned slot = (id * 2654435761u) >> 20;
+            unsigned slot = (id * 2654435761u) >> (32 - E2_CELL_HASH_LOG);
             int probes = 0;
             for (;;) {
                 // a plain look first: almost every point finds its cell already there, and compare-and-swaps of a whole
