@@ -316,7 +316,9 @@ int32_t e2sec_columns_table(const uint8_t *columns, const int32_t *frames, int32
  * D (n_tables x n_tables, host) = sum over triples of sqrt(l)/sqrt(3) / (max(n_i, n_j) * divisor), l = the
  * components of the triple that differ; divisor is 10 in getDissimilarityMatrix, 8 in
  * similarity_manipulations (which returns (1 - D) * 100).  counts (may be NULL): n_tables x n_tables x 3
- * triples with l = 1, 2, 3 -- the integers D is made of.                                             */
+ * triples with l = 1, 2, 3 -- the integers D is made of.  The counts are exact; D is formed from them as
+ * (c1/sqrt(3) + c2*sqrt(2)/sqrt(3) + c3) / (n * divisor) and agrees with the reference's pairwise float sum to <= 1e-13
+ * absolute, not bit for bit: callers that break ties on D should compare the counts.  All tables share `rows`.        */
 int e2sec_dissimilarity(e2sec_ctx *ctx, const char *codes, const int64_t *offsets, const int32_t *n_cols,
                         int32_t n_tables, int32_t rows, double divisor, double *D, uint32_t *counts);
 /* device time of the two kernels of the last e2sec_dissimilarity call, in ms */
