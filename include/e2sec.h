@@ -211,6 +211,20 @@ int e2sec_voxel_down_sample(e2sec_ctx *ctx, const double *pts, int32_t n, double
  * cross-covariance sum (a - ca)(b - cb)^T row-major.  The 3 x 3 SVD of the update stays with the caller.                  */
 int e2sec_icp_correspondences(e2sec_ctx *ctx, const double *source, int32_t n_source, const double *target, int32_t n_target,
                               const double transform[16], double max_distance, double stats[17]);
+/* The same correspondence step for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * `source` (n_source x 3), `target` (n_target x 3) and `stats` (17 doubles) are DEVICE pointers the caller owns on ctx's
+ * device; `transform` is host memory.  The kernels' scratch (moved points, nearest index and distance per source point,
+ * 36 bytes each) lives in a file-scope __device__ array of the library sized for E2SEC_STATIC_ICP_MAX_SOURCE points
+ * (2.25 MiB on every GPU that loads the library, until the process exits); n_source beyond that returns E2SEC_ERR_CAPACITY
+ * with a message in e2sec_last_error.  The call makes no cudaMalloc / cudaFree and no allocating library call, runs on
+ * ctx's stream and returns after the stream has drained.  All calls on a device share the one array (it keeps the last
+ * call's contents; every element a call reads it has written first, nothing has to start at zero): two calls of one
+ * process that overlap on a GPU (from other contexts or threads) race and must be serialised by the caller.
+ * Results are bit-identical to e2sec_icp_correspondences.                                                                */
+#define E2SEC_STATIC_ICP_MAX_SOURCE 65536
+int e2sec_icp_correspondences_static(e2sec_ctx *ctx, const double *source_dev, int32_t n_source, const double *target_dev,
+                                     int32_t n_target, const double transform[16], double max_distance, double *stats_dev);
 
 /* ---- phase 2: the sequential part of _process (:1558-1675 selection, :363-1353 relation rows,
  * :1795-1829 / :2000-2007 column emit) over records in frame order.  Host code. -------------------- */

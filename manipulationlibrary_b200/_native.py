@@ -17,6 +17,7 @@ FLAG_HAND_POINTS = 2
 PHASE2_STATE_BYTES = 512
 PHASE2_COLUMN_BYTES = 32
 IPC_HANDLE_BYTES = 64
+STATIC_ICP_MAX_SOURCE = 65536     # E2SEC_STATIC_ICP_MAX_SOURCE: points the no-allocation ICP step has scratch for
 FILTER_CLOSURE = 0
 FILTER_REFERENCE_SEEDED = 1
 FILTER_MODES = {"closure": FILTER_CLOSURE, "reference_seeded": FILTER_REFERENCE_SEEDED}
@@ -78,6 +79,7 @@ def _load():
         "e2sec_plane_inlier_mask": (C.c_int, [vp, vp, i32, vp, dbl, vp]),
         "e2sec_voxel_down_sample": (C.c_int, [vp, vp, i32, dbl, vp, vp]),
         "e2sec_icp_correspondences": (C.c_int, [vp, vp, i32, vp, i32, vp, dbl, vp]),
+        "e2sec_icp_correspondences_static": (C.c_int, [vp, vp, i32, vp, i32, vp, dbl, vp]),
         "e2sec_dissimilarity": (C.c_int, [vp, vp, vp, vp, i32, i32, dbl, vp, vp]),
         "e2sec_dissimilarity_ms": (C.c_int, [vp, vp]),
         "e2sec_resolver_create": (C.c_int, [C.POINTER(Params), C.POINTER(vp)]),

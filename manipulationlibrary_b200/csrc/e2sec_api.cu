@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <algorithm>
 #include <cmath>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1587,6 +1588,60 @@ extern "C" int e2sec_icp_correspondences(e2sec_ctx *ctx, const double *source, i
     icp_accumulate_kernel<<<1, 1024, 0, st>>>((const double *)dmv.p, (const double *)dtgt.p, (const int *)dnn.p, (const double *)dd2.p, n_source, (double *)dst.p); LAUNCHED();
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(stats, dst.p, sizeof(double) * 17, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return E2SEC_OK;
+}
+
+// ---- the correspondence step without allocations (include/e2sec.h: e2sec_icp_correspondences_static) --------------------
+// The scratch of icp_nn_kernel / icp_accumulate_kernel in a file-scope device array: per source point the moved point
+// (3 doubles), the nearest distance (double) and the nearest index (int), planes one after the other.  Every GPU that
+// loads the library holds the 2.25 MiB until the process exits; all calls on a device share it.
+#define E2_STATIC_ICP_BYTES ((size_t)E2SEC_STATIC_ICP_MAX_SOURCE * (3 * sizeof(double) + sizeof(double) + sizeof(int)))
+static __device__ __align__(256) unsigned char g_icp_static_scratch[E2_STATIC_ICP_BYTES];
+
+// In host code `g_icp_static_scratch` is only the symbol's host-side stand-in: its device address is asked for once per
+// device, with that device current, and kept here.
+#define E2_STATIC_MAX_DEVICES 64
+static unsigned char *g_icp_static_addr[E2_STATIC_MAX_DEVICES];
+static std::mutex g_icp_static_mutex;
+
+static int icp_static_scratch(e2sec_ctx *ctx, unsigned char **out)
+{
+    if (ctx->device < 0 || ctx->device >= E2_STATIC_MAX_DEVICES) return fail(ctx, E2SEC_ERR_ARG, "e2sec_icp_correspondences_static: device index out of range");
+    std::lock_guard<std::mutex> lock(g_icp_static_mutex);
+    if (!g_icp_static_addr[ctx->device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_icp_static_scratch);          // the current device's copy (cudaSetDevice by the caller)
+        if (e != cudaSuccess || !p) return fail(ctx, E2SEC_ERR_CUDA, std::string("cudaGetSymbolAddress(g_icp_static_scratch): ") + cudaGetErrorString(e));
+        g_icp_static_addr[ctx->device] = (unsigned char *)p;
+    }
+    *out = g_icp_static_addr[ctx->device];
+    return E2SEC_OK;
+}
+
+extern "C" int e2sec_icp_correspondences_static(e2sec_ctx *ctx, const double *source_dev, int32_t n_source, const double *target_dev,
+                                                int32_t n_target, const double transform[16], double max_distance, double *stats_dev)
+{
+    if (!ctx || !source_dev || !target_dev || !transform || !stats_dev || n_source < 1 || n_target < 1 || !(max_distance > 0.0)) return E2SEC_ERR_ARG;
+    if (n_source > E2SEC_STATIC_ICP_MAX_SOURCE)
+        return fail(ctx, E2SEC_ERR_CAPACITY, "e2sec_icp_correspondences_static: n_source " + std::to_string(n_source) + " exceeds the static scratch (E2SEC_STATIC_ICP_MAX_SOURCE = " +
+                                                 std::to_string(E2SEC_STATIC_ICP_MAX_SOURCE) + " points); use e2sec_icp_correspondences");
+    CU(cudaSetDevice(ctx->device));
+    unsigned char *base = nullptr;
+    if (int rc = icp_static_scratch(ctx, &base)) return rc;
+    double *moved = reinterpret_cast<double *>(base);
+    double *nn_d2 = moved + 3 * (size_t)E2SEC_STATIC_ICP_MAX_SOURCE;
+    int *nn = reinterpret_cast<int *>(nn_d2 + (size_t)E2SEC_STATIC_ICP_MAX_SOURCE);
+    cudaStream_t st = ctx->stream;
+    IcpParams p;
+    memcpy(p.T, transform, sizeof(p.T));
+    p.max_d2 = max_distance * max_distance;
+    // nothing in the scratch has to start at zero: icp_nn_kernel writes moved / nn_d2 / nn for every i < n_source and
+    // icp_accumulate_kernel reads exactly those; stats_dev[0..16] are all written.
+    const long long threads = (long long)n_source * 32;
+    icp_nn_kernel<<<(unsigned)((threads + E2_F0_THREADS - 1) / E2_F0_THREADS), E2_F0_THREADS, 0, st>>>(source_dev, n_source, target_dev, n_target, p, nn, nn_d2, moved); LAUNCHED();
+    icp_accumulate_kernel<<<1, 1024, 0, st>>>(moved, target_dev, nn, nn_d2, n_source, stats_dev); LAUNCHED();
+    CU(cudaGetLastError());
     CU(cudaStreamSynchronize(st));
     return E2SEC_OK;
 }
