@@ -514,12 +514,9 @@ extern __shared__ __align__(16) unsigned char cell_smem_raw[];
 // Entities that are not stored or have <= 3 points are finished here too (raw cloud, :1543-1546).
 // FINISH = true is the second visit (after the exact radius selection): only the entities that left a CellState (amb == 2).
 template <bool FINISH>
-__global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_kernel(Dev d)
+__device__ __forceinline__ void cell_filter_entity(const Dev &d, CellSmem &s, const int fe)
 {
-    pdl_enter();
-    CellSmem &s = *reinterpret_cast<CellSmem *>(cell_smem_raw);
-    const int fe = blockIdx.x, f = fe / d.K;
-    if (FINISH && (exact_path_idle(d) || d.amb[fe] != 2)) return;
+    const int f = fe / d.K;
     const int off = d.ent_off[fe], n = d.ent_raw[fe];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double NaN = __longlong_as_double(0x7ff8000000000000ll);
@@ -830,7 +827,9 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
         }
         if (tid == 0) {
             d.amb[fe] = resume ? 2 : 1;
-            atomicAdd(d.amb_count, 1);
+            d.amb_list[atomicAdd(d.amb_count, 1)] = fe;
+            // the bounds of phase D, when it was reached, are where the exact selection starts (radius.cuh)
+            if (filtered && !s.overflow && s.amb >= 2) { d.rad_lo[fe] = s.r_lo; d.rad_hi[fe] = s.r_hi; }
 #ifdef E2_CELL_DEBUG
             printf("amb fe=%d n=%d reason=%d (1 table overflow, 2 seed cell, 3 candidates > %d, 4 point in the band) m=%u n_cand=%u r_lo=%g r_hi=%g\n", fe, n,
                    filtered && s.overflow ? 1 : (int)s.amb, E2_CELL_UMAX, s.m, s.n_cand, s.r_lo, s.r_hi);
@@ -898,5 +897,24 @@ __global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_ker
             aabb[3 + k] = run ? h[k] : 0.0;
             mean[k] = run ? tot[k] / cntp : 0.0;
         }
+    }
+}
+
+// FINISH = false: grid F*K, one entity per CTA.  FINISH = true: any grid, striding over the exact path's list.
+template <bool FINISH>
+__global__ void __launch_bounds__(E2_CELL_THREADS, E2_CELL_CTAS) cell_filter_kernel(Dev d)
+{
+    pdl_enter();
+    CellSmem &s = *reinterpret_cast<CellSmem *>(cell_smem_raw);
+    if (!FINISH) {
+        cell_filter_entity<false>(d, s, blockIdx.x);
+        return;
+    }
+    if (exact_path_idle(d)) return;
+    const int count = exact_count(d);
+    for (int li = blockIdx.x; li < count; li += gridDim.x) {
+        const int fe = exact_entity(d, li);
+        if (d.amb[fe] == 2) cell_filter_entity<true>(d, s, fe);
+        __syncthreads();
     }
 }

@@ -15,7 +15,8 @@
 #define E2_TILE 256          // points per tile in the pair-distance kernels
 #define E2_NBINS 256         // bins per refinement pass of the radius selection
 #define E2_CT_SUB 256        // ground points per pruning box (contact.cuh)
-#define E2_CAND_CAP 4096     // candidate keys kept for the final exact selection
+#define E2_CAND_CAP 16384    // candidate keys kept for the final exact selection (one bin of a pass that starts from the
+                             // cell table's radius band holds ~0.1 % of an entity's pairs)
 
 typedef unsigned long long u64;
 
@@ -29,6 +30,7 @@ struct RadiusState {
     int phase;      // 0 = refine (histogram pass), 1 = collect, 2 = done, 3 = inactive (not filtered)
     int n;          // points of the entity
     int pad;
+    u64 ktop;       // one past the key of the largest possible d^2 (the box diagonal): the interval never has to reach beyond
 };
 
 struct CellState;
@@ -96,6 +98,8 @@ struct Dev {
                                       //                 closure is finished by cell_filter_kernel<true>
     struct CellState *cell_state;     // F x K       closure state of the entities with amb == 2 (cells.cuh)
     int *amb_count;                   // number of such entities in the batch (reset by halo_commit_kernel)
+    int *amb_list;                    // F x K       their fe, in the order they turned up: what the exact path walks
+    unsigned *exact_ticket;           // CTAs of an exact-path kernel that are done (the last one plans the next pass)
     // stats + pairs
     double *aabb;                     // F x K x 6
     double *mean;                     // F x K x 3
@@ -123,6 +127,17 @@ __device__ __forceinline__ void pdl_enter()
 __device__ __forceinline__ bool exact_path_idle(const Dev &d)
 {
     return d.radius_mode == E2SEC_RADIUS_BOUNDED && *((volatile int *)d.amb_count) == 0;
+}
+
+// The entities the exact path works on: in BOUNDED mode the few the cell table left open (amb_list, filled by
+// cell_filter_kernel<false>), otherwise every (frame, entity).  Its kernels run small fixed grids that stride over this list.
+__device__ __forceinline__ int exact_count(const Dev &d)
+{
+    return d.radius_mode == E2SEC_RADIUS_BOUNDED ? *((volatile int *)d.amb_count) : d.F * d.K;
+}
+__device__ __forceinline__ int exact_entity(const Dev &d, int li)
+{
+    return d.radius_mode == E2SEC_RADIUS_BOUNDED ? d.amb_list[li] : li;
 }
 
 // :1518-1520: an entity is filtered when it has more than 3 points and is neither the ground nor index 0 (not stored, or the

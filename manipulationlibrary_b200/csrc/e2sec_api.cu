@@ -51,7 +51,7 @@ struct e2sec_ctx {
     size_t cap_total = 0;          // stored-point capacity over the whole batch (maxF * N)
     Dev d;
     std::vector<DevBuf *> bufs;
-    DevBuf lab8_stage, gsub, amb_count, cell_state;
+    DevBuf lab8_stage, gsub, amb_count, cell_state, amb_list, exact_ticket, plan_split;
     DevBuf pcd_stage, pcd_frames, pcd_status, ltext_stage, ltext_off;       // e2sec_process_batch_pcd: file bytes, per-frame jobs
     struct PcdJob {                                                          // the batch e2sec_process_batch_pcd is handing over
         const unsigned char *files = nullptr, *ltext = nullptr;
@@ -167,7 +167,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
     cudaFuncSetAttribute(cell_filter_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
-    ctx->bufs = {&ctx->pcd_stage, &ctx->pcd_frames, &ctx->pcd_status, &ctx->ltext_stage, &ctx->ltext_off, &ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->cell_state, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
+    ctx->bufs = {&ctx->pcd_stage, &ctx->pcd_frames, &ctx->pcd_status, &ctx->ltext_stage, &ctx->ltext_off, &ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->cell_state, &ctx->amb_list, &ctx->exact_ticket, &ctx->plan_split, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
                  &ctx->radius, &ctx->rs, &ctx->hist, &ctx->cand, &ctx->cand_n, &ctx->seed_pos, &ctx->member,
                  &ctx->front_a, &ctx->front_b, &ctx->flist, &ctx->n_list, &ctx->aabb, &ctx->mean, &ctx->gx, &ctx->gy,
@@ -273,6 +273,9 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     if ((rc = ensure(ctx, ctx->rad_hi, FK * sizeof(double)))) return rc;
     if ((rc = ensure(ctx, ctx->amb, FK * sizeof(int)))) return rc;
     if ((rc = ensure(ctx, ctx->amb_count, sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->amb_list, FK * sizeof(int)))) return rc;
+    if ((rc = ensure(ctx, ctx->exact_ticket, sizeof(unsigned)))) return rc;
+    if ((rc = ensure(ctx, ctx->plan_split, sizeof(unsigned)))) return rc;
     if ((rc = ensure(ctx, ctx->cell_state, FK * sizeof(CellState)))) return rc;
     const size_t slots = (size_t)K * (K - 1) / 2 + K + (size_t)K * K;
     if ((rc = ensure(ctx, ctx->ct_cnt, (size_t)F * slots * sizeof(unsigned)))) return rc;
@@ -285,6 +288,7 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     CU(cudaMemset(ctx->error.p, 0, sizeof(int)));
     CU(cudaMemset(ctx->seg_next.p, 0, sizeof(unsigned)));
     CU(cudaMemset(ctx->amb_count.p, 0, sizeof(int)));
+    CU(cudaMemset(ctx->exact_ticket.p, 0, sizeof(unsigned)));
     ctx->maxF = F;
     ctx->N = N;
     ctx->K = K;
@@ -328,6 +332,8 @@ static int allocate(e2sec_ctx *ctx, int F, int N, int K)
     d.rad_hi = (double *)ctx->rad_hi.p;
     d.amb = (int *)ctx->amb.p;
     d.amb_count = (int *)ctx->amb_count.p;
+    d.amb_list = (int *)ctx->amb_list.p;
+    d.exact_ticket = (unsigned *)ctx->exact_ticket.p;
     d.cell_state = (CellState *)ctx->cell_state.p;
     d.seg_list = (uint4 *)ctx->seg_list.p;
     d.seg_len = (unsigned *)ctx->seg_len.p;
@@ -516,7 +522,7 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
 {
     cudaStream_t st = ctx->stream;
     const int FK = d.F * d.K;
-    PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p};
+    PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p, (unsigned *)ctx->plan_split.p};
     u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
     // BOUNDED mode selects the medians inside cell_filter_kernel
     if (need_median && d.radius_mode != E2SEC_RADIUS_BOUNDED) { launch_pdl(ctx, axis_median_kernel, dim3(dim3(3, FK)), dim3(E2_SEL_THREADS), 0, st, d); }
@@ -525,22 +531,25 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
         launch_pdl(ctx, cell_filter_kernel<false>, dim3(FK), dim3(E2_CELL_THREADS), sizeof(CellSmem), st, d);
     }
     if (need_radius) {
-        CU(cudaMemsetAsync(below_acc, 0, sizeof(u64) * FK, st));
-        CU(cudaMemsetAsync(single, 0, sizeof(u64) * FK, st));
-        launch_pdl(ctx, radius_init_kernel, dim3(FK), dim3(256), 0, st, d, min_above);
+        // The exact O(n^2) selection for the entities of the exact path's list (BOUNDED: the few the cell table left open --
+        // small fixed grids that stride over the list; otherwise every entity).  The host never waits inside a batch, so the
+        // rounds are launched unconditionally; a round with nothing left returns at once.
+        const bool bounded = d.radius_mode == E2SEC_RADIUS_BOUNDED;
         const int grid = ctx->sm_count * 3;
+        const int small_grid = bounded ? std::min(FK, ctx->sm_count * 2) : FK;
         const size_t smem = sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double);
+        launch_pdl(ctx, radius_init_kernel, dim3(small_grid), dim3(256), 0, st, d, plan, below_acc, min_above, single, grid);
         for (int round = 0; round < E2_MAX_REFINE; ++round) {
-            launch_pdl(ctx, radius_plan_kernel, dim3(1), dim3(1024), 0, st, d, plan, 0);
             launch_pdl(ctx, pair_pass_kernel<false>, dim3(grid), dim3(E2_PAIR_THREADS), smem, st, d, plan, below_acc, min_above);
-            launch_pdl(ctx, radius_select_kernel, dim3((FK + 127) / 128), dim3(128), 0, st, d, below_acc, single);
+            const bool last = round == E2_MAX_REFINE - 1;         // the plan that follows the last round is the collect pass's
+            launch_pdl(ctx, radius_select_kernel, dim3(bounded ? std::min((FK + 7) / 8, ctx->sm_count) : (FK + 7) / 8), dim3(256), 0, st, d, plan, below_acc, single,
+                       last ? 1 : 0, last ? ctx->sm_count * 8 : grid);
         }
-        launch_pdl(ctx, radius_plan_kernel, dim3(1), dim3(1024), 0, st, d, plan, 1);
         launch_pdl(ctx, pair_pass_kernel<true>, dim3(ctx->sm_count * 8), dim3(E2_PAIR_THREADS), 3 * E2_TILE * sizeof(double), st, d, plan, below_acc, min_above);
-        launch_pdl(ctx, radius_final_kernel, dim3(FK), dim3(E2_SEL_THREADS), 0, st, d, min_above, single);
+        launch_pdl(ctx, radius_final_kernel, dim3(small_grid), dim3(E2_SEL_THREADS), 0, st, d, min_above, single);
         // entities that only had a point inside the radius band: the cell closure is finished at the exact radius
-        if (d.radius_mode == E2SEC_RADIUS_BOUNDED)
-            launch_pdl(ctx, cell_filter_kernel<true>, dim3(FK), dim3(E2_CELL_THREADS), sizeof(CellSmem), st, d);
+        if (bounded)
+            launch_pdl(ctx, cell_filter_kernel<true>, dim3(small_grid), dim3(E2_CELL_THREADS), sizeof(CellSmem), st, d);
     }
     cudaEventRecord(ctx->ev[3], st);
     launch_pdl(ctx, region_filter_kernel, dim3(FK), dim3(E2_FILTER_THREADS), 0, st, d);
@@ -1007,22 +1016,20 @@ static int run_radius_only(e2sec_ctx *ctx, const Dev &d)
 {
     cudaStream_t st = ctx->stream;
     const int FK = d.F * d.K;
-    PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p};
+    PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p, (unsigned *)ctx->plan_split.p};
     u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
-    CU(cudaMemsetAsync(below_acc, 0, sizeof(u64) * FK, st));
-    CU(cudaMemsetAsync(single, 0, sizeof(u64) * FK, st));
-    radius_init_kernel<<<FK, 256, 0, st>>>(d, min_above); LAUNCHED();
+    const int grid = ctx->sm_count * 3;
+    radius_init_kernel<<<FK, 256, 0, st>>>(d, plan, below_acc, min_above, single, grid); LAUNCHED();      // + the plan of the first pass
     const size_t smem = sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double);
     for (int round = 0; round < 12; ++round) {     // an operator call may take as many rounds as it needs
-        radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 0); LAUNCHED();
         unsigned total = 0;
         CU(cudaMemcpyAsync(&total, plan.total, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         if (!total) break;
-        pair_pass_kernel<false><<<ctx->sm_count * 3, E2_PAIR_THREADS, smem, st>>>(d, plan, below_acc, min_above); LAUNCHED();
-        radius_select_kernel<<<(FK + 127) / 128, 128, 0, st>>>(d, below_acc, single); LAUNCHED();
+        pair_pass_kernel<false><<<grid, E2_PAIR_THREADS, smem, st>>>(d, plan, below_acc, min_above); LAUNCHED();
+        radius_select_kernel<<<(FK + 7) / 8, 256, 0, st>>>(d, plan, below_acc, single, 0, grid); LAUNCHED();
     }
-    radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 1); LAUNCHED();
+    radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 1, ctx->sm_count * 8); LAUNCHED();
     pair_pass_kernel<true><<<ctx->sm_count * 8, E2_PAIR_THREADS, 3 * E2_TILE * sizeof(double), st>>>(d, plan, below_acc, min_above); LAUNCHED();
     radius_final_kernel<<<FK, E2_SEL_THREADS, 0, st>>>(d, min_above, single); LAUNCHED();
     CU(cudaGetLastError());

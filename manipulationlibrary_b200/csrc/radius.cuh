@@ -6,24 +6,31 @@
 // Keys are the bit patterns of d2 (non-negative doubles order like unsigned integers).
 //
 //   radius_init_kernel     per entity: pair count, the two middle ranks, an upper bound of d2 from the
-//                          AABB, first key interval [key(D2max * 2^-16), key(D2max)]
-//   radius_plan_kernel     work list: one item = one 256 x 256 tile pair (ti <= tj) of an active entity
-//   pair_hist_kernel       every pair of the item -> bin = (key - klo) >> shift, counted in thread-private
+//                          AABB, first key interval: the cell table's band [rad_lo^2, rad_hi^2] when there is one
+//                          (BOUNDED mode), else [key(D2max * 2^-16), key(D2max)]
+//   plan_scan              work list: one item = a slice of one 256 x 256 tile pair (ti <= tj) of an active entity.  Run
+//                          by the LAST CTA to finish of radius_init_kernel / radius_select_kernel (no launch of its own)
+//   pair_pass_kernel<0>    every pair of the item -> bin = (key - klo) >> shift, counted in thread-private
 //                          uint16 shared-memory counters [bin][thread] (no atomics in the pair loop)
 //   radius_select_kernel   picks the bin holding the lower middle rank, shrinks the interval 256x; when the
 //                          interval holds <= E2_CAND_CAP pairs switches the entity to "collect"
-//   pair_collect_kernel    appends the keys inside the interval, tracks the smallest key above it
+//   pair_pass_kernel<1>    appends the keys inside the interval, tracks the smallest key above it
 //   radius_final_kernel    block_select2 over the candidates -> (sqrt(a) + sqrt(b)) / 2
+//
+// The kernels walk the exact path's entity LIST (common.cuh: exact_count / exact_entity) with small fixed grids: in BOUNDED
+// mode that is the handful of entities the cell table left open, not F x K CTAs that find out they have nothing to do.
 #pragma once
 #include "common.cuh"
 #include "select.cuh"
 
 #define E2_PAIR_THREADS 128     // 2 i-points per thread
 #define E2_FLUSH_ITEMS 100      // uint16 counters: <= 512 increments per thread per item
+#define E2_PAIR_MAX_SPLIT 8     // a tile pair is cut into up to 8 slices of its j range when there are few of them
 
 struct PairPlan {
-    unsigned *off;      // F*K + 1 exclusive prefix of items
-    unsigned *total;    // = off[F*K]
+    unsigned *off;      // count + 1 exclusive prefix of TILE PAIRS over the exact path's list
+    unsigned *total;    // items = off[count] * split
+    unsigned *split;    // slices per tile pair (1, 2, 4 or 8): enough items to occupy the grid
 };
 
 __device__ __forceinline__ int shift_for_width(u64 width)
@@ -33,115 +40,171 @@ __device__ __forceinline__ int shift_for_width(u64 width)
     return s;
 }
 
-// grid F*K CTAs of 256 threads
-__global__ void __launch_bounds__(256) radius_init_kernel(Dev d, u64 *min_above)
+// The calling CTA alone (any multiple of 32 threads): tile pairs of every listed entity in phase `want_phase`, exclusive
+// scan.  RadiusState is read around L1 -- other CTAs of the same grid have just written it.
+__device__ void plan_scan(const Dev &d, PairPlan plan, int want_phase, int grid_hint)
+{
+    __shared__ unsigned warp_tot[32];
+    __shared__ unsigned carry;
+    const int count = exact_count(d), nt = blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < count; base += nt) {
+        const int li = base + tid;
+        unsigned items = 0;
+        if (li < count) {
+            const RadiusState *rs = d.rs + exact_entity(d, li);
+            if (__ldcg(&rs->phase) == want_phase) {
+                const unsigned T = (unsigned)((__ldcg(&rs->n) + E2_TILE - 1) / E2_TILE);
+                items = T * (T + 1) / 2;
+            }
+        }
+        unsigned v = items;
+        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+        if (lane == 31) warp_tot[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned w = (lane < (nt >> 5)) ? warp_tot[lane] : 0u;
+            for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += t; }
+            warp_tot[lane] = w;
+        }
+        __syncthreads();
+        const unsigned excl = carry + v - items + (warp ? warp_tot[warp - 1] : 0u);
+        if (li < count) plan.off[li] = excl;
+        __syncthreads();
+        if (tid == nt - 1) carry = excl + items;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const unsigned pairs = carry;
+        unsigned split = 1;
+        while (split < E2_PAIR_MAX_SPLIT && pairs * split < 4u * (unsigned)grid_hint) split <<= 1;
+        plan.off[count] = pairs;
+        *plan.split = split;
+        *plan.total = pairs * split;
+    }
+}
+
+// true in exactly one CTA of the grid: the last one to get here.  Everything the other CTAs wrote before is visible to it.
+__device__ __forceinline__ bool exact_last_cta(const Dev &d)
+{
+    __shared__ int last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(d.exact_ticket, 1u);
+        last = (t == gridDim.x * gridDim.y - 1u);
+        if (last) *d.exact_ticket = 0u;              // ready for the next kernel (stream order)
+    }
+    __syncthreads();
+    if (last) __threadfence();
+    return last != 0;
+}
+
+// grid: any number of CTAs of 256 threads, striding over the list
+__global__ void __launch_bounds__(256) radius_init_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *min_above, u64 *single_count, int grid_hint)
 {
     pdl_enter();
     if (exact_path_idle(d)) return;
     __shared__ double red[6][8];
-    const int fe = blockIdx.x, f = fe / d.K;
-    const int off = d.ent_off[fe], n = d.ent_raw[fe];
-    RadiusState &rs = d.rs[fe];
-    if (threadIdx.x == 0) {
-        d.radius[fe] = __longlong_as_double(0x7ff8000000000000ll);
-        d.cand_n[fe] = 0;
-        min_above[fe] = ~0ull;
-    }
-    for (int b = threadIdx.x; b < E2_NBINS; b += blockDim.x) d.hist[(size_t)fe * E2_NBINS + b] = 0;
-    if (off < 0 || !entity_filtered(d, fe, n) || (d.radius_mode == E2SEC_RADIUS_BOUNDED && !d.amb[fe])) {   // nothing to select for this entity
-        if (threadIdx.x == 0) { rs.phase = 3; rs.n = n; }
-        return;
-    }
-    const double *x = d.px + (size_t)f * d.cap + off, *y = d.py + (size_t)f * d.cap + off, *z = d.pz + (size_t)f * d.cap + off;
-    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        lo[0] = fmin(lo[0], x[i]); hi[0] = fmax(hi[0], x[i]);
-        lo[1] = fmin(lo[1], y[i]); hi[1] = fmax(hi[1], y[i]);
-        lo[2] = fmin(lo[2], z[i]); hi[2] = fmax(hi[2], z[i]);
-    }
-    for (int a = 0; a < 3; ++a) {
-        lo[a] = warp_min_d(lo[a]);
-        hi[a] = warp_max_d(hi[a]);
-        if ((threadIdx.x & 31) == 0) { red[a][threadIdx.x >> 5] = lo[a]; red[3 + a][threadIdx.x >> 5] = hi[a]; }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double ext2 = 0.0;
+    const int count = exact_count(d);
+    for (int li = blockIdx.x; li < count; li += gridDim.x) {
+        const int fe = exact_entity(d, li), f = fe / d.K;
+        const int off = d.ent_off[fe], n = d.ent_raw[fe];
+        RadiusState &rs = d.rs[fe];
+        if (threadIdx.x == 0) {
+            d.radius[fe] = __longlong_as_double(0x7ff8000000000000ll);
+            d.cand_n[fe] = 0;
+            min_above[fe] = ~0ull;
+            below_acc[fe] = 0;
+            single_count[fe] = 0;
+        }
+        for (int b = threadIdx.x; b < E2_NBINS; b += blockDim.x) d.hist[(size_t)fe * E2_NBINS + b] = 0;
+        if (off < 0 || !entity_filtered(d, fe, n)) {                 // nothing to select for this entity
+            if (threadIdx.x == 0) { rs.phase = 3; rs.n = n; }
+            continue;
+        }
+        const double *x = d.px + (size_t)f * d.cap + off, *y = d.py + (size_t)f * d.cap + off, *z = d.pz + (size_t)f * d.cap + off;
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            lo[0] = fmin(lo[0], x[i]); hi[0] = fmax(hi[0], x[i]);
+            lo[1] = fmin(lo[1], y[i]); hi[1] = fmax(hi[1], y[i]);
+            lo[2] = fmin(lo[2], z[i]); hi[2] = fmax(hi[2], z[i]);
+        }
         for (int a = 0; a < 3; ++a) {
-            double l = red[a][0], h = red[3 + a][0];
-            for (int w = 1; w < 8; ++w) { l = fmin(l, red[a][w]); h = fmax(h, red[3 + a][w]); }
-            ext2 += (h - l) * (h - l);
+            lo[a] = warp_min_d(lo[a]);
+            hi[a] = warp_max_d(hi[a]);
+            if ((threadIdx.x & 31) == 0) { red[a][threadIdx.x >> 5] = lo[a]; red[3 + a][threadIdx.x >> 5] = hi[a]; }
         }
-        u64 P = (u64)n * (u64)(n - 1) / 2;
-        rs.k2 = P / 2;
-        rs.k1 = (P & 1) ? rs.k2 : rs.k2 - 1;
-        rs.n = n;
-        rs.below = 0;
-        if (!(ext2 > 0.0)) {           // every point identical: all distances are 0
-            d.radius[fe] = 0.0;
-            rs.phase = 2;
-            return;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double ext2 = 0.0;
+            for (int a = 0; a < 3; ++a) {
+                double l = red[a][0], h = red[3 + a][0];
+                for (int w = 1; w < 8; ++w) { l = fmin(l, red[a][w]); h = fmax(h, red[3 + a][w]); }
+                ext2 += (h - l) * (h - l);
+            }
+            u64 P = (u64)n * (u64)(n - 1) / 2;
+            rs.k2 = P / 2;
+            rs.k1 = (P & 1) ? rs.k2 : rs.k2 - 1;
+            rs.n = n;
+            rs.below = 0;
+            if (!(ext2 > 0.0)) {           // every point identical: all distances are 0
+                d.radius[fe] = 0.0;
+                rs.phase = 2;
+            } else {
+                const double top = ext2 * 1.000001;  // d2 of any pair <= squared AABB diagonal (+ rounding slack)
+                const u64 ktop = d2key(top) + 1;
+                u64 khi = ktop;
+                u64 klo = d2key(top * (1.0 / 65536.0));
+                if (d.radius_mode == E2SEC_RADIUS_BOUNDED) {
+                    // the cell table's bounds of the two middle distances (cells.cuh phase D; float32-rounded, hence the
+                    // slack).  Should they ever miss, radius_select_kernel reopens the interval on the side that is short.
+                    const double rl = d.rad_lo[fe], rh = d.rad_hi[fe];
+                    if (rl >= 0.0 && rh >= rl && rh < 1e150) {
+                        const u64 bl = d2key(rl * rl * (1.0 - 1.0 / 1048576.0));
+                        const u64 bh = d2key(rh * rh * (1.0 + 1.0 / 1048576.0)) + 1;
+                        if (bh < khi) khi = bh;
+                        if (bl < khi) klo = bl;
+                        if (klo >= khi) klo = 0;
+                    }
+                }
+                rs.ktop = ktop;
+                rs.klo = klo;
+                rs.width = khi - klo;
+                rs.shift = shift_for_width(rs.width);
+                rs.phase = 0;
+            }
         }
-        double top = ext2 * 1.000001;  // d2 of any pair <= squared AABB diagonal (+ rounding slack)
-        u64 khi = d2key(top) + 1;
-        u64 klo = d2key(top * (1.0 / 65536.0));
-        rs.klo = klo;
-        rs.width = khi - klo;
-        rs.shift = shift_for_width(rs.width);
-        rs.phase = 0;
+        __syncthreads();                   // red[] is reused by the next entity of this CTA
     }
+    if (exact_last_cta(d)) plan_scan(d, plan, 0, grid_hint);
 }
 
-// single CTA: items per entity for the wanted phase, exclusive scan
-__global__ void __launch_bounds__(1024) radius_plan_kernel(Dev d, PairPlan plan, int want_phase)
+// single CTA: the plan for one phase on its own (operator calls that decide the number of rounds on the host)
+__global__ void __launch_bounds__(1024) radius_plan_kernel(Dev d, PairPlan plan, int want_phase, int grid_hint)
 {
     pdl_enter();
     if (exact_path_idle(d)) return;
-    __shared__ unsigned warp_tot[32];
-    __shared__ unsigned carry;
-    const int n_fe = d.F * d.K;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    for (int base = 0; base < n_fe; base += 1024) {
-        int fe = base + threadIdx.x;
-        unsigned items = 0;
-        if (fe < n_fe && d.rs[fe].phase == want_phase) {
-            unsigned T = (unsigned)((d.rs[fe].n + E2_TILE - 1) / E2_TILE);
-            items = T * (T + 1) / 2;
-        }
-        unsigned v = items;
-        for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, v, o); if ((threadIdx.x & 31) >= o) v += t; }
-        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = v;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            unsigned w = warp_tot[threadIdx.x];
-            for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, w, o); if (threadIdx.x >= o) w += t; }
-            warp_tot[threadIdx.x] = w;
-        }
-        __syncthreads();
-        unsigned excl = carry + v - items + ((threadIdx.x >> 5) ? warp_tot[(threadIdx.x >> 5) - 1] : 0);
-        if (fe < n_fe) plan.off[fe] = excl;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + items;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) { plan.off[n_fe] = carry; *plan.total = carry; }
+    plan_scan(d, plan, want_phase, grid_hint);
 }
 
-struct PairItem { int fe, ti, tj; };
+struct PairItem { int fe, ti, tj, slice; };
 
-// item index -> (entity, tile pair). Row ti of the upper triangle holds tiles tj = ti .. T-1.
-__device__ __forceinline__ PairItem decode_item(const Dev &d, const PairPlan &plan, unsigned item)
+// item index -> (entity, tile pair, slice of its j range). Row ti of the upper triangle holds tiles tj = ti .. T-1.
+__device__ __forceinline__ PairItem decode_item(const Dev &d, const PairPlan &plan, unsigned item, int count, unsigned split)
 {
-    int lo = 0, hi = d.F * d.K;     // last fe with off[fe] <= item
+    const unsigned pair = item / split;
+    int lo = 0, hi = count;         // last list position with off[li] <= pair
     while (hi - lo > 1) {
         int mid = (lo + hi) >> 1;
-        if (plan.off[mid] <= item) lo = mid; else hi = mid;
+        if (plan.off[mid] <= pair) lo = mid; else hi = mid;
     }
     PairItem it;
-    it.fe = lo;
-    unsigned local = item - plan.off[lo];
-    int T = (d.rs[lo].n + E2_TILE - 1) / E2_TILE;
+    it.fe = exact_entity(d, lo);
+    it.slice = (int)(item - pair * split);
+    unsigned local = pair - plan.off[lo];
+    int T = (d.rs[it.fe].n + E2_TILE - 1) / E2_TILE;
     int ti = 0;
     unsigned row = (unsigned)T;
     while (local >= row) { local -= row; --row; ++ti; }
@@ -169,6 +232,9 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
     const int slot = ((tid & 63) << 1) | (tid >> 6);
     const unsigned total = *plan.total;
     if (total == 0) return;
+    const int count = exact_count(d);
+    const unsigned split = *plan.split;
+    const int jw = E2_TILE / (int)split;           // j points per item
     const unsigned per = (total + gridDim.x - 1) / gridDim.x;
     const unsigned first = blockIdx.x * per;
     const unsigned last = min(total, first + per);
@@ -208,7 +274,7 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
     (void)red;
 
     for (unsigned item = first; item < last; ++item) {
-        if (tid == 0) cur = decode_item(d, plan, item);
+        if (tid == 0) cur = decode_item(d, plan, item, count, split);
         __syncthreads();
         const PairItem it = cur;
         if (it.fe != cur_fe || since_flush >= E2_FLUSH_ITEMS) {
@@ -222,8 +288,8 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
         const int n = d.rs[it.fe].n;
         const size_t pb = (size_t)f * d.cap + d.ent_off[it.fe];
         const double *X = d.px + pb, *Y = d.py + pb, *Z = d.pz + pb;
-        const int jb = it.tj * E2_TILE, ib = it.ti * E2_TILE;
-        const int jn = min(E2_TILE, n - jb);
+        const int jb = it.tj * E2_TILE + it.slice * jw, ib = it.ti * E2_TILE;
+        const int jn = min(jw, n - jb);              // <= 0: the slice lies beyond the entity's last point
         __syncthreads();      // previous item's readers of sx/sy/sz are done
         for (int j = tid; j < jn; j += E2_PAIR_THREADS) { sx[j] = X[jb + j]; sy[j] = Y[jb + j]; sz[j] = Z[jb + j]; }
         const int gi0 = ib + tid, gi1 = ib + tid + E2_PAIR_THREADS;
@@ -269,84 +335,117 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
     if (cur_fe >= 0) flush(cur_fe);
 }
 
-// one thread per entity
-__global__ void radius_select_kernel(Dev d, u64 *below_acc, u64 *single_count)
+// One warp per listed entity (lanes own 8 consecutive bins each), any number of CTAs of 256 threads striding over the
+// list; the last CTA to finish plans the next pass (the items of phase `next_phase`).
+__global__ void __launch_bounds__(256) radius_select_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *single_count, int next_phase, int grid_hint)
 {
     pdl_enter();
     if (exact_path_idle(d)) return;
-    const int fe = blockIdx.x * blockDim.x + threadIdx.x;
-    if (fe >= d.F * d.K) return;
-    RadiusState &rs = d.rs[fe];
-    if (rs.phase != 0) return;
-    u64 *h = d.hist + (size_t)fe * E2_NBINS;
-    const u64 below = below_acc[fe];
-    below_acc[fe] = 0;
-    u64 total = 0;
-    for (int b = 0; b < E2_NBINS; ++b) total += h[b];
-    const u64 r1 = rs.k1;
-    if (r1 < below) {                         // the rank lies under the interval: reopen downwards
-        rs.width += rs.klo;
-        rs.klo = 0;
-        rs.shift = shift_for_width(rs.width);
-    } else if (r1 >= below + total) {         // cannot happen while the interval reaches the d2 upper bound
-        atomicExch(d.error, E2SEC_ERR_STATE);
-        rs.phase = 2;
-    } else {
-        u64 acc = below;
-        int b1 = 0;
-        for (; b1 < E2_NBINS - 1; ++b1) {
-            if (r1 < acc + h[b1]) break;
-            acc += h[b1];
-        }
-        const u64 in_bin = h[b1];
-        u64 nklo = rs.klo + ((u64)b1 << rs.shift);
-        u64 nend = rs.klo + ((u64)(b1 + 1) << rs.shift);
-        if (nend > rs.klo + rs.width || nend < nklo) nend = rs.klo + rs.width;
-        rs.klo = nklo;
-        rs.width = nend - nklo;
-        rs.below = acc;
-        if (rs.width == 1) {                  // a single key: every pair of the bin has exactly this d2
-            single_count[fe] = in_bin;
-            rs.phase = 1;
-        } else if (in_bin <= (u64)E2_CAND_CAP) {
-            single_count[fe] = 0;
-            rs.phase = 1;
+    const int count = exact_count(d), lane = threadIdx.x & 31;
+    const int warps = (blockDim.x >> 5) * gridDim.x;
+    constexpr int PER = E2_NBINS / 32;
+    for (int li = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); li < count; li += warps) {
+        const int fe = exact_entity(d, li);
+        RadiusState &rs = d.rs[fe];
+        if (rs.phase != 0) continue;
+        u64 *h = d.hist + (size_t)fe * E2_NBINS;
+        u64 hb[PER], mine = 0;
+        for (int k = 0; k < PER; ++k) { hb[k] = h[lane * PER + k]; mine += hb[k]; h[lane * PER + k] = 0; }
+        u64 incl = mine;
+        for (int o = 1; o < 32; o <<= 1) { const u64 t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        const u64 total = __shfl_sync(0xffffffffu, incl, 31);
+        const u64 below = below_acc[fe];
+        const u64 r1 = rs.k1;
+        // the first bin whose cumulative count exceeds the rank (the last bin when none does: cannot happen once
+        // r1 < below + total holds)
+        const bool holds = r1 >= below && r1 < below + incl;
+        const unsigned who = __ballot_sync(0xffffffffu, holds);
+        __syncwarp();
+        if (lane == 0) below_acc[fe] = 0;
+        if (r1 < below) {                         // the rank lies under the interval: reopen downwards
+            if (lane == 0) {
+                rs.width += rs.klo;
+                rs.klo = 0;
+                rs.shift = shift_for_width(rs.width);
+            }
+        } else if (r1 >= below + total) {
+            if (lane == 0) {
+                const u64 end = rs.klo + rs.width;
+                if (end < rs.ktop) {              // the rank lies above an interval that started from bounds: reopen upwards
+                    rs.klo = end;
+                    rs.width = rs.ktop - end;
+                    rs.shift = shift_for_width(rs.width);
+                } else {                          // cannot happen while the interval reaches the d2 upper bound
+                    atomicExch(d.error, E2SEC_ERR_STATE);
+                    rs.phase = 2;
+                }
+            }
         } else {
-            rs.shift = shift_for_width(rs.width);
+            const int owner = __ffs(who) - 1;
+            if (lane == owner) {
+                u64 acc = below + incl - mine;
+                int k = 0;
+                for (; k < PER - 1; ++k) {
+                    if (r1 < acc + hb[k]) break;
+                    acc += hb[k];
+                }
+                const int b1 = lane * PER + k;
+                const u64 in_bin = hb[k];
+                u64 nklo = rs.klo + ((u64)b1 << rs.shift);
+                u64 nend = rs.klo + ((u64)(b1 + 1) << rs.shift);
+                if (nend > rs.klo + rs.width || nend < nklo) nend = rs.klo + rs.width;
+                rs.klo = nklo;
+                rs.width = nend - nklo;
+                rs.below = acc;
+                if (rs.width == 1) {                  // a single key: every pair of the bin has exactly this d2
+                    single_count[fe] = in_bin;
+                    rs.phase = 1;
+                } else if (in_bin <= (u64)E2_CAND_CAP) {
+                    single_count[fe] = 0;
+                    rs.phase = 1;
+                } else {
+                    rs.shift = shift_for_width(rs.width);
+                }
+            }
         }
     }
-    for (int b = 0; b < E2_NBINS; ++b) h[b] = 0;
+    if (exact_last_cta(d)) plan_scan(d, plan, next_phase, grid_hint);
 }
 
-// grid F*K CTAs of E2_SEL_THREADS
+// any number of CTAs of E2_SEL_THREADS, striding over the list
 __global__ void __launch_bounds__(E2_SEL_THREADS) radius_final_kernel(Dev d, const u64 *min_above, const u64 *single_count)
 {
     pdl_enter();
     if (exact_path_idle(d)) return;
     __shared__ SelectSmem sm;
-    const int fe = blockIdx.x;
-    RadiusState &rs = d.rs[fe];
-    if (rs.phase == 0 && threadIdx.x == 0) atomicExch(d.error, E2SEC_ERR_STATE);   // the launched refinement rounds did not converge
-    if (rs.phase != 1) return;
-    const u64 r1 = rs.k1 - rs.below, r2 = rs.k2 - rs.below;
-    u64 v1, v2;
-    const u64 single = single_count[fe];
-    if (single) {
-        v1 = rs.klo;
-        v2 = (r2 < single) ? rs.klo : min_above[fe];
-    } else {
-        const unsigned m = min(d.cand_n[fe], (unsigned)E2_CAND_CAP);
-        const u64 *c = d.cand + (size_t)fe * E2_CAND_CAP;
-        if (r2 < m) {
-            block_select2([&](int i) { return c[i]; }, (int)m, r1, r2, v1, v2, sm);
+    const int count = exact_count(d);
+    for (int li = blockIdx.x; li < count; li += gridDim.x) {
+        const int fe = exact_entity(d, li);
+        RadiusState &rs = d.rs[fe];
+        if (rs.phase == 0 && threadIdx.x == 0) atomicExch(d.error, E2SEC_ERR_STATE);   // the launched refinement rounds did not converge
+        if (rs.phase != 1) continue;
+        const u64 r1 = rs.k1 - rs.below, r2 = rs.k2 - rs.below;
+        u64 v1, v2;
+        const u64 single = single_count[fe];
+        if (single) {
+            v1 = rs.klo;
+            v2 = (r2 < single) ? rs.klo : min_above[fe];
         } else {
-            block_select2([&](int i) { return c[i]; }, (int)m, r1, r1, v1, v2, sm);
-            v2 = min_above[fe];
+            const unsigned m = min(d.cand_n[fe], (unsigned)E2_CAND_CAP);
+            const u64 *c = d.cand + (size_t)fe * E2_CAND_CAP;
+            if (r2 < m) {
+                block_select2([&](int i) { return c[i]; }, (int)m, r1, r2, v1, v2, sm);
+            } else {
+                block_select2([&](int i) { return c[i]; }, (int)m, r1, r1, v1, v2, sm);
+                v2 = min_above[fe];
+            }
         }
-    }
-    if (threadIdx.x == 0) {
-        double a = sqrt(key2d(v1)), b = sqrt(key2d(v2));
-        d.radius[fe] = (rs.k1 == rs.k2) ? a : (a + b) / 2.0;
-        rs.phase = 2;
+        __syncthreads();                          // every thread has read rs before thread 0 moves it on
+        if (threadIdx.x == 0) {
+            double a = sqrt(key2d(v1)), b = sqrt(key2d(v2));
+            d.radius[fe] = (rs.k1 == rs.k2) ? a : (a + b) / 2.0;
+            rs.phase = 2;
+        }
+        __syncthreads();
     }
 }
