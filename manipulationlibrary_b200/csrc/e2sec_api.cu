@@ -153,8 +153,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
         return fail(nullptr, E2SEC_ERR_CUDA, msg);
     }
     ctx->ev_valid = true;
-    cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)(sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double)));
+    cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E2_PAIR_SMEM_HIST);
     cudaFuncSetAttribute(cell_filter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
     cudaFuncSetAttribute(cell_filter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CellSmem));
     cudaFuncSetAttribute(seg_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SegFusedSmem));
@@ -537,7 +536,7 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
         const bool bounded = d.radius_mode == E2SEC_RADIUS_BOUNDED;
         const int grid = ctx->sm_count * 3;
         const int small_grid = bounded ? std::min(FK, ctx->sm_count * 2) : FK;
-        const size_t smem = sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double);
+        const size_t smem = E2_PAIR_SMEM_HIST;
         launch_pdl(ctx, radius_init_kernel, dim3(small_grid), dim3(256), 0, st, d, plan, below_acc, min_above, single, grid);
         for (int round = 0; round < E2_MAX_REFINE; ++round) {
             launch_pdl(ctx, pair_pass_kernel<false>, dim3(grid), dim3(E2_PAIR_THREADS), smem, st, d, plan, below_acc, min_above);
@@ -545,7 +544,7 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
             launch_pdl(ctx, radius_select_kernel, dim3(bounded ? std::min((FK + 7) / 8, ctx->sm_count) : (FK + 7) / 8), dim3(256), 0, st, d, plan, below_acc, single,
                        last ? 1 : 0, last ? ctx->sm_count * 8 : grid);
         }
-        launch_pdl(ctx, pair_pass_kernel<true>, dim3(ctx->sm_count * 8), dim3(E2_PAIR_THREADS), 3 * E2_TILE * sizeof(double), st, d, plan, below_acc, min_above);
+        launch_pdl(ctx, pair_pass_kernel<true>, dim3(ctx->sm_count * 8), dim3(E2_PAIR_THREADS), E2_PAIR_SMEM_COLLECT, st, d, plan, below_acc, min_above);
         launch_pdl(ctx, radius_final_kernel, dim3(small_grid), dim3(E2_SEL_THREADS), 0, st, d, min_above, single);
         // entities that only had a point inside the radius band: the cell closure is finished at the exact radius
         if (bounded)
@@ -1020,7 +1019,7 @@ static int run_radius_only(e2sec_ctx *ctx, const Dev &d)
     u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
     const int grid = ctx->sm_count * 3;
     radius_init_kernel<<<FK, 256, 0, st>>>(d, plan, below_acc, min_above, single, grid); LAUNCHED();      // + the plan of the first pass
-    const size_t smem = sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS + 3 * E2_TILE * sizeof(double);
+    const size_t smem = E2_PAIR_SMEM_HIST;
     for (int round = 0; round < 12; ++round) {     // an operator call may take as many rounds as it needs
         unsigned total = 0;
         CU(cudaMemcpyAsync(&total, plan.total, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
@@ -1030,7 +1029,7 @@ static int run_radius_only(e2sec_ctx *ctx, const Dev &d)
         radius_select_kernel<<<(FK + 7) / 8, 256, 0, st>>>(d, plan, below_acc, single, 0, grid); LAUNCHED();
     }
     radius_plan_kernel<<<1, 1024, 0, st>>>(d, plan, 1, ctx->sm_count * 8); LAUNCHED();
-    pair_pass_kernel<true><<<ctx->sm_count * 8, E2_PAIR_THREADS, 3 * E2_TILE * sizeof(double), st>>>(d, plan, below_acc, min_above); LAUNCHED();
+    pair_pass_kernel<true><<<ctx->sm_count * 8, E2_PAIR_THREADS, E2_PAIR_SMEM_COLLECT, st>>>(d, plan, below_acc, min_above); LAUNCHED();
     radius_final_kernel<<<FK, E2_SEL_THREADS, 0, st>>>(d, min_above, single); LAUNCHED();
     CU(cudaGetLastError());
     return E2SEC_OK;

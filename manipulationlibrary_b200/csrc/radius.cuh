@@ -215,19 +215,75 @@ __device__ __forceinline__ PairItem decode_item(const Dev &d, const PairPlan &pl
 
 extern __shared__ __align__(16) unsigned char pair_smem[];
 
-// Shared layout: uint16 cnt[E2_NBINS][E2_PAIR_THREADS] | double sx[256], sy[256], sz[256]
+#define E2_PAIR_ROWS (E2_NBINS + 2)     // the bins, then one row for keys under the interval and one for everything else
+#define E2_PAIR_CNT_BYTES (sizeof(unsigned short) * E2_PAIR_ROWS * E2_PAIR_THREADS)
+#define E2_PAIR_SMEM_HIST (E2_PAIR_CNT_BYTES + 3 * E2_TILE * sizeof(double))
+#define E2_PAIR_SMEM_COLLECT (3 * E2_TILE * sizeof(double))
+
+struct PairLoopState {
+    u64 klo, width;
+    int shift;
+    u64 above_ta;       // COLLECT: smallest (key - klo) >= width seen so far
+};
+
+// All pairs (i, j) of one item for the two i-points of this thread, j over the shared-memory slice.  No data-dependent
+// branch: a pair outside the interval counts into the row "below" or "rest" (keys under klo wrap around to >= 2^63), a
+// pair that is not one (DIAG: j <= i on the diagonal tile; i beyond the entity: the caller gives it x = +inf, a key above
+// every interval) into "rest".  The FP64 pipe -- 8 operations per pair -- is the floor; everything else has to fit under it.
+template <bool COLLECT, bool DIAG>
+__device__ __forceinline__ void pair_loop(const Dev &d, int fe, const double *sx, const double *sy, const double *sz, int jn, int jb,
+                                          int gi0, int gi1, double x0, double y0, double z0, double x1, double y1, double z1,
+                                          unsigned short *cnt_slot, PairLoopState &st)
+{
+    const u64 klo = st.klo, width = st.width;
+    const int shift = st.shift;
+#pragma unroll 2
+    for (int j = 0; j < jn; ++j) {
+        const double xj = sx[j], yj = sy[j], zj = sz[j];
+        const int gj = jb + j;
+        const u64 ka = d2key(dist2(x0, y0, z0, xj, yj, zj));
+        const u64 kb = d2key(dist2(x1, y1, z1, xj, yj, zj));
+        const u64 ta = ka - klo, tb = kb - klo;
+        bool ha = ta < width, hb = tb < width;
+        if (!COLLECT) {
+            unsigned ra = ha ? (unsigned)(ta >> shift) : (unsigned)(E2_NBINS + 1) - (unsigned)(ta >> 63);
+            unsigned rb = hb ? (unsigned)(tb >> shift) : (unsigned)(E2_NBINS + 1) - (unsigned)(tb >> 63);
+            if (DIAG) { ra = (gj > gi0) ? ra : (unsigned)(E2_NBINS + 1); rb = (gj > gi1) ? rb : (unsigned)(E2_NBINS + 1); }
+            cnt_slot[ra * E2_PAIR_THREADS] += 1;
+            cnt_slot[rb * E2_PAIR_THREADS] += 1;
+        } else {
+            if (DIAG) { ha = ha && gj > gi0; hb = hb && gj > gi1; }
+            // candidates are appended with one global atomic per warp (the j loop is uniform across the CTA)
+            const unsigned ba = __ballot_sync(0xffffffffu, ha), bb = __ballot_sync(0xffffffffu, hb);
+            if (ba | bb) {
+                const int lane = threadIdx.x & 31;
+                unsigned base = 0;
+                if (lane == 0) base = atomicAdd(d.cand_n + fe, (unsigned)(__popc(ba) + __popc(bb)));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const unsigned lt = (1u << lane) - 1u;
+                if (ha) { const unsigned pos = base + __popc(ba & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)fe * E2_CAND_CAP + pos] = ka; }
+                if (hb) { const unsigned pos = base + __popc(ba) + __popc(bb & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)fe * E2_CAND_CAP + pos] = kb; }
+            }
+            u64 ca = ha ? ~0ull : ta, cb = hb ? ~0ull : tb;
+            if (DIAG) { ca = (gj > gi0) ? ca : ~0ull; cb = (gj > gi1) ? cb : ~0ull; }
+            const u64 c = ca < cb ? ca : cb;
+            st.above_ta = c < st.above_ta ? c : st.above_ta;
+        }
+    }
+}
+
+// Shared layout: uint16 cnt[E2_PAIR_ROWS][E2_PAIR_THREADS] (histogram passes only) | double sx[256], sy[256], sz[256]
 template <bool COLLECT>
 __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *min_above)
 {
     pdl_enter();
     if (exact_path_idle(d)) return;
     unsigned short *cnt = reinterpret_cast<unsigned short *>(pair_smem);
-    double *sx = reinterpret_cast<double *>(pair_smem + (COLLECT ? 0 : sizeof(unsigned short) * E2_NBINS * E2_PAIR_THREADS));
+    double *sx = reinterpret_cast<double *>(pair_smem + (COLLECT ? 0 : E2_PAIR_CNT_BYTES));
     double *sy = sx + E2_TILE, *sz = sy + E2_TILE;
     __shared__ PairItem cur;
-    __shared__ u64 red[E2_PAIR_THREADS / 32];
     const int tid = threadIdx.x;
-    // counter slot of this thread inside a bin row: lanes of one warp hit 32 distinct 4-byte words (banks);
+    // counter slot of this thread inside a row: lanes of one warp hit 32 distinct 4-byte words (banks);
     // threads tid and tid + 64 share a word but own different halves of it
     const int slot = ((tid & 63) << 1) | (tid >> 6);
     const unsigned total = *plan.total;
@@ -239,40 +295,40 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
     const unsigned first = blockIdx.x * per;
     const unsigned last = min(total, first + per);
     if (first >= last) return;
+    constexpr int CNT_WORDS = E2_PAIR_ROWS * E2_PAIR_THREADS / 2;
     if (!COLLECT)
-        for (int i = tid; i < E2_NBINS * E2_PAIR_THREADS / 2; i += E2_PAIR_THREADS) reinterpret_cast<unsigned *>(cnt)[i] = 0;
+        for (int i = tid; i < CNT_WORDS; i += E2_PAIR_THREADS) reinterpret_cast<unsigned *>(cnt)[i] = 0;
     int cur_fe = -1, since_flush = 0;
-    u64 below = 0, above_min = ~0ull;
-    u64 klo = 0, width = 0;
-    int shift = 0;
+    PairLoopState st;
+    st.klo = 0; st.width = 0; st.shift = 0; st.above_ta = ~0ull;
 
     auto flush = [&](int fe) {
         __syncthreads();
         if (!COLLECT) {
-            for (int b = tid; b < E2_NBINS; b += E2_PAIR_THREADS) {
+            for (int b = tid; b <= E2_NBINS; b += E2_PAIR_THREADS) {           // the bins and the row "below"
                 const unsigned *row = reinterpret_cast<const unsigned *>(cnt + b * E2_PAIR_THREADS);
                 unsigned s = 0;
                 for (int w = 0; w < E2_PAIR_THREADS / 2; ++w) {
                     unsigned v = row[(w + tid) & (E2_PAIR_THREADS / 2 - 1)];
                     s += (v & 0xffffu) + (v >> 16);
                 }
-                if (s) atomicAdd(d.hist + (size_t)fe * E2_NBINS + b, (u64)s);
+                if (s) {
+                    if (b < E2_NBINS) atomicAdd(d.hist + (size_t)fe * E2_NBINS + b, (u64)s);
+                    else atomicAdd(below_acc + fe, (u64)s);
+                }
             }
             __syncthreads();
-            for (int i = tid; i < E2_NBINS * E2_PAIR_THREADS / 2; i += E2_PAIR_THREADS) reinterpret_cast<unsigned *>(cnt)[i] = 0;
-            u64 b = warp_sum_u64(below);
-            if ((tid & 31) == 0 && b) atomicAdd(below_acc + fe, b);
-            below = 0;
+            for (int i = tid; i < CNT_WORDS; i += E2_PAIR_THREADS) reinterpret_cast<unsigned *>(cnt)[i] = 0;
         } else {
-            u64 m = warp_min_u64(above_min);
-            if ((tid & 31) == 0 && m != ~0ull) atomicMin(min_above + fe, m);
-            above_min = ~0ull;
+            const u64 m = warp_min_u64(st.above_ta);
+            if ((tid & 31) == 0 && m < (1ull << 63)) atomicMin(min_above + fe, st.klo + m);
+            st.above_ta = ~0ull;
         }
         __syncthreads();
         since_flush = 0;
     };
-    (void)red;
 
+    const double inf = __longlong_as_double(0x7ff0000000000000ll);
     for (unsigned item = first; item < last; ++item) {
         if (tid == 0) cur = decode_item(d, plan, item, count, split);
         __syncthreads();
@@ -281,7 +337,7 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
             if (cur_fe >= 0) flush(cur_fe);
             cur_fe = it.fe;
             const RadiusState &rs = d.rs[it.fe];
-            klo = rs.klo; width = rs.width; shift = rs.shift;
+            st.klo = rs.klo; st.width = rs.width; st.shift = rs.shift;
         }
         ++since_flush;
         const int f = it.fe / d.K;
@@ -293,44 +349,13 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
         __syncthreads();      // previous item's readers of sx/sy/sz are done
         for (int j = tid; j < jn; j += E2_PAIR_THREADS) { sx[j] = X[jb + j]; sy[j] = Y[jb + j]; sz[j] = Z[jb + j]; }
         const int gi0 = ib + tid, gi1 = ib + tid + E2_PAIR_THREADS;
-        double x0 = 0, y0 = 0, z0 = 0, x1 = 0, y1 = 0, z1 = 0;
+        // an i beyond the entity sits at x = +inf: its d2 is +inf, above every interval, and counts nowhere
+        double x0 = inf, y0 = 0, z0 = 0, x1 = inf, y1 = 0, z1 = 0;
         if (gi0 < n) { x0 = X[gi0]; y0 = Y[gi0]; z0 = Z[gi0]; }
         if (gi1 < n) { x1 = X[gi1]; y1 = Y[gi1]; z1 = Z[gi1]; }
         __syncthreads();
-        // pair (i, j) is taken when i < j; i beyond n is switched off by giving it the largest index
-        const int lim0 = (gi0 < n) ? gi0 : 0x7fffffff, lim1 = (gi1 < n) ? gi1 : 0x7fffffff;
-        for (int j = 0; j < jn; ++j) {
-            const double xj = sx[j], yj = sy[j], zj = sz[j];
-            const int gj = jb + j;
-            const u64 ka = d2key(dist2(x0, y0, z0, xj, yj, zj));
-            const u64 kb = d2key(dist2(x1, y1, z1, xj, yj, zj));
-            const u64 ta = ka - klo, tb = kb - klo;
-            if (!COLLECT) {
-                if (gj > lim0) {
-                    if (ta < width) cnt[(unsigned)(ta >> shift) * E2_PAIR_THREADS + slot] += 1;
-                    else if (ka < klo) ++below;
-                }
-                if (gj > lim1) {
-                    if (tb < width) cnt[(unsigned)(tb >> shift) * E2_PAIR_THREADS + slot] += 1;
-                    else if (kb < klo) ++below;
-                }
-            } else {
-                // candidates are appended with one global atomic per warp (the j loop is uniform across the CTA)
-                const bool ha = gj > lim0 && ta < width, hb = gj > lim1 && tb < width;
-                const unsigned ba = __ballot_sync(0xffffffffu, ha), bb = __ballot_sync(0xffffffffu, hb);
-                if (ba | bb) {
-                    const int lane = tid & 31;
-                    unsigned base = 0;
-                    if (lane == 0) base = atomicAdd(d.cand_n + it.fe, (unsigned)(__popc(ba) + __popc(bb)));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    const unsigned lt = (1u << lane) - 1u;
-                    if (ha) { const unsigned pos = base + __popc(ba & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)it.fe * E2_CAND_CAP + pos] = ka; }
-                    if (hb) { const unsigned pos = base + __popc(ba) + __popc(bb & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)it.fe * E2_CAND_CAP + pos] = kb; }
-                }
-                if (gj > lim0 && !(ta < width) && !(ka < klo) && ka < above_min) above_min = ka;
-                if (gj > lim1 && !(tb < width) && !(kb < klo) && kb < above_min) above_min = kb;
-            }
-        }
+        if (it.ti == it.tj) pair_loop<COLLECT, true>(d, it.fe, sx, sy, sz, jn, jb, gi0, gi1, x0, y0, z0, x1, y1, z1, cnt + slot, st);
+        else pair_loop<COLLECT, false>(d, it.fe, sx, sy, sz, jn, jb, gi0, gi1, x0, y0, z0, x1, y1, z1, cnt + slot, st);
     }
     if (cur_fe >= 0) flush(cur_fe);
 }
