@@ -472,20 +472,22 @@ __device__ bool cell_axis_medians(CellSmem &s, const Dev &d, const double *X, co
 struct CellState {
     unsigned char member[E2_CELL_MAX];
     unsigned ulist[E2_CELL_UMAX];
+    double udist[E2_CELL_UMAX];      // distance^2 of every open candidate to the member set of the first visit
     unsigned n_u;
     int seed;
 };
 
 // Point-level settlement of the nU candidate points against the member POINTS (exact float64 distances): a candidate whose
 // distance to a member is <= t_join becomes a member itself (virtual cell E2_CELL_JOIN); repeated until nothing changes,
-// so s.udist ends up measured against the final member set.
+// so s.udist ends up measured against the final member set.  Only the first round looks at the whole cloud: afterwards the
+// member set grows by the candidates that have just joined, and udist = min(udist, distance to those).  HAVE_UDIST: udist
+// already holds the distances to the current member set (the second visit of an entity, cell_filter_kernel<true>).
+template <bool HAVE_UDIST>
 __device__ __forceinline__ void cell_settle(CellSmem &s, const double *X, const double *Y, const double *Z, unsigned short *pcell,
                                             int n, unsigned nU, double t_join)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (;;) {
-        if (tid == 0) s.n_new = 0;
-        __syncthreads();
+    if (!HAVE_UDIST) {
         for (unsigned u = warp; u < nU; u += E2_CELL_WARPS) {
             if (s.joined[u]) continue;
             const unsigned p = s.ulist[u];
@@ -494,15 +496,34 @@ __device__ __forceinline__ void cell_settle(CellSmem &s, const double *X, const 
             for (int q = lane; q < n; q += 32)
                 if (s.member[pcell[q]]) best = fmin(best, dist2(x, y, z, X[q], Y[q], Z[q]));
             best = warp_min_d(best);
-            if (lane == 0) {
-                s.udist[u] = best;
-                if (best <= t_join) { s.joined[u] = 1; pcell[p] = (unsigned short)E2_CELL_JOIN; s.n_new = 1; }
-            }
+            if (lane == 0) s.udist[u] = best;
         }
+    }
+    unsigned short *fresh = s.front[0];                 // the candidates that joined in this round (the closure's lists are free)
+    for (;;) {
+        if (tid == 0) s.n_new = 0;
+        __syncthreads();
+        for (unsigned u = tid; u < nU; u += E2_CELL_THREADS)
+            if (!s.joined[u] && s.udist[u] <= t_join) {
+                s.joined[u] = 1;
+                pcell[s.ulist[u]] = (unsigned short)E2_CELL_JOIN;
+                fresh[atomicAdd(&s.n_new, 1u)] = (unsigned short)u;
+            }
         __syncthreads();
         const unsigned grew = s.n_new;
-        __syncthreads();
         if (!grew) break;
+        for (unsigned u = tid; u < nU; u += E2_CELL_THREADS) {
+            if (s.joined[u]) continue;
+            const unsigned p = s.ulist[u];
+            const double x = X[p], y = Y[p], z = Z[p];
+            double best = s.udist[u];
+            for (unsigned k = 0; k < grew; ++k) {
+                const unsigned q = s.ulist[fresh[k]];
+                best = fmin(best, dist2(x, y, z, X[q], Y[q], Z[q]));
+            }
+            s.udist[u] = best;
+        }
+        __syncthreads();
     }
 }
 
@@ -542,10 +563,10 @@ __device__ __forceinline__ void cell_filter_entity(const Dev &d, CellSmem &s, co
         const CellState &cs = d.cell_state[fe];
         for (int i = tid; i < E2_CELL_MAX; i += E2_CELL_THREADS) s.member[i] = cs.member[i];
         const unsigned nU = cs.n_u;
-        for (unsigned u = tid; u < nU; u += E2_CELL_THREADS) { const unsigned p = cs.ulist[u]; s.ulist[u] = p; s.joined[u] = pcell[p] == E2_CELL_JOIN; }
+        for (unsigned u = tid; u < nU; u += E2_CELL_THREADS) { const unsigned p = cs.ulist[u]; s.ulist[u] = p; s.joined[u] = pcell[p] == E2_CELL_JOIN; s.udist[u] = cs.udist[u]; }
         if (tid == 0) { s.seed = cs.seed; s.overflow = 0; s.amb = 0; s.t_lo = sq_threshold((double)(float)d.radius[fe]); }
         __syncthreads();
-        cell_settle(s, X, Y, Z, pcell, n, nU, s.t_lo);
+        cell_settle<true>(s, X, Y, Z, pcell, n, nU, s.t_lo);
     }
     if (!FINISH && filtered) {
         // ---- A: seed, mean absolute deviation, AABB ------------------------------------------------------------
@@ -804,7 +825,7 @@ __device__ __forceinline__ void cell_filter_entity(const Dev &d, CellSmem &s, co
             for (int u = tid; u < E2_CELL_UMAX; u += E2_CELL_THREADS) s.joined[u] = 0;
             if (tid == 0) s.member[E2_CELL_JOIN] = 1;            // virtual cell of the points that join here
             __syncthreads();
-            cell_settle(s, X, Y, Z, pcell, n, nU, t_lo);           // reachable at every radius >= r_lo
+            cell_settle<false>(s, X, Y, Z, pcell, n, nU, t_lo);    // reachable at every radius >= r_lo
             // the last round changed nothing: udist is measured against the final member set
             for (unsigned u = tid; u < nU; u += E2_CELL_THREADS)
                 if (!s.joined[u] && s.udist[u] <= t_hi) s.amb = 4;      // reachable at r_hi but not at r_lo
@@ -822,7 +843,7 @@ __device__ __forceinline__ void cell_filter_entity(const Dev &d, CellSmem &s, co
         if (resume) {
             CellState &cs = d.cell_state[fe];
             for (int i = tid; i < E2_CELL_MAX; i += E2_CELL_THREADS) cs.member[i] = s.member[i];
-            for (unsigned u = tid; u < s.n_cand; u += E2_CELL_THREADS) cs.ulist[u] = s.ulist[u];
+            for (unsigned u = tid; u < s.n_cand; u += E2_CELL_THREADS) { cs.ulist[u] = s.ulist[u]; cs.udist[u] = s.udist[u]; }
             if (tid == 0) { cs.n_u = s.n_cand; cs.seed = s.seed; }
         }
         if (tid == 0) {

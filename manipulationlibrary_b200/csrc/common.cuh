@@ -121,6 +121,10 @@ __device__ __forceinline__ void pdl_enter()
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
+// The two halves on their own: a kernel that is launched in plain stream order (e2sec_api.cu: launch_plain) still lets the
+// grid after it start its launch early, once its own work is done.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // BOUNDED radius mode and the cell table decided every entity of the batch: the kernels of the exact O(n^2) radius have
 // nothing to do (they are launched unconditionally -- the host never waits for the device inside a batch)

@@ -75,6 +75,7 @@ struct e2sec_ctx {
     int sf_cluster = 8;
     bool seg_cluster = false;      // E2SEC_SEG_MODE=cluster: the one-kernel cluster segmentation instead of the unit stream
     bool pdl = true;
+    bool pdl_once_off = false;  // the next launch_pdl launches in plain stream order (launch_plain)
     cudaError_t launch_err = cudaSuccess;
     bool force_two_pass = false;   // E2SEC_SEG_TWO_PASS=1: always take the two-pass segmentation (tests compare both)
 };
@@ -165,6 +166,16 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     { const char *e = getenv("E2SEC_PDL"); ctx->pdl = !(e && e[0] == '0'); }
     { const char *e = getenv("E2SEC_SF_CLUSTER"); int c = e ? atoi(e) : E2_SF_CLUSTER; ctx->sf_cluster = (c == 1 || c == 2 || c == 4 || c == 8) ? c : E2_SF_CLUSTER; }
     cudaFuncSetAttribute(cell_filter_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    // The exact path's kernels follow each other under programmatic launch: a pass's CTAs (72 KB each, three per SM) arrive
+    // while the small kernel before it is still resident, and an SM cannot change its shared-memory carve-out with CTAs on it
+    // -- with the default preference the pass ran with fewer CTAs per SM, 1.5x slower.  Same carve-out for the whole chain.
+    cudaFuncSetAttribute(cell_filter_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(radius_init_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(radius_select_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(radius_final_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(radius_plan_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(pair_pass_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
     ctx->bufs = {&ctx->pcd_stage, &ctx->pcd_frames, &ctx->pcd_status, &ctx->ltext_stage, &ctx->ltext_off, &ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->cell_state, &ctx->amb_list, &ctx->exact_ticket, &ctx->plan_split, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
@@ -500,10 +511,23 @@ static inline void launch_pdl(e2sec_ctx *ctx, void (*k)(P...), dim3 g, dim3 b, s
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = ctx->pdl ? 1 : 0;
+    cfg.numAttrs = (ctx->pdl && !ctx->pdl_once_off) ? 1 : 0;
+    ctx->pdl_once_off = false;
     const cudaError_t e = cudaLaunchKernelEx(&cfg, k, P(a)...);
     if (e != cudaSuccess && ctx->launch_err == cudaSuccess) ctx->launch_err = e;     // the first failing launch is the one reported
     ++ctx->launches;
+}
+
+// The same without the attribute, for the persistent kernels whose whole grid is one resident wave (pair_pass_kernel,
+// contact_work_kernel): launched early, their CTAs take their places while the kernel before them still holds part of the SMs,
+// and the pass then runs 1.45x slower than when it starts on an empty machine (measured: 36 vs 25 ms for the two passes of a
+// 200-frame batch of the bundled recording; 0.8 % of the step for contact_work_kernel).  A few microseconds of launch gap
+// are cheap against that.
+template <class... P, class... A>
+static inline void launch_plain(e2sec_ctx *ctx, void (*k)(P...), dim3 g, dim3 b, size_t smem, cudaStream_t st, A... a)
+{
+    ctx->pdl_once_off = true;
+    launch_pdl(ctx, k, g, b, smem, st, a...);
 }
 
 // every launch is checked; the pipeline functions report the first failure once they have queued their launches
@@ -539,12 +563,12 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
         const size_t smem = E2_PAIR_SMEM_HIST;
         launch_pdl(ctx, radius_init_kernel, dim3(small_grid), dim3(256), 0, st, d, plan, below_acc, min_above, single, grid);
         for (int round = 0; round < E2_MAX_REFINE; ++round) {
-            launch_pdl(ctx, pair_pass_kernel<false>, dim3(grid), dim3(E2_PAIR_THREADS), smem, st, d, plan, below_acc, min_above);
+            launch_plain(ctx, pair_pass_kernel<false>, dim3(grid), dim3(E2_PAIR_THREADS), smem, st, d, plan, below_acc, min_above);
             const bool last = round == E2_MAX_REFINE - 1;         // the plan that follows the last round is the collect pass's
             launch_pdl(ctx, radius_select_kernel, dim3(bounded ? std::min((FK + 7) / 8, ctx->sm_count) : (FK + 7) / 8), dim3(256), 0, st, d, plan, below_acc, single,
                        last ? 1 : 0, last ? ctx->sm_count * 8 : grid);
         }
-        launch_pdl(ctx, pair_pass_kernel<true>, dim3(ctx->sm_count * 8), dim3(E2_PAIR_THREADS), E2_PAIR_SMEM_COLLECT, st, d, plan, below_acc, min_above);
+        launch_plain(ctx, pair_pass_kernel<true>, dim3(ctx->sm_count * 8), dim3(E2_PAIR_THREADS), E2_PAIR_SMEM_COLLECT, st, d, plan, below_acc, min_above);
         launch_pdl(ctx, radius_final_kernel, dim3(small_grid), dim3(E2_SEL_THREADS), 0, st, d, min_above, single);
         // entities that only had a point inside the radius band: the cell closure is finished at the exact radius
         if (bounded)
@@ -563,7 +587,7 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
         const int n_idx = d.F * cp.slots;
         launch_pdl(ctx, contact_plan_kernel, dim3((n_idx + 255) / 256), dim3(256), 0, st, d, cp);
         launch_pdl(ctx, contact_scan_kernel, dim3(1), dim3(1024), 0, st, cp, n_idx);
-        launch_pdl(ctx, contact_work_kernel, dim3(ctx->sm_count * 4), dim3(E2_CT_THREADS), 0, st, d, cp);
+        launch_plain(ctx, contact_work_kernel, dim3(ctx->sm_count * 4), dim3(E2_CT_THREADS), 0, st, d, cp);
         launch_pdl(ctx, halo_save_kernel, dim3(64), dim3(256), 0, st, d);
         launch_pdl(ctx, halo_commit_kernel, dim3(1), dim3(1), 0, st, d);
     }

@@ -6,8 +6,8 @@
 // Keys are the bit patterns of d2 (non-negative doubles order like unsigned integers).
 //
 //   radius_init_kernel     per entity: pair count, the two middle ranks, an upper bound of d2 from the
-//                          AABB, first key interval: the cell table's band [rad_lo^2, rad_hi^2] when there is one
-//                          (BOUNDED mode), else [key(D2max * 2^-16), key(D2max)]
+//                          AABB, first key interval: two order statistics of a fixed sample of 16384 pairs around the
+//                          median, cut to the cell table's band [rad_lo^2, rad_hi^2] when there is one (BOUNDED mode)
 //   plan_scan              work list: one item = a slice of one 256 x 256 tile pair (ti <= tj) of an active entity.  Run
 //                          by the LAST CTA to finish of radius_init_kernel / radius_select_kernel (no launch of its own)
 //   pair_pass_kernel<0>    every pair of the item -> bin = (key - klo) >> shift, counted in thread-private
@@ -23,8 +23,11 @@
 #include "common.cuh"
 #include "select.cuh"
 
-#define E2_PAIR_THREADS 128     // 2 i-points per thread
-#define E2_FLUSH_ITEMS 100      // uint16 counters: <= 512 increments per thread per item
+#ifndef E2_PAIR_IPT
+#define E2_PAIR_IPT 2           // i-points per thread
+#endif
+#define E2_PAIR_THREADS (E2_TILE / E2_PAIR_IPT)
+#define E2_FLUSH_ITEMS (200 / E2_PAIR_IPT)      // uint16 counters: <= 256 * E2_PAIR_IPT increments per thread per item
 #define E2_PAIR_MAX_SPLIT 8     // a tile pair is cut into up to 8 slices of its j range when there are few of them
 
 struct PairPlan {
@@ -101,12 +104,29 @@ __device__ __forceinline__ bool exact_last_cta(const Dev &d)
     return last != 0;
 }
 
-// grid: any number of CTAs of 256 threads, striding over the list
-__global__ void __launch_bounds__(256) radius_init_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *min_above, u64 *single_count, int grid_hint)
+#define E2_SAMPLE_MAX 16384      // pairs sampled per entity to place the first interval (<= E2_CAND_CAP: they are parked in d.cand)
+
+__device__ __forceinline__ unsigned mix32(unsigned x)
+{
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+
+// grid: any number of CTAs of 256 threads, striding over the list.
+// Where the first histogram pass looks: a fixed pseudo-random sample of M pairs puts the median between two of its order
+// statistics, M / 2 -+ 2 sqrt(M) (4 sigma of the median's rank in the sample): a fraction 4 / sqrt(M) of all pairs (3 % at
+// M = 16384), so that one of the 128 .. 256 bins of that pass holds fewer than E2_CAND_CAP pairs up to 10^8 pairs per
+// entity -- the collect pass can follow at once.  In BOUNDED mode the interval is cut to the cell table's guaranteed band, and the band alone is used when it is
+// narrow enough for the entity's pair count.  The sample only chooses where to look: the ranks are counted exactly, and
+// radius_select_kernel reopens the interval on the side that is short should the guess ever miss.
+// Entities with at most E2_CAND_CAP pairs skip the histogram altogether.
+__global__ void __launch_bounds__(E2_SEL_THREADS) radius_init_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *min_above, u64 *single_count, int grid_hint)
 {
     pdl_enter();
     if (exact_path_idle(d)) return;
     __shared__ double red[6][8];
+    __shared__ SelectSmem sm;
+    __shared__ int mode;                   // 0: settled here, otherwise the sample size
     const int count = exact_count(d);
     for (int li = blockIdx.x; li < count; li += gridDim.x) {
         const int fe = exact_entity(d, li), f = fe / d.K;
@@ -137,6 +157,7 @@ __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, PairPlan plan, 
             if ((threadIdx.x & 31) == 0) { red[a][threadIdx.x >> 5] = lo[a]; red[3 + a][threadIdx.x >> 5] = hi[a]; }
         }
         __syncthreads();
+        const u64 P = (u64)n * (u64)(n - 1) / 2;
         if (threadIdx.x == 0) {
             double ext2 = 0.0;
             for (int a = 0; a < 3; ++a) {
@@ -144,11 +165,11 @@ __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, PairPlan plan, 
                 for (int w = 1; w < 8; ++w) { l = fmin(l, red[a][w]); h = fmax(h, red[3 + a][w]); }
                 ext2 += (h - l) * (h - l);
             }
-            u64 P = (u64)n * (u64)(n - 1) / 2;
             rs.k2 = P / 2;
             rs.k1 = (P & 1) ? rs.k2 : rs.k2 - 1;
             rs.n = n;
             rs.below = 0;
+            mode = 0;
             if (!(ext2 > 0.0)) {           // every point identical: all distances are 0
                 d.radius[fe] = 0.0;
                 rs.phase = 2;
@@ -156,10 +177,9 @@ __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, PairPlan plan, 
                 const double top = ext2 * 1.000001;  // d2 of any pair <= squared AABB diagonal (+ rounding slack)
                 const u64 ktop = d2key(top) + 1;
                 u64 khi = ktop;
-                u64 klo = d2key(top * (1.0 / 65536.0));
+                u64 klo = 0;                         // the sample below narrows it
                 if (d.radius_mode == E2SEC_RADIUS_BOUNDED) {
-                    // the cell table's bounds of the two middle distances (cells.cuh phase D; float32-rounded, hence the
-                    // slack).  Should they ever miss, radius_select_kernel reopens the interval on the side that is short.
+                    // the cell table's bounds of the two middle distances (cells.cuh phase D; float32-rounded, hence the slack)
                     const double rl = d.rad_lo[fe], rh = d.rad_hi[fe];
                     if (rl >= 0.0 && rh >= rl && rh < 1e150) {
                         const u64 bl = d2key(rl * rl * (1.0 - 1.0 / 1048576.0));
@@ -174,9 +194,47 @@ __global__ void __launch_bounds__(256) radius_init_kernel(Dev d, PairPlan plan, 
                 rs.width = khi - klo;
                 rs.shift = shift_for_width(rs.width);
                 rs.phase = 0;
+                if (P <= (u64)E2_CAND_CAP) {          // few pairs: collect them all, no histogram
+                    rs.klo = 0;
+                    rs.width = ktop;
+                    rs.phase = 1;
+                } else if (klo == 0 || P > 12000000ull) {
+                    // (a band holds ~30 % of the pairs: below 1.2e7 pairs one of its 256 bins fits the candidate buffer as it is)
+                    // sqrt(M) >= 4 P / (128 E2_CAND_CAP) would do (a pass uses 128 .. 256 of its bins), but a narrower
+                    // interval also means fewer candidates for the collect pass to append: the largest sample that fits
+                    // d.cand, except for small entities
+                    const int M = P > 2000000ull ? E2_SAMPLE_MAX : 4096;
+                    mode = M;
+                }
             }
         }
-        __syncthreads();                   // red[] is reused by the next entity of this CTA
+        __syncthreads();                   // red[] is reused by the next entity of this CTA; mode is set
+        if (mode) {
+            const int M = mode, half = (int)ceil(2.0 * sqrt((double)M));
+            u64 *smp = d.cand + (size_t)fe * E2_CAND_CAP;
+            for (int t = threadIdx.x; t < M; t += blockDim.x) {
+                const unsigned h1 = mix32((unsigned)t * 2u + 1u + (unsigned)fe * 0x9e3779b9u), h2 = mix32(h1 + 0x85ebca6bu + (unsigned)t);
+                const int i = (int)(h1 % (unsigned)n);
+                int j = (int)(h2 % (unsigned)(n - 1));
+                j += (j >= i);
+                smp[t] = d2key(dist2(x[i], y[i], z[i], x[j], y[j], z[j]));
+            }
+            __syncthreads();
+            u64 qlo, qhi, unused;
+            block_select2([&](int t) { return smp[t]; }, M, (u64)(M / 2 - half), (u64)(M / 2 - half), qlo, unused, sm);
+            __syncthreads();
+            block_select2([&](int t) { return smp[t]; }, M, (u64)(M / 2 + half), (u64)(M / 2 + half), qhi, unused, sm);
+            if (threadIdx.x == 0) {
+                const u64 klo = rs.klo, khi = rs.klo + rs.width;
+                const u64 nlo = qlo > klo ? qlo : klo, nhi = (qhi + 1 < khi) ? qhi + 1 : khi;
+                if (nlo < nhi) {
+                    rs.klo = nlo;
+                    rs.width = nhi - nlo;
+                    rs.shift = shift_for_width(rs.width);
+                }
+            }
+            __syncthreads();
+        }
     }
     if (exact_last_cta(d)) plan_scan(d, plan, 0, grid_hint);
 }
@@ -226,14 +284,15 @@ struct PairLoopState {
     u64 above_ta;       // COLLECT: smallest (key - klo) >= width seen so far
 };
 
-// All pairs (i, j) of one item for the two i-points of this thread, j over the shared-memory slice.  No data-dependent
-// branch: a pair outside the interval counts into the row "below" or "rest" (keys under klo wrap around to >= 2^63), a
-// pair that is not one (DIAG: j <= i on the diagonal tile; i beyond the entity: the caller gives it x = +inf, a key above
-// every interval) into "rest".  The FP64 pipe -- 8 operations per pair -- is the floor; everything else has to fit under it.
+// All pairs (i, j) of one item for the E2_PAIR_IPT i-points of this thread, j over the shared-memory slice.  No
+// data-dependent branch: a pair outside the interval counts into the row "below" or "rest" (keys under klo wrap around to
+// >= 2^63), a pair that is not one (DIAG: j <= i on the diagonal tile; i beyond the entity: the caller gives it x = +inf, a
+// key above every interval) into "rest".  The FP64 pipe -- 8 operations per pair -- is the floor; everything else has to
+// fit under it.
 template <bool COLLECT, bool DIAG>
 __device__ __forceinline__ void pair_loop(const Dev &d, int fe, const double *sx, const double *sy, const double *sz, int jn, int jb,
-                                          int gi0, int gi1, double x0, double y0, double z0, double x1, double y1, double z1,
-                                          unsigned short *cnt_slot, PairLoopState &st)
+                                          const int (&gi)[E2_PAIR_IPT], const double (&xi)[E2_PAIR_IPT], const double (&yi)[E2_PAIR_IPT],
+                                          const double (&zi)[E2_PAIR_IPT], unsigned short *cnt_slot, PairLoopState &st)
 {
     const u64 klo = st.klo, width = st.width;
     const int shift = st.shift;
@@ -241,33 +300,49 @@ __device__ __forceinline__ void pair_loop(const Dev &d, int fe, const double *sx
     for (int j = 0; j < jn; ++j) {
         const double xj = sx[j], yj = sy[j], zj = sz[j];
         const int gj = jb + j;
-        const u64 ka = d2key(dist2(x0, y0, z0, xj, yj, zj));
-        const u64 kb = d2key(dist2(x1, y1, z1, xj, yj, zj));
-        const u64 ta = ka - klo, tb = kb - klo;
-        bool ha = ta < width, hb = tb < width;
+        u64 k[E2_PAIR_IPT], t[E2_PAIR_IPT];
+        bool h[E2_PAIR_IPT];
+#pragma unroll
+        for (int q = 0; q < E2_PAIR_IPT; ++q) {
+            k[q] = d2key(dist2(xi[q], yi[q], zi[q], xj, yj, zj));
+            t[q] = k[q] - klo;
+            h[q] = t[q] < width;
+        }
         if (!COLLECT) {
-            unsigned ra = ha ? (unsigned)(ta >> shift) : (unsigned)(E2_NBINS + 1) - (unsigned)(ta >> 63);
-            unsigned rb = hb ? (unsigned)(tb >> shift) : (unsigned)(E2_NBINS + 1) - (unsigned)(tb >> 63);
-            if (DIAG) { ra = (gj > gi0) ? ra : (unsigned)(E2_NBINS + 1); rb = (gj > gi1) ? rb : (unsigned)(E2_NBINS + 1); }
-            cnt_slot[ra * E2_PAIR_THREADS] += 1;
-            cnt_slot[rb * E2_PAIR_THREADS] += 1;
+#pragma unroll
+            for (int q = 0; q < E2_PAIR_IPT; ++q) {
+                unsigned r = h[q] ? (unsigned)(t[q] >> shift) : (unsigned)(E2_NBINS + 1) - (unsigned)(t[q] >> 63);
+                if (DIAG) r = (gj > gi[q]) ? r : (unsigned)(E2_NBINS + 1);
+                cnt_slot[r * E2_PAIR_THREADS] += 1;
+            }
         } else {
-            if (DIAG) { ha = ha && gj > gi0; hb = hb && gj > gi1; }
+            unsigned bal[E2_PAIR_IPT], any = 0, tot = 0;
+#pragma unroll
+            for (int q = 0; q < E2_PAIR_IPT; ++q) {
+                if (DIAG) h[q] = h[q] && gj > gi[q];
+                bal[q] = __ballot_sync(0xffffffffu, h[q]);
+                any |= bal[q];
+                tot += __popc(bal[q]);
+            }
             // candidates are appended with one global atomic per warp (the j loop is uniform across the CTA)
-            const unsigned ba = __ballot_sync(0xffffffffu, ha), bb = __ballot_sync(0xffffffffu, hb);
-            if (ba | bb) {
+            if (any) {
                 const int lane = threadIdx.x & 31;
                 unsigned base = 0;
-                if (lane == 0) base = atomicAdd(d.cand_n + fe, (unsigned)(__popc(ba) + __popc(bb)));
+                if (lane == 0) base = atomicAdd(d.cand_n + fe, tot);
                 base = __shfl_sync(0xffffffffu, base, 0);
                 const unsigned lt = (1u << lane) - 1u;
-                if (ha) { const unsigned pos = base + __popc(ba & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)fe * E2_CAND_CAP + pos] = ka; }
-                if (hb) { const unsigned pos = base + __popc(ba) + __popc(bb & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)fe * E2_CAND_CAP + pos] = kb; }
+#pragma unroll
+                for (int q = 0; q < E2_PAIR_IPT; ++q) {
+                    if (h[q]) { const unsigned pos = base + __popc(bal[q] & lt); if (pos < E2_CAND_CAP) d.cand[(size_t)fe * E2_CAND_CAP + pos] = k[q]; }
+                    base += __popc(bal[q]);
+                }
             }
-            u64 ca = ha ? ~0ull : ta, cb = hb ? ~0ull : tb;
-            if (DIAG) { ca = (gj > gi0) ? ca : ~0ull; cb = (gj > gi1) ? cb : ~0ull; }
-            const u64 c = ca < cb ? ca : cb;
-            st.above_ta = c < st.above_ta ? c : st.above_ta;
+#pragma unroll
+            for (int q = 0; q < E2_PAIR_IPT; ++q) {
+                u64 c = h[q] ? ~0ull : t[q];
+                if (DIAG) c = (gj > gi[q]) ? c : ~0ull;
+                st.above_ta = c < st.above_ta ? c : st.above_ta;
+            }
         }
     }
 }
@@ -276,7 +351,7 @@ __device__ __forceinline__ void pair_loop(const Dev &d, int fe, const double *sx
 template <bool COLLECT>
 __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *min_above)
 {
-    pdl_enter();
+    pdl_wait();                                    // launched in plain stream order (launch_plain); the next grid is released at the end
     if (exact_path_idle(d)) return;
     unsigned short *cnt = reinterpret_cast<unsigned short *>(pair_smem);
     double *sx = reinterpret_cast<double *>(pair_smem + (COLLECT ? 0 : E2_PAIR_CNT_BYTES));
@@ -284,8 +359,8 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
     __shared__ PairItem cur;
     const int tid = threadIdx.x;
     // counter slot of this thread inside a row: lanes of one warp hit 32 distinct 4-byte words (banks);
-    // threads tid and tid + 64 share a word but own different halves of it
-    const int slot = ((tid & 63) << 1) | (tid >> 6);
+    // threads tid and tid + E2_PAIR_THREADS / 2 share a word but own different halves of it
+    const int slot = ((tid % (E2_PAIR_THREADS / 2)) << 1) | (tid / (E2_PAIR_THREADS / 2));
     const unsigned total = *plan.total;
     if (total == 0) return;
     const int count = exact_count(d);
@@ -348,15 +423,20 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
         const int jn = min(jw, n - jb);              // <= 0: the slice lies beyond the entity's last point
         __syncthreads();      // previous item's readers of sx/sy/sz are done
         for (int j = tid; j < jn; j += E2_PAIR_THREADS) { sx[j] = X[jb + j]; sy[j] = Y[jb + j]; sz[j] = Z[jb + j]; }
-        const int gi0 = ib + tid, gi1 = ib + tid + E2_PAIR_THREADS;
         // an i beyond the entity sits at x = +inf: its d2 is +inf, above every interval, and counts nowhere
-        double x0 = inf, y0 = 0, z0 = 0, x1 = inf, y1 = 0, z1 = 0;
-        if (gi0 < n) { x0 = X[gi0]; y0 = Y[gi0]; z0 = Z[gi0]; }
-        if (gi1 < n) { x1 = X[gi1]; y1 = Y[gi1]; z1 = Z[gi1]; }
+        int gi[E2_PAIR_IPT];
+        double xi[E2_PAIR_IPT], yi[E2_PAIR_IPT], zi[E2_PAIR_IPT];
+#pragma unroll
+        for (int q = 0; q < E2_PAIR_IPT; ++q) {
+            gi[q] = ib + tid + q * E2_PAIR_THREADS;
+            xi[q] = inf; yi[q] = 0; zi[q] = 0;
+            if (gi[q] < n) { xi[q] = X[gi[q]]; yi[q] = Y[gi[q]]; zi[q] = Z[gi[q]]; }
+        }
         __syncthreads();
-        if (it.ti == it.tj) pair_loop<COLLECT, true>(d, it.fe, sx, sy, sz, jn, jb, gi0, gi1, x0, y0, z0, x1, y1, z1, cnt + slot, st);
-        else pair_loop<COLLECT, false>(d, it.fe, sx, sy, sz, jn, jb, gi0, gi1, x0, y0, z0, x1, y1, z1, cnt + slot, st);
+        if (it.ti == it.tj) pair_loop<COLLECT, true>(d, it.fe, sx, sy, sz, jn, jb, gi, xi, yi, zi, cnt + slot, st);
+        else pair_loop<COLLECT, false>(d, it.fe, sx, sy, sz, jn, jb, gi, xi, yi, zi, cnt + slot, st);
     }
+    pdl_release();
     if (cur_fe >= 0) flush(cur_fe);
 }
 
