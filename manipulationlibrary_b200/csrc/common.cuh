@@ -100,6 +100,7 @@ struct Dev {
     int *amb_count;                   // number of such entities in the batch (reset by halo_commit_kernel)
     int *amb_list;                    // F x K       their fe, in the order they turned up: what the exact path walks
     unsigned *exact_ticket;           // CTAs of an exact-path kernel that are done (the last one plans the next pass)
+    int test_exact_start;             // tests only (E2SEC_TEST_EXACT_START): 1 / 2 = start the selection under / above the median
     // stats + pairs
     double *aabb;                     // F x K x 6
     double *mean;                     // F x K x 3

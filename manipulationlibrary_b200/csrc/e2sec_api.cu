@@ -177,6 +177,7 @@ extern "C" int e2sec_create(int device, e2sec_ctx **out)
     cudaFuncSetAttribute(pair_pass_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     cudaFuncSetAttribute(pair_pass_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     memset(&ctx->d, 0, sizeof(Dev));
+    { const char *e = getenv("E2SEC_TEST_EXACT_START"); ctx->d.test_exact_start = e ? atoi(e) : 0; }     // radius.cuh: forces the reopening paths
     ctx->bufs = {&ctx->pcd_stage, &ctx->pcd_frames, &ctx->pcd_status, &ctx->ltext_stage, &ctx->ltext_off, &ctx->lab8_stage, &ctx->gsub, &ctx->amb_count, &ctx->cell_state, &ctx->amb_list, &ctx->exact_ticket, &ctx->plan_split, &ctx->xyz_stage, &ctx->lab_stage, &ctx->rowmap, &ctx->colmap, &ctx->lut, &ctx->frame_ids, &ctx->seg_cnt,
                  &ctx->ent_raw, &ctx->ent_off, &ctx->flags, &ctx->px, &ctx->py, &ctx->pz, &ctx->pidx, &ctx->med,
                  &ctx->radius, &ctx->rs, &ctx->hist, &ctx->cand, &ctx->cand_n, &ctx->seed_pos, &ctx->member,

@@ -232,6 +232,12 @@ __global__ void __launch_bounds__(E2_SEL_THREADS) radius_init_kernel(Dev d, Pair
                     rs.width = nhi - nlo;
                     rs.shift = shift_for_width(rs.width);
                 }
+                if (d.test_exact_start) {          // tests: a first interval that misses the median on purpose
+                    const double top = key2d(rs.ktop - 1);
+                    rs.klo = d.test_exact_start == 1 ? 0 : d2key(top * 0.9999);
+                    rs.width = d.test_exact_start == 1 ? d2key(top * 1e-12) + 1 : rs.ktop - rs.klo;
+                    rs.shift = shift_for_width(rs.width);
+                }
             }
             __syncthreads();
         }

@@ -119,6 +119,60 @@ def test_pairwise_median_degenerate(engine):
     assert engine.pairwise_median(grid) == eo.pairwise_median(grid)      # massive ties
 
 
+def _median_cases():
+    rng = np.random.default_rng(4242)
+    blob = lambda n, s=0.05: rng.normal(0.0, s, (n, 3)) + [0.3, -0.1, 1.2]
+    two = np.concatenate([blob(1500, 0.01), blob(1500, 0.01) + [2.0, 0.0, 0.0]])            # the middle ranks sit at the jump between
+    two_odd = two[:-1]                                                                    # within- and between-cluster distances
+    outlier = np.concatenate([blob(3000, 0.002), [[40.0, -30.0, 25.0]]])                   # box diagonal >> median
+    grid = np.stack(np.meshgrid(np.arange(60.0), np.arange(60.0), [0.0], indexing="ij"), -1).reshape(-1, 3) * 0.004   # one key holds
+    line = np.column_stack([np.arange(2200.0) * 1e-3, np.zeros(2200), np.zeros(2200)])     # far more pairs than the candidate buffer
+    return {"181 (all pairs fit the candidate buffer)": blob(181), "182 (one more than fits)": blob(182), "6000": blob(6000),
+            "two clusters": two, "two clusters, odd pair count": two_odd, "outlier": outlier, "grid ties": grid, "line ties": line}
+
+
+@pytest.mark.parametrize("name", list(_median_cases()))
+def test_pairwise_median_sampled_interval(engine, name):
+    """radius.cuh places the first histogram interval from a sample of pairs (and skips the histogram for small entities): the
+    result stays the exact np.median(pdist()) whatever the distance distribution looks like."""
+    pts = np.ascontiguousarray(_median_cases()[name])
+    assert engine.pairwise_median(pts) == eo.pairwise_median(pts)
+
+
+@pytest.mark.parametrize("start", [1, 2])
+def test_pairwise_median_reopens_a_missed_interval(start, monkeypatch):
+    """The sample only chooses where the first pass looks.  E2SEC_TEST_EXACT_START makes radius_init_kernel start under (1) /
+    above (2) the median on purpose: radius_select_kernel has to reopen the interval upwards / downwards and the result is
+    still exact -- through the operator and through a whole batch in exact radius mode."""
+    from manipulationlibrary_b200 import _native as nat
+    from manipulationlibrary_b200.engine import Engine
+    from manipulationlibrary_b200.synthetic import SyntheticStream
+    monkeypatch.setenv("E2SEC_TEST_EXACT_START", str(start))
+    eng = Engine(0)
+    monkeypatch.delenv("E2SEC_TEST_EXACT_START")
+    plain = Engine(0)
+    try:
+        rng = np.random.default_rng(77 + start)
+        for n in (300, 2500):
+            pts = _cloud(rng, n)
+            assert eng.pairwise_median(pts) == eo.pairwise_median(pts)
+        s = SyntheticStream(width=320, height=240, n_objects=4, config=97, cycle=24)
+        ids = np.arange(4, 10, dtype=np.int32)
+        xyz, lab = s.fetch(ids)
+        rec = []
+        for e in (eng, plain):
+            p, keep = nat.make_params(**s.params(radius_mode="exact"))
+            e.configure(p, len(ids), s.N, keep)
+            rec.append(e.process_batch(xyz, lab, ids))
+        assert np.array_equal(rec[0], rec[1], equal_nan=True)
+        K = eng.K
+        radius = rec[0][:, nat.REC_HEADER + 3: nat.REC_HEADER + nat.REC_ENTITY * K: nat.REC_ENTITY]
+        assert np.isfinite(radius).sum() >= 4 * len(ids), "the batch should have gone through the exact selection"
+    finally:
+        eng.close()
+        plain.close()
+
+
 @pytest.mark.parametrize("n", [5, 64, 300, 1500])
 def test_region_filter_closure(engine, n):
     rng = np.random.default_rng(200 + n)
