@@ -1516,6 +1516,17 @@ extern "C" int e2sec_debug_cell_profile(unsigned long long out[16], int reset)
 }
 #endif
 
+#ifdef E2_LZ_PROFILE
+// debugging aid (not in e2sec.h): clock ticks per stage of lzf_decode_kernel summed over warps; reset != 0 clears them
+extern "C" int e2sec_debug_lzf_profile(unsigned long long out[16], int reset)
+{
+    cudaDeviceSynchronize();
+    if (out && cudaMemcpyFromSymbol(out, g_lz_prof, sizeof(unsigned long long) * 16) != cudaSuccess) return E2SEC_ERR_CUDA;
+    if (reset) { unsigned long long z[16] = {0}; if (cudaMemcpyToSymbol(g_lz_prof, z, sizeof(z)) != cudaSuccess) return E2SEC_ERR_CUDA; }
+    return E2SEC_OK;
+}
+#endif
+
 // ---- frame-0 setup geometry (frame0.cuh) ---------------------------------------------------------------------------------
 // small scratch device buffers of the operators below
 struct F0Buf {
