@@ -33,6 +33,7 @@ from .engine import Engine, Resolver, esec_to_e2sec_native, rec_entity
 
 IMAGE_SHAPE = (480, 640)            # :1390, :1433
 BATCH_FRAMES = 25                   # frames per GPU batch (E2SEC_BATCH_FRAMES overrides)
+CONTEXTS_PER_GPU = 3                # engines per GPU that take batches in turn (E2SEC_CONTEXTS overrides)
 READ_THREADS = 4                    # file decode runs ahead of the GPUs on this many threads
 
 final_columns = []
@@ -141,11 +142,14 @@ def _start_sequence(label0, ground_label, hand_label, support_hand, replace, old
         for e in _state["engines"]:
             e.close()
         _state["resolver"].close()
-    # every visible GPU takes batches of the sequence in turn (E2SEC_DEVICES limits how many); _process, frame by frame, uses one
-    n_dev = max(1, min(int(nat.lib.e2sec_device_count()), int(os.environ.get("E2SEC_DEVICES", "64")), 1 if icp else n_devices))
+    # every visible GPU takes batches of the sequence in turn (E2SEC_DEVICES limits how many), each through CONTEXTS_PER_GPU
+    # engines (E2SEC_CONTEXTS): a compressed cloud is decoded by one warp, a batch's decode has a fixed latency, and only
+    # other batches in flight on the same GPU hide it.  _process, frame by frame, and model tracking use one engine.
+    n_gpu = max(1, min(int(nat.lib.e2sec_device_count()), int(os.environ.get("E2SEC_DEVICES", "64")), 1 if icp else n_devices))
+    per_gpu = 1 if (icp or n_devices == 1) else max(1, int(os.environ.get("E2SEC_CONTEXTS", CONTEXTS_PER_GPU)))
     engines = []
-    for dev in range(n_dev):
-        eng = Engine(dev)
+    for i in range(n_gpu * per_gpu):
+        eng = Engine(i % n_gpu)
         eng.configure(p, max_frames + 1, IMAGE_SHAPE[0] * IMAGE_SHAPE[1], keep)      # + the halo frame in front of a batch
         engines.append(eng)
     _state = dict(engine=engines[0], engines=engines, resolver=Resolver(p, keep), params=p, keep=keep, K=len(tul), records={},
