@@ -734,6 +734,7 @@ static int process_batch_impl(e2sec_ctx *ctx, const float *xyz, const void *labe
         else launch_pdl(ctx, seg_stream_kernel<false>, dim3(ctas), dim3(E2_SS_THREADS), sizeof(SegStreamSmem), st, du, next);
         cudaEventRecord(ctx->ev[9], st);
         ctx->ev_stream = true;
+        launch_pdl(ctx, seg_prefix_kernel, dim3(n_frames), dim3(256), 0, st, du);
         launch_pdl(ctx, seg_emit_kernel, dim3((du.S + E2_SS_WARPS - 1) / E2_SS_WARPS, n_frames), dim3(E2_SS_THREADS), 0, st, du, next);
     } else if (fused) {
         const int tpf = (N + E2_SF_TILE - 1) / E2_SF_TILE;

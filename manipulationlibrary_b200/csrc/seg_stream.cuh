@@ -9,8 +9,9 @@
 //                       / entity; stays in L2) and leaves the unit's per-entity counts in seg_cnt[frame][unit][entity].
 //                       Units are small and handed out dynamically, so object-heavy image rows do not stall anybody
 //                       (the cluster kernel of seg_fused.cuh spends 38 % of its stall samples at barriers).
-//   seg_emit_kernel     one warp per unit (the CTA first sums the frame's small count table: entity totals, offsets
-//                       :1456-1472, and the prefix of its own units): re-reads the unit's list (13 % of the input on the 640x480 stream), ranks the
+//   seg_prefix_kernel   one CTA per frame: the small count table becomes the exclusive prefix over the units; entity totals
+//                       and offsets (:1456-1472).
+//   seg_emit_kernel     one warp per unit: re-reads the unit's list (13 % of the input on the 640x480 stream), ranks the
 //                       points per entity (stable) from the unit's prefix and writes `translation` then `roll` applied in
 //                       float64 (:1482-1485) as SoA + raster indices.
 // Same results as seg_fused.cuh and as the two-pass kernels of seg.cuh (tests compare all three bit for bit).
@@ -182,66 +183,55 @@ __global__ void __launch_bounds__(E2_SS_THREADS, E2_SS_CTAS) seg_stream_kernel(D
     }
 }
 
-// grid (ceil(S / E2_SS_WARPS), F): one warp per unit.  Every CTA first sums the frame's count table itself (S x K counters,
-// a few kB out of L2: thread (g, e) walks the units g, g + 2, ... of entity e with 8 loads in flight) -- entity totals,
-// offsets (:1456-1472; index 0 and the ground are counted, never stored, :1520) and the prefix of its own four units --
-// which is cheaper than a separate scan kernel between the two.
-__global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned *next)
+// grid F, 256 threads: the frame's count table (S units x K entities) becomes, in place, the exclusive prefix over the
+// units -- where every unit's points of an entity start inside the entity -- and the totals give the entity sizes and
+// offsets (:1456-1472; index 0 and the ground are counted, never stored, :1520).  One warp per entity, 32 units per step.
+__global__ void __launch_bounds__(256) seg_prefix_kernel(Dev d)
 {
     pdl_enter();
-    __shared__ unsigned wc[E2_SS_WARPS][E2SEC_MAX_ENTITIES];
-    __shared__ unsigned part[2][E2_SS_WARPS + 1][E2SEC_MAX_ENTITIES];
-    __shared__ int ent_off[E2SEC_MAX_ENTITIES];
-    static_assert(E2_SS_THREADS == 2 * E2SEC_MAX_ENTITIES, "two thread groups of one thread per entity");
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int f = blockIdx.y, u0 = blockIdx.x * E2_SS_WARPS, u = u0 + warp, S = d.S, K = d.K;
-    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *next = 0;      // the counter of the next batch's stream kernel
-    // a CTA whose units hold no stored point has nothing to place (the first CTA of a frame still publishes the totals)
-    unsigned mlen = 0;
-    if (u < S) mlen = d.seg_len[(size_t)f * S + u];
-    if (!__syncthreads_or(mlen != 0) && blockIdx.x != 0) return;
-    {
-        const int e = threadIdx.x % E2SEC_MAX_ENTITIES, g = threadIdx.x / E2SEC_MAX_ENTITIES;
-        unsigned tot = 0, pre = 0;
-        if (e < K) {
-            const unsigned *c = d.seg_cnt + (size_t)f * S * K + e;
-            for (int s0 = g; s0 < S; s0 += 16) {
-                unsigned v[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = (s0 + 2 * j < S) ? c[(size_t)(s0 + 2 * j) * K] : 0u;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    tot += v[j];
-                    pre += (s0 + 2 * j < u0) ? v[j] : 0u;
-                }
-            }
+    __shared__ unsigned total[E2SEC_MAX_ENTITIES];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, f = blockIdx.x, S = d.S, K = d.K;
+    unsigned *c = d.seg_cnt + (size_t)f * S * K;
+    for (int e = warp; e < K; e += 8) {
+        unsigned carry = 0;
+        for (int u0 = 0; u0 < S; u0 += 32) {
+            const int u = u0 + lane;
+            const unsigned v = u < S ? c[(size_t)u * K + e] : 0u;
+            unsigned incl = v;
+            for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+            if (u < S) c[(size_t)u * K + e] = carry + incl - v;
+            carry += __shfl_sync(0xffffffffu, incl, 31);
         }
-        part[g][0][e] = pre;                                   // stored points of entity e in the units before this CTA's
-        part[g][E2_SS_WARPS][e] = tot;
+        if (lane == 0) total[e] = carry;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
         int off = 0;
         for (int k = 0; k < K; ++k) {
             const bool stored = (k != 0 && k != d.ground_idx);
-            const int tk = (int)(part[0][E2_SS_WARPS][k] + part[1][E2_SS_WARPS][k]);
-            ent_off[k] = stored ? off : -1;
-            if (blockIdx.x == 0) { d.ent_raw[f * K + k] = tk; d.ent_off[f * K + k] = stored ? off : -1; }
-            if (stored) off += tk;
+            d.ent_raw[f * K + k] = (int)total[k];
+            d.ent_off[f * K + k] = stored ? off : -1;
+            if (stored) off += (int)total[k];
         }
-        if (blockIdx.x == 0) {
-            d.frame_used[f] = off < d.cap ? off : d.cap;
-            if (off > d.cap) atomicExch(d.error, E2SEC_ERR_CAPACITY);
-        }
+        d.frame_used[f] = off < d.cap ? off : d.cap;
+        if (off > d.cap) atomicExch(d.error, E2SEC_ERR_CAPACITY);
     }
-    __syncthreads();
-    const unsigned M = mlen;
-    if (M == 0) return;
+}
+
+// grid (ceil(S / E2_SS_WARPS), F): one warp per unit (after seg_prefix_kernel): re-reads the unit's list, ranks the points
+// per entity (stable) from the unit's first positions and writes the transformed SoA.
+__global__ void __launch_bounds__(E2_SS_THREADS) seg_emit_kernel(Dev d, unsigned *next)
+{
+    pdl_enter();
+    __shared__ unsigned wc[E2_SS_WARPS][E2SEC_MAX_ENTITIES];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int f = blockIdx.y, u = blockIdx.x * E2_SS_WARPS + warp, S = d.S, K = d.K;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *next = 0;      // the counter of the next batch's stream kernel
+    const unsigned M = u < S ? d.seg_len[(size_t)f * S + u] : 0u;
+    if (M == 0) return;                                          // a unit without stored points has nothing to place
     for (int e = lane; e < K; e += 32) {
-        const int off = ent_off[e];
-        unsigned first = (unsigned)off + part[0][0][e] + part[1][0][e];
-        for (int w = 0; w < warp; ++w) first += d.seg_cnt[((size_t)f * S + u0 + w) * K + e];    // the CTA's earlier units
-        wc[warp][e] = off < 0 ? 0xffffffffu : first;              // first output position of the unit, per entity
+        const int off = d.ent_off[f * K + e];
+        wc[warp][e] = off < 0 ? 0xffffffffu : (unsigned)off + d.seg_cnt[((size_t)f * S + u) * K + e];   // first output position of the unit, per entity
     }
     __syncwarp();
     const uint4 *list = d.seg_list + (size_t)f * d.N + (size_t)u * E2_SS_UNIT;
