@@ -273,6 +273,7 @@ def run_b200(args):
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_near_gpu(torch, local)
     saved_stdout = None
     if world > 1:
         # NCCL prints its version banner on stdout when the communicator comes up: keep stdout for the one JSON line
@@ -554,7 +555,8 @@ def run_b200(args):
                "h2d_bytes_per_step": h2d_frames * N * (13 if lab8 else BYTES_PER_POINT),
                "d2h_bytes_per_step": h2d_frames * rec_w * 8, "host_labels": "uint8" if lab8 else "int32",
                "blocks": len(eruns), "best": frames / (min(r[1] for r in eruns) * 1e-3),
-               "timing": "wall clock around the C-ABI calls of a block (median block), pinned host buffers, records back to the host"}
+               "timing": "wall clock around the C-ABI calls of a block (median block), pinned host buffers, records back to the host",
+               "host_numa": numa}      # rank 0's binding (bind_near_gpu): the pinned pools sit on the GPU's own NUMA node
 
     if rank == 0:
         peaks = {}
@@ -618,6 +620,32 @@ def run_b200(args):
         e.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def bind_near_gpu(torch, local):
+    """Keep this rank on the cores of the NUMA node its GPU hangs off, before the pinned host pools are allocated: the
+    pages of a pinned buffer land on the node of the thread that allocates them, and with eight ranks feeding eight PCIe
+    links at once a pool on the far socket sends every byte over the inter-socket link first (the e2e figure at 8 GPUs).
+    -> {"node": n, "cpus": count} or None when the box does not say (no sysfs entry, one node, or a cpuset without those cores)."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/numa_node" % bdf) as fh:
+            node = int(fh.read())
+        if node < 0:
+            return None
+        cpus = set()
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as fh:
+            for part in fh.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        mine = os.sched_getaffinity(0) & cpus
+        if not mine:
+            return None
+        os.sched_setaffinity(0, mine)
+        return {"node": node, "cpus": len(mine), "gpu": bdf}
+    except Exception:
+        return None
 
 
 def main():
