@@ -495,7 +495,7 @@ __device__ __forceinline__ void cell_settle(CellSmem &s, const double *X, const 
             double best = 1e300;
             for (int q = lane; q < n; q += 32)
                 if (s.member[pcell[q]]) best = fmin(best, dist2(x, y, z, X[q], Y[q], Z[q]));
-            best = warp_min_d(best);
+            best = warp_min_nonneg_d(best);
             if (lane == 0) s.udist[u] = best;
         }
     }

@@ -190,6 +190,16 @@ __device__ __forceinline__ double warp_min_d(double v)
     for (int o = 16; o; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
+// the same for values that are never negative (squared distances): their bit patterns order like unsigned integers, so
+// the minimum is two 32-bit warp reductions (high words, then the low words of the lanes that hold the smallest high word)
+// instead of five 64-bit shuffle + compare steps
+__device__ __forceinline__ double warp_min_nonneg_d(double v)
+{
+    const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+    const unsigned mhi = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+    return __hiloint2double((int)mhi, (int)mlo);
+}
 __device__ __forceinline__ double warp_max_d(double v)
 {
     for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));

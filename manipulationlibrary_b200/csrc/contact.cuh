@@ -200,7 +200,7 @@ __device__ __forceinline__ void contact_sweep(const ContactSmem &s, unsigned mB,
 #pragma unroll
             for (int k = 0; k < NK; ++k)
                 if (d32[k] <= guard) best = fmin(best, dist2(ax[k], ay[k], az[k], s.dx[j], s.dy[j], s.dz[j]));
-            best = warp_min_d(best);
+            best = warp_min_nonneg_d(best);
             guard = contact_guard(best, c0);
         }
     }
@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(E2_CT_THREADS, 3) contact_work_kernel(Dev d, C
             default: contact_sweep<4>(s, mB, 0u, 1u, rx, ry, rz, ax, ay, az, best, guard, c0); break;
             }
             // share the minimum: every thread continues with the block's best, which tightens guard and the B filter
-            const double wb = warp_min_d(best);
+            const double wb = warp_min_nonneg_d(best);
             if (lane == 0) s.red[0][warp] = wb;
             __syncthreads();
             best = s.red[0][0];

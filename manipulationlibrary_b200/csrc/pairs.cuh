@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(E2_PD_THREADS) pair_distance_kernel(Dev d)
         }
         __syncthreads();
     }
-    best = warp_min_d(best);
+    best = warp_min_nonneg_d(best);
     if ((tid & 31) == 0) red[tid >> 5] = best;
     __syncthreads();
     if (tid == 0) {
