@@ -158,7 +158,6 @@ __global__ void __launch_bounds__(32) lzf_decode_kernel(const unsigned char *blo
         const unsigned produced = __reduce_min_sync(0xffffffffu, drop != 0xffffffffu ? at0 : total_out);
         const unsigned ntok = first_drop_t != 0xffffffffu ? first_drop_t : total_tok;
         ip += (first_drop != 0xffffffffu) ? first_drop : next_window;
-        if (lane == 0) tok_r[ntok] = (unsigned short)produced;             // (8192 fits)
         LZ_TICK(3);
         // ---- the token of every output byte: token starts are marked in src ------------------------------------------------------
         for (unsigned i = lane; i < (produced + 7) / 8; i += 32) reinterpret_cast<uint4 *>(src)[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
