@@ -499,7 +499,7 @@ static int upload_maps(e2sec_ctx *ctx, int lw, int lh, int width, int height)
 
 // Kernels of the per-batch pipeline are launched with programmatic stream serialization: every one of them starts with
 // griddepcontrol.wait (common.cuh: pdl_enter), so the next grid's launch latency and prologue hide behind the tail of the
-// previous one instead of adding a gap per launch (33 launches per batch).  E2SEC_PDL=0 falls back to plain ordering.
+// previous one instead of adding a gap per launch (30 launches per batch).  E2SEC_PDL=0 falls back to plain ordering.
 template <class... P, class... A>
 static inline void launch_pdl(e2sec_ctx *ctx, void (*k)(P...), dim3 g, dim3 b, size_t smem, cudaStream_t st, A... a)
 {
