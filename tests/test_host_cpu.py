@@ -211,3 +211,24 @@ def test_record_gather_gloo_world2(tmp_path):
                          capture_output=True, text=True, timeout=300, env=env, cwd=ROOT)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert out.stdout.count("ok") == 2
+
+
+def test_bench_numa_binding_is_harmless_without_topology():
+    """bench.bind_near_gpu keeps a rank near its GPU when the box says where that is; on a box that does not (no sysfs entry
+    for the device, a single node) it changes nothing and says so."""
+    import bench
+
+    class _Props:
+        pci_domain_id, pci_bus_id, pci_device_id = 0xffff, 0xfe, 0x1f            # no such device
+
+    class _Cuda:
+        @staticmethod
+        def get_device_properties(i):
+            return _Props()
+
+    class _Torch:
+        cuda = _Cuda()
+
+    before = os.sched_getaffinity(0)
+    assert bench.bind_near_gpu(_Torch(), 0) is None
+    assert os.sched_getaffinity(0) == before
