@@ -13,7 +13,10 @@
 #define E2_SEG 1024          // points per warp segment in the segmentation kernels
 #define E2_SEG_WARPS 8       // warps per CTA there
 #define E2_TILE 256          // points per tile in the pair-distance kernels
-#define E2_NBINS 256         // bins per refinement pass of the radius selection
+#ifndef E2_NBINS
+#define E2_NBINS 192         // bins per refinement pass of the radius selection (a multiple of 32; the thread-private
+                             // counters of a pass are (E2_NBINS + 2) x 256 bytes per CTA: 192 bins let four CTAs share an SM)
+#endif
 #define E2_CT_SUB 256        // ground points per pruning box (contact.cuh)
 #define E2_CAND_CAP 16384    // candidate keys kept for the final exact selection (one bin of a pass that starts from the
                              // cell table's radius band holds ~0.1 % of an entity's pairs)

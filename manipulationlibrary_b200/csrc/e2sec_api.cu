@@ -559,7 +559,7 @@ static int run_entity_stages(e2sec_ctx *ctx, const Dev &d, bool need_median, boo
         // small fixed grids that stride over the list; otherwise every entity).  The host never waits inside a batch, so the
         // rounds are launched unconditionally; a round with nothing left returns at once.
         const bool bounded = d.radius_mode == E2SEC_RADIUS_BOUNDED;
-        const int grid = ctx->sm_count * 3;
+        const int grid = ctx->sm_count * E2_PAIR_CTAS;
         const int small_grid = bounded ? std::min(FK, ctx->sm_count * 2) : FK;
         const size_t smem = E2_PAIR_SMEM_HIST;
         launch_pdl(ctx, radius_init_kernel, dim3(small_grid), dim3(256), 0, st, d, plan, below_acc, min_above, single, grid);
@@ -1043,7 +1043,7 @@ static int run_radius_only(e2sec_ctx *ctx, const Dev &d)
     const int FK = d.F * d.K;
     PairPlan plan{(unsigned *)ctx->plan_off.p, (unsigned *)ctx->plan_total.p, (unsigned *)ctx->plan_split.p};
     u64 *below_acc = (u64 *)ctx->below_acc.p, *min_above = (u64 *)ctx->min_above.p, *single = (u64 *)ctx->single_count.p;
-    const int grid = ctx->sm_count * 3;
+    const int grid = ctx->sm_count * E2_PAIR_CTAS;
     radius_init_kernel<<<FK, 256, 0, st>>>(d, plan, below_acc, min_above, single, grid); LAUNCHED();      // + the plan of the first pass
     const size_t smem = E2_PAIR_SMEM_HIST;
     for (int round = 0; round < 12; ++round) {     // an operator call may take as many rounds as it needs

@@ -12,7 +12,7 @@
 //                          by the LAST CTA to finish of radius_init_kernel / radius_select_kernel (no launch of its own)
 //   pair_pass_kernel<0>    every pair of the item -> bin = (key - klo) >> shift, counted in thread-private
 //                          uint16 shared-memory counters [bin][thread] (no atomics in the pair loop)
-//   radius_select_kernel   picks the bin holding the lower middle rank, shrinks the interval 256x; when the
+//   radius_select_kernel   picks the bin holding the lower middle rank, shrinks the interval E2_NBINS x; when the
 //                          interval holds <= E2_CAND_CAP pairs switches the entity to "collect"
 //   pair_pass_kernel<1>    appends the keys inside the interval, tracks the smallest key above it
 //   radius_final_kernel    block_select2 over the candidates -> (sqrt(a) + sqrt(b)) / 2
@@ -29,6 +29,13 @@
 #define E2_PAIR_THREADS (E2_TILE / E2_PAIR_IPT)
 #define E2_FLUSH_ITEMS (200 / E2_PAIR_IPT)      // uint16 counters: <= 256 * E2_PAIR_IPT increments per thread per item
 #define E2_PAIR_MAX_SPLIT 8     // a tile pair is cut into up to 8 slices of its j range when there are few of them
+#ifndef E2_PAIR_CTAS
+#define E2_PAIR_CTAS 4          // CTAs of a histogram pass per SM (their counters: (E2_NBINS + 2) x 256 bytes each)
+#endif
+#ifndef E2_SAMPLE_SPAN
+#define E2_SAMPLE_SPAN 1.5      // the sampled interval spans the ranks M / 2 -+ E2_SAMPLE_SPAN sqrt(M): 1.5 = 3 sigma of the
+                                // median's rank (one entity in 370 reopens its interval and takes two or three cheap rounds more)
+#endif
 
 struct PairPlan {
     unsigned *off;      // count + 1 exclusive prefix of TILE PAIRS over the exact path's list
@@ -114,8 +121,8 @@ __device__ __forceinline__ unsigned mix32(unsigned x)
 
 // grid: any number of CTAs of 256 threads, striding over the list.
 // Where the first histogram pass looks: a fixed pseudo-random sample of M pairs puts the median between two of its order
-// statistics, M / 2 -+ 2 sqrt(M) (4 sigma of the median's rank in the sample): a fraction 4 / sqrt(M) of all pairs (3 % at
-// M = 16384), so that one of the 128 .. 256 bins of that pass holds fewer than E2_CAND_CAP pairs up to 10^8 pairs per
+// statistics, M / 2 -+ 1.5 sqrt(M) (3 sigma of the median's rank in the sample): a fraction 3 / sqrt(M) of all pairs (2.3 %
+// at M = 16384), so that one of the 96 .. 192 bins of that pass holds fewer than E2_CAND_CAP pairs up to ~7 * 10^7 pairs per
 // entity -- the collect pass can follow at once.  In BOUNDED mode the interval is cut to the cell table's guaranteed band, and the band alone is used when it is
 // narrow enough for the entity's pair count.  The sample only chooses where to look: the ranks are counted exactly, and
 // radius_select_kernel reopens the interval on the side that is short should the guess ever miss.
@@ -199,7 +206,8 @@ __global__ void __launch_bounds__(E2_SEL_THREADS) radius_init_kernel(Dev d, Pair
                     rs.width = ktop;
                     rs.phase = 1;
                 } else if (klo == 0 || P > 12000000ull) {
-                    // (a band holds ~30 % of the pairs: below 1.2e7 pairs one of its 256 bins fits the candidate buffer as it is)
+                    // (a band holds ~30 % of the pairs: below 1.2e7 pairs one of its bins usually fits the candidate buffer as it is, and
+                    // a second histogram pass over such an entity costs less than the sample)
                     // sqrt(M) >= 4 P / (128 E2_CAND_CAP) would do (a pass uses 128 .. 256 of its bins), but a narrower
                     // interval also means fewer candidates for the collect pass to append: the largest sample that fits
                     // d.cand, except for small entities
@@ -210,7 +218,7 @@ __global__ void __launch_bounds__(E2_SEL_THREADS) radius_init_kernel(Dev d, Pair
         }
         __syncthreads();                   // red[] is reused by the next entity of this CTA; mode is set
         if (mode) {
-            const int M = mode, half = (int)ceil(2.0 * sqrt((double)M));
+            const int M = mode, half = (int)ceil(E2_SAMPLE_SPAN * sqrt((double)M));
             u64 *smp = d.cand + (size_t)fe * E2_CAND_CAP;
             for (int t = threadIdx.x; t < M; t += blockDim.x) {
                 const unsigned h1 = mix32((unsigned)t * 2u + 1u + (unsigned)fe * 0x9e3779b9u), h2 = mix32(h1 + 0x85ebca6bu + (unsigned)t);
@@ -446,7 +454,7 @@ __global__ void __launch_bounds__(E2_PAIR_THREADS) pair_pass_kernel(Dev d, PairP
     if (cur_fe >= 0) flush(cur_fe);
 }
 
-// One warp per listed entity (lanes own 8 consecutive bins each), any number of CTAs of 256 threads striding over the
+// One warp per listed entity (lanes own E2_NBINS / 32 consecutive bins each), any number of CTAs of 256 threads striding over the
 // list; the last CTA to finish plans the next pass (the items of phase `next_phase`).
 __global__ void __launch_bounds__(256) radius_select_kernel(Dev d, PairPlan plan, u64 *below_acc, u64 *single_count, int next_phase, int grid_hint)
 {
